@@ -1,0 +1,203 @@
+/*
+ * m3ae_b200.h — C-ABI of the B200-native M3AE fusion hot path (libm3ae_b200.so).
+ *
+ * The reference (better62/MM-VQA-Healthcare) is pure Python: it has no FFI/plugin interface, every
+ * "kernel" is an implicit PyTorch library call.  This header is therefore the boundary a maintainer
+ * would bind with ctypes underneath the reference's nn.Modules; each entry point names the reference
+ * call sites (file:line, relative to the reference root) whose arithmetic it replaces.
+ *
+ * Conventions (all entry points):
+ *   - plain pointers and sizes only; every buffer (inputs, outputs, saved-for-backward, workspace) is
+ *     caller-allocated DEVICE memory; the library never allocates, frees or retains caller memory;
+ *   - returns 0 on success, a negative M3AE_ERR_* code otherwise; m3ae_last_error() (thread-local)
+ *     describes the failure; host wrappers raise RuntimeError with that text;
+ *   - asynchronous on the cudaStream_t passed as `stream` (void* to keep CUDA types out of the ABI);
+ *   - sm_100a only: refuses to run on any other architecture; there is no CPU fallback;
+ *   - dtype codes: M3AE_F32 / M3AE_BF16.  bf16 is the product path (tcgen05 tensor cores, fp32
+ *     accumulate); f32 is the strict-parity path (1e-4 gate).
+ */
+#ifndef M3AE_B200_H_
+#define M3AE_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define M3AE_B200_VERSION 100
+
+#define M3AE_F32 0
+#define M3AE_BF16 1
+
+#define M3AE_ACT_NONE 0
+#define M3AE_ACT_GELU 1 /* exact erf GELU — HF ACT2FN["gelu"], bert_model.py:421 */
+#define M3AE_ACT_RELU 2 /* decoder FFN, m3ae_decoder.py:45 */
+
+#define M3AE_MAJOR_K 0  /* operand stored [rows = M or N, cols = K], K contiguous */
+#define M3AE_MAJOR_MN 1 /* operand stored [rows = K, cols = M or N], M/N contiguous */
+
+#define M3AE_GEMM_AUTO 0
+#define M3AE_GEMM_TCGEN05 1 /* TMA + tcgen05.mma + TMEM (bf16 inputs only) */
+#define M3AE_GEMM_SIMT 2    /* fp32 FFMA tiles (f32 or bf16 inputs): strict-parity + debugging path */
+
+#define M3AE_OK 0
+#define M3AE_ERR_INVALID (-1)
+#define M3AE_ERR_CUDA (-2)
+#define M3AE_ERR_ARCH (-3)
+#define M3AE_ERR_UNSUPPORTED (-4)
+
+int m3ae_version(void);
+const char* m3ae_last_error(void);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int64_t m3ae_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * GEMM with fused epilogue:  out[M,N] (+)= epi( alpha * A[M,K] · B[N,K]^T )
+ * Replaces nn.Linear at bert_model.py:263,276-277,285-286 (Q/K/V), :361 (attention out-proj),
+ * :426 (FFN up) and :439 (FFN down), m3ae_module.py:235,252 (modality projections),
+ * m3ae_decoder.py:60-61,78-79 (in/out projections), :85 (FFN), :136 (vocab projection), and —
+ * with MN-major operands — their autograd backward (dgrad: dX = dY·W, wgrad: dW = dY^T·X).
+ * Epilogue order = the reference modules': (+bias) -> [aux_out := pre-activation] -> act ->
+ * (* act'(aux_in)) -> dropout -> (+residual)   (BertSelfOutput :361-363, BertIntermediate :426-427,
+ * BertOutput :439-441).
+ * --------------------------------------------------------------------------------------------- */
+typedef struct m3ae_gemm_epilogue_t {
+  void* out;            /* [M,N] row-major, leading dimension ldo (elements) */
+  int32_t out_dtype;    /* M3AE_F32 | M3AE_BF16 */
+  int64_t ldo;
+  const float* bias;    /* [N] fp32 or NULL */
+  int32_t act;          /* M3AE_ACT_* applied after bias */
+  void* aux_out;        /* optional: pre-activation copy, dtype out_dtype, ld ldo */
+  const void* aux_in;   /* optional: forward pre-activation for dact, ld ld_aux_in */
+  int32_t aux_in_dtype;
+  int64_t ld_aux_in;
+  int32_t dact;         /* M3AE_ACT_*: multiply result by act'(aux_in) (backward through the activation) */
+  const void* residual; /* optional [M,N], added last */
+  int32_t res_dtype;
+  int64_t ldr;
+  float drop_p;         /* dropout probability applied before the residual add (0 = off) */
+  uint64_t drop_seed;
+  uint64_t drop_stream; /* distinguishes dropout sites; element index = row*ldo+col */
+  int32_t accumulate;   /* 1: out (fp32) += result (atomic; required when split_k > 1) */
+  float alpha;
+} m3ae_gemm_epilogue_t;
+
+typedef struct m3ae_gemm_problem_t {
+  const void* a; /* logical [M,K] */
+  const void* b; /* logical [N,K] */
+  int64_t lda;   /* elements between consecutive stored rows */
+  int64_t ldb;
+  int32_t a_major; /* M3AE_MAJOR_* */
+  int32_t b_major;
+  int32_t M, N, K;
+  int32_t split_k; /* >= 1; > 1 requires epi.accumulate = 1 and fp32 out */
+  m3ae_gemm_epilogue_t epi;
+} m3ae_gemm_problem_t;
+
+/* Runs 1..4 independent problems in ONE persistent launch (the text and image streams of a fusion
+ * layer pair are independent, m3ae_module.py:276-277, so their GEMMs are co-scheduled). */
+int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n_problems, int32_t in_dtype, int32_t backend, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused scaled-dot-product attention (flash-style: online softmax in registers + warp shuffles,
+ * scores never materialised).  Replaces bert_model.py:301,319-322,325,334,340,342-344
+ * (BertSelfAttention core, self and cross mode) and the attention inside nn.MultiheadAttention at
+ * m3ae_decoder.py:60-61,78-79.
+ *   S = scale * Q K^T + mask[b, key] (+ causal -inf);  P = softmax(S);  P' = dropout(P);  O = P' V
+ * Row r = b*L + i of q/k/v/out holds token i of batch b; head h occupies columns [h*dh, (h+1)*dh).
+ * ld* are row strides in elements, so q/k/v may point into a fused QKV projection buffer.
+ * --------------------------------------------------------------------------------------------- */
+typedef struct m3ae_attn_params_t {
+  const void* q;
+  const void* k;
+  const void* v;
+  int64_t ldq, ldk, ldv;
+  const float* mask; /* additive [B, Lk] fp32 (the reference's [B,1,1,Lk] extended mask) or NULL */
+  void* out;         /* [B*Lq, H*dh] */
+  int64_t ldo;
+  float* lse;        /* [B,H,Lq] log-sum-exp of S, saved for backward */
+  float* probs;      /* optional [B,H,Lq,Lk] fp32: P' (post-dropout, as the reference returns) or NULL */
+  int32_t B, H, Lq, Lk, dh;
+  float scale;
+  int32_t causal;
+  float drop_p;
+  uint64_t drop_seed;
+  uint64_t drop_stream;
+  int32_t dtype;     /* dtype of q,k,v,out (and dq,dk,dv,dout) */
+  /* backward only */
+  const void* dout;  /* [B*Lq, H*dh], ld ldo */
+  void* dq;
+  void* dk;
+  void* dv;
+  int64_t lddq, lddk, lddv;
+  float* delta;      /* workspace [B,H,Lq] fp32: rowsum(dO*O) */
+} m3ae_attn_params_t;
+
+int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream);
+/* dq, dk, dv are fully overwritten. */
+int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * LayerNorm over the last dimension (fp32 statistics, two-pass variance).
+ * Replaces nn.LayerNorm at bert_model.py:363,441 (eps 1e-12), m3ae_module.py:122 (eps 1e-5),
+ * m3ae_decoder.py:46-49 (eps 1e-5).  The residual add and bias are fused into the producing GEMM.
+ * --------------------------------------------------------------------------------------------- */
+int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                       int64_t M, int32_t H, float eps, int32_t dtype, void* stream);
+/* dx = LN'(dy); dgamma/dbeta (+)= column reductions (atomic accumulate into caller-zeroed or
+ * grad-accumulating fp32 buffers); dcolsum (optional, fp32 [H]) += column sums of dx, which is the
+ * bias gradient of the Linear that produced x. */
+int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
+                       void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype,
+                       void* stream);
+
+/* out[N] (fp32) += column sums of x[M,N] (ld elements).  Bias gradients of the projections. */
+int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int32_t dtype, void* stream);
+
+/* dst[i] = (dst_dtype) src[i]  — fp32 master parameters -> bf16 operand cache, activations casts. */
+int m3ae_cast(const void* src, int32_t src_dtype, void* dst, int32_t dst_dtype, int64_t n, void* stream);
+
+/* out[r, :] = a[r, :] + b[:]  (row-broadcast add; modality type embedding, m3ae_module.py:260-263). */
+int m3ae_add_rowvec(const void* a, const float* b, void* out, int64_t M, int32_t N, int32_t in_dtype, int32_t out_dtype,
+                    void* stream);
+
+/* In-place dropout-scale of a gradient: x[i] = keep(i) ? x[i]/(1-p) : 0 with the same Philox stream the
+ * forward GEMM epilogue used (element index = row*ld+col). */
+int m3ae_dropout_apply(const void* x, void* y, int64_t M, int32_t N, int64_t ld, float p, uint64_t seed,
+                       uint64_t stream_id, int32_t dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * KV-cached single-token decoder step (greedy generation).  Replaces one iteration of
+ * Decoder.search_path (m3ae_decoder.py:149-161), which re-runs Decoder.forward on the whole prefix;
+ * only dec_layers[-1] is live (m3ae_decoder.py:131-134 feeds every layer the embedding and keeps
+ * the last result).  See mm-vqa-healthcare_b200/decoder.py for the orchestration.
+ *   attention for ONE query token per (batch, head) against a cache of `len` keys:
+ *   out[b, h*dh:(h+1)*dh] = softmax(scale * q·K^T) V     (no mask: causal prefix / all memory valid)
+ * k/v caches are [B, Lmax, H*dh] (row stride ldk/ldv, batch stride = Lmax*ld).
+ * --------------------------------------------------------------------------------------------- */
+int m3ae_decode_attn(const void* q, int64_t ldq, const void* kcache, const void* vcache, int64_t ldk, int64_t ldv,
+                     int64_t batch_stride_k, int64_t batch_stride_v, void* out, int64_t ldo, int32_t B, int32_t H,
+                     int32_t len, int32_t dh, float scale, int32_t dtype, void* stream);
+
+/* Row-wise argmax over logits [M,N] fp32/bf16 (first maximal index, as torch.argmax) -> int64 ids.
+ * log_softmax (m3ae_decoder.py:151) is monotone and is skipped. */
+int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M, int32_t N, int32_t dtype, void* stream);
+
+/* Decoder input embedding (m3ae_decoder.py:125-127): out[r,:] = 2*E[ids[r],:] + pe[pos[r],:]. */
+int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M,
+                       int32_t D, int32_t out_dtype, void* stream);
+
+/* Test hook: 0 = auto (tensor-core attention for bf16), 2 = force the generic fp32-math attention kernels. */
+int m3ae_set_attention_backend(int32_t backend);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3AE_B200_H_ */

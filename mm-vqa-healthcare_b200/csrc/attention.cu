@@ -1,0 +1,524 @@
+// Fused scaled-dot-product attention, forward and backward, flash-style: scores are never written to
+// HBM; the running max / sum / output live in registers and are combined with warp shuffles.
+// Reference arithmetic: BertSelfAttention core, bert_model.py:301 (QK^T), :319 (/sqrt(dh)), :320-322 (+mask),
+// :325 (softmax), :334 (dropout on probs), :340 (PV), :342-344 (merge heads); nn.MultiheadAttention inside
+// DecoderLayer, m3ae_decoder.py:60-61,78-79 (causal / no mask, dh = 96).
+//
+// This file holds the generic fp32-math kernels (T = float for the strict-parity path, T = bf16 storage
+// with fp32 math as the always-correct reference for the tensor-core kernels in attention_mma.cu).
+// One lane <-> one key inside a 32-key chunk; one warp <-> a few query rows.
+#include "common.cuh"
+
+namespace m3ae {
+void count_launch();
+int attn_fwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);  // attention_mma.cu; returns M3AE_ERR_UNSUPPORTED if shape not covered
+int attn_bwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);
+
+namespace {
+
+constexpr int KC = 32;  // keys per chunk == warp width
+
+template <typename T, int DH, int ROWS_PER_WARP>
+__global__ void __launch_bounds__(128) attn_fwd_kernel(const m3ae_attn_params_t P) {
+  constexpr int WARPS = 4;
+  constexpr int ROWS = WARPS * ROWS_PER_WARP;
+  constexpr int ND = DH / 32;
+  __shared__ float sK[KC][DH + 1];
+  __shared__ float sV[KC][DH];
+  __shared__ float sQ[ROWS][DH];
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int q0 = blockIdx.x * ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const T* __restrict__ Q = (const T*)P.q + (size_t)b * P.Lq * P.ldq + (size_t)h * DH;
+  const T* __restrict__ K = (const T*)P.k + (size_t)b * P.Lk * P.ldk + (size_t)h * DH;
+  const T* __restrict__ V = (const T*)P.v + (size_t)b * P.Lk * P.ldv + (size_t)h * DH;
+  const float* __restrict__ mask = P.mask ? P.mask + (size_t)b * P.Lk : nullptr;
+
+  for (int idx = threadIdx.x; idx < ROWS * DH; idx += 128) {
+    const int r = idx / DH, d = idx % DH;
+    sQ[r][d] = (q0 + r < P.Lq) ? to_f32<T>(Q[(size_t)(q0 + r) * P.ldq + d]) : 0.f;
+  }
+  float m[ROWS_PER_WARP], l[ROWS_PER_WARP], o[ROWS_PER_WARP][ND];
+#pragma unroll
+  for (int r = 0; r < ROWS_PER_WARP; ++r) {
+    m[r] = -INFINITY; l[r] = 0.f;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) o[r][i] = 0.f;
+  }
+  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+
+  for (int k0 = 0; k0 < P.Lk; k0 += KC) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < KC * DH; idx += 128) {
+      const int r = idx / DH, d = idx % DH;
+      const bool ok = k0 + r < P.Lk;
+      sK[r][d] = ok ? to_f32<T>(K[(size_t)(k0 + r) * P.ldk + d]) : 0.f;
+      sV[r][d] = ok ? to_f32<T>(V[(size_t)(k0 + r) * P.ldv + d]) : 0.f;
+    }
+    __syncthreads();
+    const int key = k0 + lane;
+    const float madd = (key < P.Lk) ? (mask ? mask[key] : 0.f) : -INFINITY;
+#pragma unroll
+    for (int r = 0; r < ROWS_PER_WARP; ++r) {
+      const int lr = warp * ROWS_PER_WARP + r;
+      const int qi = q0 + lr;
+      if (qi >= P.Lq) break;  // warp-uniform
+      float s = 0.f;
+#pragma unroll 16
+      for (int d = 0; d < DH; ++d) s = fmaf(sQ[lr][d], sK[lane][d], s);
+      s = s * P.scale + madd;
+      if (P.causal && key > qi) s = -INFINITY;
+      const float m_new = fmaxf(m[r], warp_max(s));
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float p = expf(s - m_use);
+      const float corr = expf(m[r] - m_use);
+      l[r] = l[r] * corr + warp_sum(p);
+      m[r] = m_new;
+      float pd = p;
+      if (P.drop_p > 0.f && key < P.Lk) {
+        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
+        pd = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? p * keep_scale : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < ND; ++i) o[r][i] *= corr;
+#pragma unroll 8
+      for (int j = 0; j < KC; ++j) {
+        const float pj = __shfl_sync(0xffffffffu, pd, j);
+#pragma unroll
+        for (int i = 0; i < ND; ++i) o[r][i] = fmaf(pj, sV[j][i * 32 + lane], o[r][i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < ROWS_PER_WARP; ++r) {
+    const int qi = q0 + warp * ROWS_PER_WARP + r;
+    if (qi >= P.Lq) break;
+    const float inv = l[r] > 0.f ? 1.0f / l[r] : 0.f;
+    T* out = (T*)P.out + (size_t)(b * P.Lq + qi) * P.ldo + (size_t)h * DH;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) out[i * 32 + lane] = from_f32<T>(o[r][i] * inv);
+    if (lane == 0 && P.lse) P.lse[((size_t)b * P.H + h) * P.Lq + qi] = m[r] + logf(l[r]);
+  }
+}
+
+// probs[b,h,i,j] = dropout(exp(scale*q_i.k_j + mask_j - lse_i))  -- only for output_attentions=True
+template <typename T, int DH>
+__global__ void __launch_bounds__(128) attn_probs_kernel(const m3ae_attn_params_t P) {
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int qi = blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (qi >= P.Lq) return;
+  const T* __restrict__ Q = (const T*)P.q + (size_t)(b * P.Lq + qi) * P.ldq + (size_t)h * DH;
+  const T* __restrict__ K = (const T*)P.k + (size_t)b * P.Lk * P.ldk + (size_t)h * DH;
+  const float lse = P.lse[((size_t)b * P.H + h) * P.Lq + qi];
+  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  float* out = P.probs + (((size_t)b * P.H + h) * P.Lq + qi) * (size_t)P.Lk;
+  for (int key = lane; key < P.Lk; key += 32) {
+    float s = 0.f;
+    for (int d = 0; d < DH; ++d) s = fmaf(to_f32<T>(Q[d]), to_f32<T>(K[(size_t)key * P.ldk + d]), s);
+    s = s * P.scale + (P.mask ? P.mask[(size_t)b * P.Lk + key] : 0.f);
+    float p = (P.causal && key > qi) ? 0.f : expf(s - lse);
+    if (P.drop_p > 0.f) {
+      const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
+      p = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? p * keep_scale : 0.f;
+    }
+    out[key] = p;
+  }
+}
+
+// delta[b,h,i] = sum_d dO[i,d] * O[i,d]
+template <typename T, int DH>
+__global__ void __launch_bounds__(128) attn_delta_kernel(const m3ae_attn_params_t P) {
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int qi = blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (qi >= P.Lq) return;
+  const size_t off = (size_t)(b * P.Lq + qi) * P.ldo + (size_t)h * DH;
+  const T* __restrict__ O = (const T*)P.out + off;
+  const T* __restrict__ dO = (const T*)P.dout + off;
+  float s = 0.f;
+  for (int d = lane; d < DH; d += 32) s += to_f32<T>(O[d]) * to_f32<T>(dO[d]);
+  s = warp_sum(s);
+  if (lane == 0) P.delta[((size_t)b * P.H + h) * P.Lq + qi] = s;
+}
+
+// dQ_i = scale * sum_j dS_ij K_j,  dS_ij = P_ij (dP_ij - delta_i),  dP_ij = keep_ij/(1-p) * dO_i.V_j
+template <typename T, int DH>
+__global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params_t P) {
+  constexpr int RPW = 4, ROWS = 16, ND = DH / 32;
+  __shared__ float sK[KC][DH + 1];
+  __shared__ float sV[KC][DH + 1];
+  __shared__ float sQ[ROWS][DH];
+  __shared__ float sdO[ROWS][DH];
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int q0 = blockIdx.x * ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const T* __restrict__ Q = (const T*)P.q + (size_t)b * P.Lq * P.ldq + (size_t)h * DH;
+  const T* __restrict__ K = (const T*)P.k + (size_t)b * P.Lk * P.ldk + (size_t)h * DH;
+  const T* __restrict__ V = (const T*)P.v + (size_t)b * P.Lk * P.ldv + (size_t)h * DH;
+  const T* __restrict__ dO = (const T*)P.dout + (size_t)b * P.Lq * P.ldo + (size_t)h * DH;
+  const float* __restrict__ mask = P.mask ? P.mask + (size_t)b * P.Lk : nullptr;
+  for (int idx = threadIdx.x; idx < ROWS * DH; idx += 128) {
+    const int r = idx / DH, d = idx % DH;
+    const bool ok = q0 + r < P.Lq;
+    sQ[r][d] = ok ? to_f32<T>(Q[(size_t)(q0 + r) * P.ldq + d]) : 0.f;
+    sdO[r][d] = ok ? to_f32<T>(dO[(size_t)(q0 + r) * P.ldo + d]) : 0.f;
+  }
+  float lse[RPW], dl[RPW], dq[RPW][ND];
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    const int qi = q0 + warp * RPW + r;
+    const size_t si = ((size_t)b * P.H + h) * P.Lq + (qi < P.Lq ? qi : 0);
+    lse[r] = P.lse[si]; dl[r] = P.delta[si];
+#pragma unroll
+    for (int i = 0; i < ND; ++i) dq[r][i] = 0.f;
+  }
+  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  for (int k0 = 0; k0 < P.Lk; k0 += KC) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < KC * DH; idx += 128) {
+      const int r = idx / DH, d = idx % DH;
+      const bool ok = k0 + r < P.Lk;
+      sK[r][d] = ok ? to_f32<T>(K[(size_t)(k0 + r) * P.ldk + d]) : 0.f;
+      sV[r][d] = ok ? to_f32<T>(V[(size_t)(k0 + r) * P.ldv + d]) : 0.f;
+    }
+    __syncthreads();
+    const int key = k0 + lane;
+    const float madd = (key < P.Lk) ? (mask ? mask[key] : 0.f) : -INFINITY;
+#pragma unroll
+    for (int r = 0; r < RPW; ++r) {
+      const int lr = warp * RPW + r;
+      const int qi = q0 + lr;
+      if (qi >= P.Lq) break;
+      float s = 0.f, dp = 0.f;
+#pragma unroll 16
+      for (int d = 0; d < DH; ++d) {
+        s = fmaf(sQ[lr][d], sK[lane][d], s);
+        dp = fmaf(sdO[lr][d], sV[lane][d], dp);
+      }
+      s = s * P.scale + madd;
+      if (P.causal && key > qi) s = -INFINITY;
+      const float p = expf(s - lse[r]);
+      if (P.drop_p > 0.f && key < P.Lk) {
+        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
+        dp = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? dp * keep_scale : 0.f;
+      }
+      const float ds = p * (dp - dl[r]) * P.scale;
+#pragma unroll 8
+      for (int j = 0; j < KC; ++j) {
+        const float dsj = __shfl_sync(0xffffffffu, ds, j);
+#pragma unroll
+        for (int i = 0; i < ND; ++i) dq[r][i] = fmaf(dsj, sK[j][i * 32 + lane], dq[r][i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    const int qi = q0 + warp * RPW + r;
+    if (qi >= P.Lq) break;
+    T* out = (T*)P.dq + (size_t)(b * P.Lq + qi) * P.lddq + (size_t)h * DH;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) out[i * 32 + lane] = from_f32<T>(dq[r][i]);
+  }
+}
+
+// dV_j = sum_i P'_ij dO_i,  dK_j = scale * sum_i dS_ij Q_i  (one lane <-> one query inside a 32-query chunk)
+template <typename T, int DH>
+__global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const m3ae_attn_params_t P) {
+  constexpr int RPW = 4, ROWS = 16, ND = DH / 32;
+  __shared__ float sQ[KC][DH + 1];
+  __shared__ float sdO[KC][DH + 1];
+  __shared__ float sK[ROWS][DH];
+  __shared__ float sV[ROWS][DH];
+  __shared__ float sLse[KC], sDl[KC];
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int kbase = blockIdx.x * ROWS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const T* __restrict__ Q = (const T*)P.q + (size_t)b * P.Lq * P.ldq + (size_t)h * DH;
+  const T* __restrict__ K = (const T*)P.k + (size_t)b * P.Lk * P.ldk + (size_t)h * DH;
+  const T* __restrict__ V = (const T*)P.v + (size_t)b * P.Lk * P.ldv + (size_t)h * DH;
+  const T* __restrict__ dO = (const T*)P.dout + (size_t)b * P.Lq * P.ldo + (size_t)h * DH;
+  const float* __restrict__ mask = P.mask ? P.mask + (size_t)b * P.Lk : nullptr;
+  for (int idx = threadIdx.x; idx < ROWS * DH; idx += 128) {
+    const int r = idx / DH, d = idx % DH;
+    const bool ok = kbase + r < P.Lk;
+    sK[r][d] = ok ? to_f32<T>(K[(size_t)(kbase + r) * P.ldk + d]) : 0.f;
+    sV[r][d] = ok ? to_f32<T>(V[(size_t)(kbase + r) * P.ldv + d]) : 0.f;
+  }
+  float dk[RPW][ND], dv[RPW][ND], madd[RPW];
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    const int key = kbase + warp * RPW + r;
+    madd[r] = (mask && key < P.Lk) ? mask[key] : 0.f;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) { dk[r][i] = 0.f; dv[r][i] = 0.f; }
+  }
+  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  for (int i0 = 0; i0 < P.Lq; i0 += KC) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < KC * DH; idx += 128) {
+      const int r = idx / DH, d = idx % DH;
+      const bool ok = i0 + r < P.Lq;
+      sQ[r][d] = ok ? to_f32<T>(Q[(size_t)(i0 + r) * P.ldq + d]) : 0.f;
+      sdO[r][d] = ok ? to_f32<T>(dO[(size_t)(i0 + r) * P.ldo + d]) : 0.f;
+    }
+    if (threadIdx.x < KC) {
+      const int qi = i0 + threadIdx.x;
+      const size_t si = ((size_t)b * P.H + h) * P.Lq + (qi < P.Lq ? qi : 0);
+      sLse[threadIdx.x] = P.lse[si];
+      sDl[threadIdx.x] = P.delta[si];
+    }
+    __syncthreads();
+    const int qi = i0 + lane;
+    const bool q_ok = qi < P.Lq;
+#pragma unroll
+    for (int r = 0; r < RPW; ++r) {
+      const int lr = warp * RPW + r;
+      const int key = kbase + lr;
+      if (key >= P.Lk) break;
+      float s = 0.f, dp = 0.f;
+#pragma unroll 16
+      for (int d = 0; d < DH; ++d) {
+        s = fmaf(sK[lr][d], sQ[lane][d], s);
+        dp = fmaf(sV[lr][d], sdO[lane][d], dp);
+      }
+      s = s * P.scale + madd[r];
+      float p = (q_ok && !(P.causal && key > qi)) ? expf(s - sLse[lane]) : 0.f;
+      float pd = p;
+      if (P.drop_p > 0.f && q_ok) {
+        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
+        const bool keep = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p);
+        pd = keep ? p * keep_scale : 0.f;
+        dp = keep ? dp * keep_scale : 0.f;
+      }
+      const float ds = p * (dp - sDl[lane]) * P.scale;
+#pragma unroll 8
+      for (int j = 0; j < KC; ++j) {
+        const float pj = __shfl_sync(0xffffffffu, pd, j);
+        const float dsj = __shfl_sync(0xffffffffu, ds, j);
+#pragma unroll
+        for (int i = 0; i < ND; ++i) {
+          dv[r][i] = fmaf(pj, sdO[j][i * 32 + lane], dv[r][i]);
+          dk[r][i] = fmaf(dsj, sQ[j][i * 32 + lane], dk[r][i]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    const int key = kbase + warp * RPW + r;
+    if (key >= P.Lk) break;
+    T* ok_ = (T*)P.dk + (size_t)(b * P.Lk + key) * P.lddk + (size_t)h * DH;
+    T* ov_ = (T*)P.dv + (size_t)(b * P.Lk + key) * P.lddv + (size_t)h * DH;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) {
+      ok_[i * 32 + lane] = from_f32<T>(dk[r][i]);
+      ov_[i * 32 + lane] = from_f32<T>(dv[r][i]);
+    }
+  }
+}
+
+// One query token per (b,h) against a KV cache of `len` keys (greedy decoding step).
+// HBM-bound: reads len*dh*2*sizeof(T) bytes per (b,h); grid = B*H CTAs of 4 warps splitting the keys.
+template <typename T, int DH>
+__global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ q, int64_t ldq, const T* __restrict__ kc,
+                                                         const T* __restrict__ vc, int64_t ldk, int64_t ldv, int64_t bsk,
+                                                         int64_t bsv, T* __restrict__ out, int64_t ldo, int H, int len,
+                                                         float scale) {
+  constexpr int ND = DH / 32;
+  __shared__ float sm[4], sl[4], so[4][DH];
+  const int b = blockIdx.x / H, h = blockIdx.x % H;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const T* Q = q + (size_t)b * ldq + (size_t)h * DH;
+  const T* K = kc + (size_t)b * bsk + (size_t)h * DH;
+  const T* V = vc + (size_t)b * bsv + (size_t)h * DH;
+  float qv[ND];
+#pragma unroll
+  for (int i = 0; i < ND; ++i) qv[i] = to_f32<T>(Q[i * 32 + lane]) * scale;
+  float m = -INFINITY, l = 0.f, o[ND];
+#pragma unroll
+  for (int i = 0; i < ND; ++i) o[i] = 0.f;
+  // each warp takes keys warp, warp+4, ...; lanes split the head dimension (coalesced 64/192-byte rows)
+  for (int j = warp; j < len; j += 4) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) s = fmaf(qv[i], to_f32<T>(K[(size_t)j * ldk + i * 32 + lane]), s);
+    s = warp_sum(s);
+    const float m_new = fmaxf(m, s);
+    const float corr = expf(m - m_new), p = expf(s - m_new);
+    l = l * corr + p;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) o[i] = o[i] * corr + p * to_f32<T>(V[(size_t)j * ldv + i * 32 + lane]);
+    m = m_new;
+  }
+  if (lane == 0) { sm[warp] = m; sl[warp] = l; }
+#pragma unroll
+  for (int i = 0; i < ND; ++i) so[warp][i * 32 + lane] = o[i];
+  __syncthreads();
+  if (warp == 0) {
+    float M = fmaxf(fmaxf(sm[0], sm[1]), fmaxf(sm[2], sm[3]));
+    float L = 0.f;
+    float acc[ND];
+#pragma unroll
+    for (int i = 0; i < ND; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float c = (sm[w] == -INFINITY) ? 0.f : expf(sm[w] - M);
+      L += sl[w] * c;
+#pragma unroll
+      for (int i = 0; i < ND; ++i) acc[i] += so[w][i * 32 + lane] * c;
+    }
+    T* O = out + (size_t)b * ldo + (size_t)h * DH;
+#pragma unroll
+    for (int i = 0; i < ND; ++i) O[i * 32 + lane] = from_f32<T>(acc[i] / L);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) argmax_rows_kernel(const T* __restrict__ x, int64_t ld, int64_t* __restrict__ out, int N) {
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  const T* row = x + (size_t)blockIdx.x * ld;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int c = threadIdx.x; c < N; c += 256) {
+    const float v = to_f32<T>(row[c]);
+    if (v > best || (v == best && c < bi)) { best = v; bi = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+    out[blockIdx.x] = (int64_t)bi;
+  }
+}
+
+template <typename TO>
+__global__ void decoder_embed_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ pos,
+                                     const float* __restrict__ table, const float* __restrict__ pe, TO* __restrict__ out, int D) {
+  // target_embed += positional_encoding(target_embed)  ==> 2*E[id] + pe[pos]   (m3ae_decoder.py:125-127, :36)
+  const int64_t r = blockIdx.x;
+  const float* e = table + (size_t)ids[r] * D;
+  const float* p = pe + (size_t)pos[r] * D;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    const float v = e[d];
+    out[(size_t)r * D + d] = from_f32<TO>(v + (v + p[d]));
+  }
+}
+
+template <typename T>
+int launch_generic_fwd(const m3ae_attn_params_t* p, cudaStream_t st) {
+  if (p->dh == 64) {
+    dim3 grid((p->Lq + 31) / 32, p->H, p->B);
+    attn_fwd_kernel<T, 64, 8><<<grid, 128, 0, st>>>(*p);
+  } else {
+    dim3 grid((p->Lq + 15) / 16, p->H, p->B);
+    attn_fwd_kernel<T, 96, 4><<<grid, 128, 0, st>>>(*p);
+  }
+  count_launch();
+  if (p->probs) {
+    dim3 g2((p->Lq + 3) / 4, p->H, p->B);
+    if (p->dh == 64) attn_probs_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
+    else attn_probs_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
+    count_launch();
+  }
+  return M3AE_OK;
+}
+
+template <typename T>
+int launch_generic_bwd(const m3ae_attn_params_t* p, cudaStream_t st) {
+  dim3 g0((p->Lq + 3) / 4, p->H, p->B);
+  dim3 g1((p->Lq + 15) / 16, p->H, p->B);
+  dim3 g2((p->Lk + 15) / 16, p->H, p->B);
+  if (p->dh == 64) {
+    attn_delta_kernel<T, 64><<<g0, 128, 0, st>>>(*p);
+    attn_bwd_dq_kernel<T, 64><<<g1, 128, 0, st>>>(*p);
+    attn_bwd_dkv_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
+  } else {
+    attn_delta_kernel<T, 96><<<g0, 128, 0, st>>>(*p);
+    attn_bwd_dq_kernel<T, 96><<<g1, 128, 0, st>>>(*p);
+    attn_bwd_dkv_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
+  }
+  count_launch(); count_launch(); count_launch();
+  return M3AE_OK;
+}
+
+int validate(const m3ae_attn_params_t* p, bool bwd) {
+  M3AE_CHECK(p != nullptr, M3AE_ERR_INVALID, "attention: null params");
+  M3AE_CHECK(p->B > 0 && p->H > 0 && p->Lq > 0 && p->Lk > 0, M3AE_ERR_INVALID, "attention: empty shape B=%d H=%d Lq=%d Lk=%d", p->B, p->H, p->Lq, p->Lk);
+  M3AE_CHECK(p->dh == 64 || p->dh == 96, M3AE_ERR_UNSUPPORTED, "attention: head dim %d unsupported (64 for the fusion stack, 96 for the decoder)", p->dh);
+  M3AE_CHECK(p->dtype == M3AE_F32 || p->dtype == M3AE_BF16, M3AE_ERR_INVALID, "attention: bad dtype %d", p->dtype);
+  M3AE_CHECK(p->q && p->k && p->v && p->out && p->lse, M3AE_ERR_INVALID, "attention: null tensor pointer");
+  M3AE_CHECK(p->drop_p >= 0.f && p->drop_p < 1.f, M3AE_ERR_INVALID, "attention: dropout %f not in [0,1)", p->drop_p);
+  if (bwd) M3AE_CHECK(p->dout && p->dq && p->dk && p->dv && p->delta, M3AE_ERR_INVALID, "attention backward: null gradient pointer");
+  return M3AE_OK;
+}
+
+}  // namespace
+
+int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
+  int rc = validate(p, false);
+  if (rc) return rc;
+  if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
+    rc = attn_fwd_mma(p, st);
+    if (rc != M3AE_ERR_UNSUPPORTED) return rc;
+  }
+  if (p->dtype == M3AE_BF16) launch_generic_fwd<bf16>(p, st);
+  else launch_generic_fwd<float>(p, st);
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
+  int rc = validate(p, true);
+  if (rc) return rc;
+  if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
+    rc = attn_bwd_mma(p, st);
+    if (rc != M3AE_ERR_UNSUPPORTED) return rc;
+  }
+  if (p->dtype == M3AE_BF16) launch_generic_bwd<bf16>(p, st);
+  else launch_generic_bwd<float>(p, st);
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int decode_attn(const void* q, int64_t ldq, const void* kc, const void* vc, int64_t ldk, int64_t ldv, int64_t bsk, int64_t bsv,
+                void* out, int64_t ldo, int B, int H, int len, int dh, float scale, int dtype, cudaStream_t st) {
+  M3AE_CHECK(B > 0 && H > 0 && len > 0, M3AE_ERR_INVALID, "decode_attn: empty shape");
+  M3AE_CHECK(dh == 64 || dh == 96, M3AE_ERR_UNSUPPORTED, "decode_attn: head dim %d unsupported", dh);
+#define DA(T, DH) decode_attn_kernel<T, DH><<<B * H, 128, 0, st>>>((const T*)q, ldq, (const T*)kc, (const T*)vc, ldk, ldv, bsk, bsv, (T*)out, ldo, H, len, scale)
+  if (dtype == M3AE_BF16) { if (dh == 64) DA(bf16, 64); else DA(bf16, 96); }
+  else { if (dh == 64) DA(float, 64); else DA(float, 96); }
+#undef DA
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int argmax_rows(const void* x, int64_t ld, int64_t* out, int64_t M, int N, int dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "argmax_rows: empty input");
+  if (dtype == M3AE_BF16) argmax_rows_kernel<bf16><<<(unsigned)M, 256, 0, st>>>((const bf16*)x, ld, out, N);
+  else argmax_rows_kernel<float><<<(unsigned)M, 256, 0, st>>>((const float*)x, ld, out, N);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M, int D,
+                  int out_dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0 && D > 0, M3AE_ERR_INVALID, "decoder_embed: empty input");
+  if (out_dtype == M3AE_BF16) decoder_embed_kernel<bf16><<<(unsigned)M, 256, 0, st>>>(ids, pos, table, pe, (bf16*)out, D);
+  else decoder_embed_kernel<float><<<(unsigned)M, 256, 0, st>>>(ids, pos, table, pe, (float*)out, D);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+}  // namespace m3ae

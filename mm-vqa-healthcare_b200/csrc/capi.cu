@@ -1,0 +1,168 @@
+// extern "C" surface of libm3ae_b200.so (declared in include/m3ae_b200.h): argument validation,
+// architecture gate (sm_100 only, no CPU fallback), dispatch to the kernels.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace m3ae {
+
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static int g_sms[64];
+static int g_major[64];
+static std::once_flag g_dev_once[64];
+
+static int query_device(int* sms, int* major) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    set_last_error("cudaGetDevice failed: %s", cudaGetErrorString(e));
+    return M3AE_ERR_CUDA;
+  }
+  std::call_once(g_dev_once[dev], [dev] {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) {
+      g_sms[dev] = prop.multiProcessorCount;
+      g_major[dev] = prop.major;
+    }
+  });
+  *sms = g_sms[dev];
+  *major = g_major[dev];
+  return M3AE_OK;
+}
+
+int sm_count() {
+  int sms = 0, major = 0;
+  query_device(&sms, &major);
+  return sms > 0 ? sms : 148;
+}
+
+int check_device_sm100() {
+  int sms = 0, major = 0;
+  int rc = query_device(&sms, &major);
+  if (rc) return rc;
+  if (major != 10) {
+    set_last_error("libm3ae_b200 requires an sm_100 (B200) device; current device has compute capability major %d. There is no fallback path.", major);
+    return M3AE_ERR_ARCH;
+  }
+  return M3AE_OK;
+}
+
+int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t stream);
+int gemm_simt_launch(const m3ae_gemm_problem_t* probs, int n, int in_dtype, cudaStream_t stream);
+int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
+int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
+int layernorm_fwd(const void*, const float*, const float*, void*, float*, float*, int64_t, int, float, int, cudaStream_t);
+int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, cudaStream_t);
+int colsum(const void*, float*, int64_t, int, int64_t, int, cudaStream_t);
+int cast(const void*, int, void*, int, int64_t, cudaStream_t);
+int add_rowvec(const void*, const float*, void*, int64_t, int, int, int, cudaStream_t);
+int dropout_apply(const void*, void*, int64_t, int, int64_t, float, uint64_t, uint64_t, int, cudaStream_t);
+int decode_attn(const void*, int64_t, const void*, const void*, int64_t, int64_t, int64_t, int64_t, void*, int64_t, int, int, int, int, float, int, cudaStream_t);
+int argmax_rows(const void*, int64_t, int64_t*, int64_t, int, int, cudaStream_t);
+int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, void*, int64_t, int, int, cudaStream_t);
+
+static int g_attn_backend = M3AE_GEMM_AUTO;
+
+}  // namespace m3ae
+
+using namespace m3ae;
+
+#define ARCH_GATE()                     \
+  do {                                  \
+    int _rc = check_device_sm100();     \
+    if (_rc) return _rc;                \
+  } while (0)
+
+extern "C" {
+
+int m3ae_version(void) { return M3AE_B200_VERSION; }
+const char* m3ae_last_error(void) { return g_err; }
+int64_t m3ae_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n, int32_t in_dtype, int32_t backend, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(problems != nullptr && n >= 1 && n <= 4, M3AE_ERR_INVALID, "m3ae_gemm: need 1..4 problems, got %d", n);
+  M3AE_CHECK(in_dtype == M3AE_F32 || in_dtype == M3AE_BF16, M3AE_ERR_INVALID, "m3ae_gemm: bad input dtype %d", in_dtype);
+  for (int i = 0; i < n; ++i) {
+    const m3ae_gemm_problem_t& g = problems[i];
+    M3AE_CHECK(g.a && g.b && g.epi.out, M3AE_ERR_INVALID, "m3ae_gemm: null operand in problem %d", i);
+    M3AE_CHECK(g.epi.drop_p >= 0.f && g.epi.drop_p < 1.f, M3AE_ERR_INVALID, "m3ae_gemm: dropout %f not in [0,1)", g.epi.drop_p);
+    M3AE_CHECK(g.epi.dact == M3AE_ACT_NONE || g.epi.aux_in != nullptr, M3AE_ERR_INVALID, "m3ae_gemm: dact needs aux_in");
+    M3AE_CHECK(g.split_k <= 1 || (!g.epi.bias && g.epi.act == M3AE_ACT_NONE && !g.epi.residual && g.epi.dact == M3AE_ACT_NONE && g.epi.drop_p == 0.f && !g.epi.aux_out),
+               M3AE_ERR_INVALID, "m3ae_gemm: split_k > 1 supports only the plain accumulate epilogue");
+  }
+  if (backend == M3AE_GEMM_AUTO) backend = (in_dtype == M3AE_BF16) ? M3AE_GEMM_TCGEN05 : M3AE_GEMM_SIMT;
+  if (backend == M3AE_GEMM_TCGEN05) {
+    M3AE_CHECK(in_dtype == M3AE_BF16, M3AE_ERR_UNSUPPORTED, "m3ae_gemm: the tcgen05 backend takes bf16 operands (fp32 parity runs use the SIMT backend)");
+    return gemm_tcgen05_launch(problems, n, (cudaStream_t)stream);
+  }
+  M3AE_CHECK(backend == M3AE_GEMM_SIMT, M3AE_ERR_INVALID, "m3ae_gemm: unknown backend %d", backend);
+  return gemm_simt_launch(problems, n, in_dtype, (cudaStream_t)stream);
+}
+
+/* Test hook: 0 = auto (tensor-core kernels for bf16), 2 = force the generic fp32-math attention kernels. */
+int m3ae_set_attention_backend(int32_t backend) { g_attn_backend = backend; return M3AE_OK; }
+
+int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_fwd(p, g_attn_backend, (cudaStream_t)stream); }
+int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_bwd(p, g_attn_backend, (cudaStream_t)stream); }
+
+int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd, int64_t M, int32_t H, float eps, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(x && gamma && beta && y && mean && rstd, M3AE_ERR_INVALID, "layernorm_fwd: null pointer");
+  return layernorm_fwd(x, gamma, beta, y, mean, rstd, M, H, eps, dtype, (cudaStream_t)stream);
+}
+int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(dy && x && mean && rstd && gamma && dx, M3AE_ERR_INVALID, "layernorm_bwd: null pointer");
+  return layernorm_bwd(dy, x, mean, rstd, gamma, dx, dgamma, dbeta, dcolsum, M, H, dtype, (cudaStream_t)stream);
+}
+int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(x && out, M3AE_ERR_INVALID, "colsum: null pointer");
+  return colsum(x, out, M, N, ld, dtype, (cudaStream_t)stream);
+}
+int m3ae_cast(const void* src, int32_t sd, void* dst, int32_t dd, int64_t n, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK((src && dst) || n == 0, M3AE_ERR_INVALID, "cast: null pointer");
+  return cast(src, sd, dst, dd, n, (cudaStream_t)stream);
+}
+int m3ae_add_rowvec(const void* a, const float* b, void* out, int64_t M, int32_t N, int32_t in_dtype, int32_t out_dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(a && b && out, M3AE_ERR_INVALID, "add_rowvec: null pointer");
+  return add_rowvec(a, b, out, M, N, in_dtype, out_dtype, (cudaStream_t)stream);
+}
+int m3ae_dropout_apply(const void* x, void* y, int64_t M, int32_t N, int64_t ld, float p, uint64_t seed, uint64_t stream_id, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(x && y, M3AE_ERR_INVALID, "dropout_apply: null pointer");
+  return dropout_apply(x, y, M, N, ld, p, seed, stream_id, dtype, (cudaStream_t)stream);
+}
+int m3ae_decode_attn(const void* q, int64_t ldq, const void* kcache, const void* vcache, int64_t ldk, int64_t ldv, int64_t bsk, int64_t bsv, void* out, int64_t ldo, int32_t B, int32_t H, int32_t len, int32_t dh, float scale, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(q && kcache && vcache && out, M3AE_ERR_INVALID, "decode_attn: null pointer");
+  return decode_attn(q, ldq, kcache, vcache, ldk, ldv, bsk, bsv, out, ldo, B, H, len, dh, scale, dtype, (cudaStream_t)stream);
+}
+int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M, int32_t N, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(logits && out_ids, M3AE_ERR_INVALID, "argmax_rows: null pointer");
+  return argmax_rows(logits, ld, out_ids, M, N, dtype, (cudaStream_t)stream);
+}
+int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M, int32_t D, int32_t out_dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(ids && pos && table && pe && out, M3AE_ERR_INVALID, "decoder_embed: null pointer");
+  return decoder_embed(ids, pos, table, pe, out, M, D, out_dtype, (cudaStream_t)stream);
+}
+
+}  // extern "C"

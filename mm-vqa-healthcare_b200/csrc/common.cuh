@@ -1,0 +1,286 @@
+// Shared device/host helpers for the M3AE fusion hot path on sm_100a.
+// PTX wrappers (mbarrier, TMA, tcgen05/TMEM), Philox dropout RNG, dtype helpers,
+// and the GEMM epilogue that is shared by the tcgen05 and the SIMT (fp32 parity) GEMMs.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/m3ae_b200.h"
+
+namespace m3ae {
+
+// ---------------------------------------------------------------- errors
+void set_last_error(const char* fmt, ...);
+#define M3AE_CHECK(cond, code, ...)                \
+  do {                                             \
+    if (!(cond)) {                                 \
+      ::m3ae::set_last_error(__VA_ARGS__);         \
+      return (code);                               \
+    }                                              \
+  } while (0)
+
+#define M3AE_CUDA(expr)                                                              \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      ::m3ae::set_last_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                             __FILE__, __LINE__);                                    \
+      return M3AE_ERR_CUDA;                                                          \
+    }                                                                                \
+  } while (0)
+
+int check_device_sm100();  // 0 when the current device is sm_100, else error code (and sets last error)
+int sm_count();
+
+// ---------------------------------------------------------------- dtype helpers
+typedef __nv_bfloat16 bf16;
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<bf16>(bf16 v) { return __bfloat162float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float load_as_f32(const void* p, int dtype, size_t idx) {
+  return dtype == M3AE_BF16 ? __bfloat162float(((const bf16*)p)[idx]) : ((const float*)p)[idx];
+}
+__device__ __forceinline__ void store_from_f32(void* p, int dtype, size_t idx, float v) {
+  if (dtype == M3AE_BF16) ((bf16*)p)[idx] = __float2bfloat16_rn(v);
+  else ((float*)p)[idx] = v;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
+  __nv_bfloat162 t = *reinterpret_cast<__nv_bfloat162*>(&v);
+  return __bfloat1622float2(t);
+}
+
+// ---------------------------------------------------------------- activations
+// Exact erf GELU (reference: HF ACT2FN["gelu"], bert_model.py:421,427).
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+  const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+// ---------------------------------------------------------------- Philox4x32-10 (counter-based RNG for dropout)
+struct Philox {
+  uint32_t key0, key1;
+  __device__ __forceinline__ Philox(uint64_t seed) : key0((uint32_t)seed), key1((uint32_t)(seed >> 32)) {}
+  __device__ __forceinline__ uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
+    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+    uint32_t k0 = key0, k1 = key1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+      c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+      k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+// Keep-decision for element `idx` of dropout stream `stream_id`: one Philox call yields 4 lanes,
+// element idx uses lane idx&3 of counter idx>>2, so forward and backward regenerate identical masks.
+__device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
+  Philox ph(seed);
+  const uint4 r = ph(idx >> 2, stream_id);
+  const uint32_t lane = (uint32_t)(idx & 3);
+  const uint32_t v = lane == 0 ? r.x : lane == 1 ? r.y : lane == 2 ? r.z : r.w;
+  // uniform in [0,1): keep when u >= p
+  return (float)(v >> 8) * (1.0f / 16777216.0f) >= p;
+}
+// 4 consecutive elements starting at idx (idx % 4 == 0): returns a 4-bit keep mask.
+__device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
+  Philox ph(seed);
+  const uint4 r = ph(idx >> 2, stream_id);
+  const float s = 1.0f / 16777216.0f;
+  uint32_t m = 0;
+  m |= ((float)(r.x >> 8) * s >= p) ? 1u : 0u;
+  m |= ((float)(r.y >> 8) * s >= p) ? 2u : 0u;
+  m |= ((float)(r.z >> 8) * s >= p) ? 4u : 0u;
+  m |= ((float)(r.w >> 8) * s >= p) ? 8u : 0u;
+  return m;
+}
+
+// ---------------------------------------------------------------- warp helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------- GEMM epilogue (shared)
+// Device-side view of m3ae_gemm_epilogue_t (include/m3ae_b200.h).
+struct EpiDev {
+  void* out; int out_dtype; int64_t ldo;
+  const float* bias;
+  int act;                 // M3AE_ACT_*
+  void* aux_out;           // pre-activation copy (dtype = out_dtype, ld = ldo) or null
+  const void* aux_in;      // pre-activation of the forward op (dtype = aux_in_dtype, ld = ld_aux_in) for dact
+  int aux_in_dtype; int64_t ld_aux_in;
+  int dact;                // M3AE_ACT_* whose derivative multiplies the result (uses aux_in)
+  const void* residual; int res_dtype; int64_t ldr;
+  float drop_p; uint64_t drop_seed; uint64_t drop_stream;
+  int accumulate;          // 1: atomicAdd into fp32 out (split-K partials / grad accumulation)
+  float alpha;
+};
+
+// Applies the epilogue to `n` consecutive columns [col, col+n) of row `row` whose accumulators are acc[0..n).
+// Order matches the reference modules: dense(+bias) -> act -> dropout -> +residual
+// (BertSelfOutput bert_model.py:361-363, BertIntermediate :426-427, BertOutput :439-441).
+template <int NV>
+__device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int64_t col, int n_valid, float (&acc)[NV]) {
+  const float alpha = e.alpha;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) acc[j] *= alpha;
+  if (e.bias) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (j < n_valid) acc[j] += __ldg(e.bias + col + j);
+  }
+  if (e.aux_out) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (j < n_valid) store_from_f32(e.aux_out, e.out_dtype, (size_t)(row * e.ldo + col + j), acc[j]);
+  }
+  if (e.act == M3AE_ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) acc[j] = gelu_erf(acc[j]);
+  } else if (e.act == M3AE_ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) acc[j] = fmaxf(acc[j], 0.0f);
+  }
+  if (e.dact != M3AE_ACT_NONE) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (j < n_valid) {
+      const float u = load_as_f32(e.aux_in, e.aux_in_dtype, (size_t)(row * e.ld_aux_in + col + j));
+      acc[j] *= (e.dact == M3AE_ACT_GELU) ? gelu_erf_grad(u) : (u > 0.0f ? 1.0f : 0.0f);
+    }
+  }
+  if (e.drop_p > 0.0f) {
+    const float inv = 1.0f / (1.0f - e.drop_p);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (j < n_valid) {
+      const bool keep = dropout_keep(e.drop_seed, e.drop_stream, (uint64_t)(row * e.ldo + col + j), e.drop_p);
+      acc[j] = keep ? acc[j] * inv : 0.0f;
+    }
+  }
+  if (e.residual) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (j < n_valid) acc[j] += load_as_f32(e.residual, e.res_dtype, (size_t)(row * e.ldr + col + j));
+  }
+}
+
+// ---------------------------------------------------------------- PTX: mbarrier / TMA / tcgen05
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)m) : "memory");
+}
+// 2-D tiled TMA load global -> shared, completion signalled on `bar` (complete_tx::bytes).
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"((uint64_t)m), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], single-CTA, kind::f16 (bf16/fp16 in, fp32 accumulate)
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrive on `bar` once every previously issued tcgen05.mma of this thread has completed.
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread i <-> TMEM lane base+i).
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n"
+      ".reg .b32 rx;\n"
+      ".reg .pred px;\n"
+      "elect.sync rx|px, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, px;\n"
+      "}\n"
+      : "=r"(pred)::"memory");
+  return pred != 0;
+}
+
+}  // namespace m3ae

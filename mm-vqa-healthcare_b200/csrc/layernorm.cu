@@ -1,0 +1,315 @@
+// LayerNorm forward/backward, one warp per row, 128-bit vector loads, fp32 two-pass statistics.
+// HBM-bound: forward moves 2*M*H*sizeof(T) (+8*M) bytes, backward 3*M*H*sizeof(T) (+8*M).
+// Reference: nn.LayerNorm at bert_model.py:363,441 (eps=1e-12), m3ae_module.py:122, m3ae_decoder.py:46-49.
+#include "common.cuh"
+
+namespace m3ae {
+void count_launch();
+namespace {
+
+template <typename T> struct Vec;  // 16-byte vector of T
+template <> struct Vec<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const float* p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ static void store(float* p, const float (&v)[4]) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+};
+template <> struct Vec<bf16> {
+  static constexpr int N = 8;
+  __device__ static void load(const bf16* p, float (&v)[8]) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p);
+    float2 f;
+    f = unpack_bf16x2(t.x); v[0] = f.x; v[1] = f.y;
+    f = unpack_bf16x2(t.y); v[2] = f.x; v[3] = f.y;
+    f = unpack_bf16x2(t.z); v[4] = f.x; v[5] = f.y;
+    f = unpack_bf16x2(t.w); v[6] = f.x; v[7] = f.y;
+  }
+  __device__ static void store(bf16* p, const float (&v)[8]) {
+    uint4 t;
+    t.x = pack_bf16x2(v[0], v[1]); t.y = pack_bf16x2(v[2], v[3]);
+    t.z = pack_bf16x2(v[4], v[5]); t.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = t;
+  }
+};
+
+constexpr int LN_WARPS = 4;
+
+// H == HV * 32 * Vec<T>::N exactly (768 or 1536 columns on this path).
+template <typename T, int HV>
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, T* __restrict__ y,
+                                                              float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                              int64_t M, int H, float eps) {
+  constexpr int VN = Vec<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const T* xr = x + row * H;
+  float v[HV][VN];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < HV; ++i) {
+    Vec<T>::load(xr + (i * 32 + lane) * VN, v[i]);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) s += v[i][j];
+  }
+  const float mean = warp_sum(s) / (float)H;
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < HV; ++i)
+#pragma unroll
+    for (int j = 0; j < VN; ++j) { const float d = v[i][j] - mean; ss += d * d; }
+  const float var = warp_sum(ss) / (float)H;
+  const float rstd = rsqrtf(var + eps);
+  if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+  T* yr = y + row * H;
+#pragma unroll
+  for (int i = 0; i < HV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    float o[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) o[j] = (v[i][j] - mean) * rstd * __ldg(gamma + c + j) + __ldg(beta + c + j);
+    Vec<T>::store(yr + c, o);
+  }
+}
+
+// Backward: each warp walks rows row0, row0+stride, ... and keeps per-lane column partials of
+// dgamma / dbeta / colsum(dx) in registers; one smem reduction + one atomicAdd per column per CTA.
+template <typename T, int HV>
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                              const float* __restrict__ gamma, T* __restrict__ dx,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                              float* __restrict__ dcolsum, int64_t M, int H) {
+  constexpr int VN = Vec<T>::N;
+  extern __shared__ float red[];  // [LN_WARPS][H]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float g[HV][VN], pg[HV][VN], pb[HV][VN], pc[HV][VN];
+#pragma unroll
+  for (int i = 0; i < HV; ++i)
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      g[i][j] = __ldg(gamma + (i * 32 + lane) * VN + j);
+      pg[i][j] = 0.f; pb[i][j] = 0.f; pc[i][j] = 0.f;
+    }
+  const float invH = 1.0f / (float)H;
+  for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < M; row += (int64_t)gridDim.x * LN_WARPS) {
+    const float mu = mean[row], rs = rstd[row];
+    float xh[HV][VN], gd[HV][VN];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      float dv[VN];
+      Vec<T>::load(x + row * H + c, xh[i]);
+      Vec<T>::load(dy + row * H + c, dv);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        xh[i][j] = (xh[i][j] - mu) * rs;
+        pg[i][j] += dv[j] * xh[i][j];
+        pb[i][j] += dv[j];
+        gd[i][j] = dv[j] * g[i][j];
+        c1 += gd[i][j];
+        c2 += gd[i][j] * xh[i][j];
+      }
+    }
+    c1 = warp_sum(c1) * invH;
+    c2 = warp_sum(c2) * invH;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      float o[VN];
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        o[j] = rs * (gd[i][j] - c1 - xh[i][j] * c2);
+        pc[i][j] += to_f32<T>(from_f32<T>(o[j]));  // column sum of what downstream consumers actually read
+      }
+      Vec<T>::store(dx + row * H + c, o);
+    }
+  }
+  // CTA reduction of the three column partials, one at a time through the same smem buffer.
+  for (int which = 0; which < 3; ++which) {
+    float* dst = which == 0 ? dgamma : which == 1 ? dbeta : dcolsum;
+    if (dst == nullptr) continue;  // uniform
+#pragma unroll
+    for (int i = 0; i < HV; ++i)
+#pragma unroll
+      for (int j = 0; j < VN; ++j)
+        red[warp * H + (i * 32 + lane) * VN + j] = which == 0 ? pg[i][j] : which == 1 ? pb[i][j] : pc[i][j];
+    __syncthreads();
+    for (int c = threadIdx.x; c < H; c += LN_WARPS * 32) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < LN_WARPS; ++w) s += red[w * H + c];
+      atomicAdd(dst + c, s);
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void colsum_kernel(const T* __restrict__ x, float* __restrict__ out, int64_t M, int N, int64_t ld, int rows_per_cta) {
+  // block = (32 columns) x (8 row lanes); each CTA covers rows [blockIdx.y*rows_per_cta, ...)
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+  const int64_t r1 = min(M, r0 + rows_per_cta);
+  float s = 0.f;
+  if (c < N)
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += 8) s += to_f32<T>(x[r * ld + c]);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    atomicAdd(out + c, t);
+  }
+}
+
+template <typename TS, typename TD>
+__global__ void cast_kernel(const TS* __restrict__ src, TD* __restrict__ dst, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = from_f32<TD>(to_f32<TS>(src[i]));
+}
+// 8 fp32 -> 8 bf16 per thread-iteration (n % 8 == 0, aligned)
+__global__ void cast_f32_bf16_vec_kernel(const float4* __restrict__ src, uint4* __restrict__ dst, int64_t n8) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const float4 a = src[2 * i], b = src[2 * i + 1];
+    uint4 o;
+    o.x = pack_bf16x2(a.x, a.y); o.y = pack_bf16x2(a.z, a.w);
+    o.z = pack_bf16x2(b.x, b.y); o.w = pack_bf16x2(b.z, b.w);
+    dst[i] = o;
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void add_rowvec_kernel(const TI* __restrict__ a, const float* __restrict__ b, TO* __restrict__ out, int64_t M, int N) {
+  const int64_t total = M * N;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+    out[i] = from_f32<TO>(to_f32<TI>(a[i]) + __ldg(b + (i % N)));
+}
+
+template <typename T>
+__global__ void dropout_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int N, int64_t ld, float p,
+                                     uint64_t seed, uint64_t stream_id) {
+  const int64_t total = M * N;
+  const float inv = 1.0f / (1.0f - p);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t r = i / N, c = i % N;
+    const int64_t e = r * ld + c;
+    y[e] = dropout_keep(seed, stream_id, (uint64_t)e, p) ? from_f32<T>(to_f32<T>(x[e]) * inv) : from_f32<T>(0.f);
+  }
+}
+
+}  // namespace
+
+int layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd, int64_t M, int H,
+                  float eps, int dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
+  const unsigned grid = (unsigned)((M + LN_WARPS - 1) / LN_WARPS);
+#define LN_FWD(T, HV) ln_fwd_kernel<T, HV><<<grid, LN_WARPS * 32, 0, st>>>((const T*)x, gamma, beta, (T*)y, mean, rstd, M, H, eps)
+  if (dtype == M3AE_BF16 && H == 768) LN_FWD(bf16, 3);
+  else if (dtype == M3AE_BF16 && H == 1536) LN_FWD(bf16, 6);
+  else if (dtype == M3AE_F32 && H == 768) LN_FWD(float, 6);
+  else if (dtype == M3AE_F32 && H == 1536) LN_FWD(float, 12);
+  else M3AE_CHECK(false, M3AE_ERR_UNSUPPORTED, "layernorm: unsupported (dtype=%d, H=%d); H must be 768 or 1536", dtype, H);
+#undef LN_FWD
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx,
+                  float* dgamma, float* dbeta, float* dcolsum, int64_t M, int H, int dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
+  int64_t want = (M + LN_WARPS - 1) / LN_WARPS;
+  const int64_t cap = (int64_t)sm_count() * 4;
+  const unsigned grid = (unsigned)(want < cap ? want : cap);
+  const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
+#define LN_BWD(T, HV)                                                                                                     \
+  ln_bwd_kernel<T, HV><<<grid, LN_WARPS * 32, smem, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
+                                                          dbeta, dcolsum, M, H)
+  if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3);
+  else if (dtype == M3AE_BF16 && H == 1536) LN_BWD(bf16, 6);
+  else if (dtype == M3AE_F32 && H == 768) LN_BWD(float, 6);
+  else if (dtype == M3AE_F32 && H == 1536) LN_BWD(float, 12);
+  else M3AE_CHECK(false, M3AE_ERR_UNSUPPORTED, "layernorm: unsupported (dtype=%d, H=%d); H must be 768 or 1536", dtype, H);
+#undef LN_BWD
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int colsum(const void* x, float* out, int64_t M, int N, int64_t ld, int dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "colsum: empty input");
+  const int col_blocks = (N + 31) / 32;
+  int row_blocks = (int)((int64_t)sm_count() * 8 / col_blocks);
+  if (row_blocks < 1) row_blocks = 1;
+  if ((int64_t)row_blocks * 64 > M) row_blocks = (int)((M + 63) / 64);
+  const int rows_per = (int)((M + row_blocks - 1) / row_blocks);
+  dim3 grid(col_blocks, row_blocks), block(32, 8);
+  if (dtype == M3AE_BF16) colsum_kernel<bf16><<<grid, block, 0, st>>>((const bf16*)x, out, M, N, ld, rows_per);
+  else colsum_kernel<float><<<grid, block, 0, st>>>((const float*)x, out, M, N, ld, rows_per);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int cast(const void* src, int sd, void* dst, int dd, int64_t n, cudaStream_t st) {
+  if (n == 0) return M3AE_OK;
+  const int threads = 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (sd == M3AE_F32 && dd == M3AE_BF16 && n % 8 == 0 && ((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0) {
+    const int64_t n8 = n / 8;
+    int64_t b = (n8 + threads - 1) / threads;
+    cast_f32_bf16_vec_kernel<<<(unsigned)(b < cap ? b : cap), threads, 0, st>>>((const float4*)src, (uint4*)dst, n8);
+  } else {
+    int64_t b = (n + threads - 1) / threads;
+    const unsigned grid = (unsigned)(b < cap ? b : cap);
+    if (sd == M3AE_F32 && dd == M3AE_BF16) cast_kernel<float, bf16><<<grid, threads, 0, st>>>((const float*)src, (bf16*)dst, n);
+    else if (sd == M3AE_BF16 && dd == M3AE_F32) cast_kernel<bf16, float><<<grid, threads, 0, st>>>((const bf16*)src, (float*)dst, n);
+    else if (sd == M3AE_F32 && dd == M3AE_F32) cast_kernel<float, float><<<grid, threads, 0, st>>>((const float*)src, (float*)dst, n);
+    else cast_kernel<bf16, bf16><<<grid, threads, 0, st>>>((const bf16*)src, (bf16*)dst, n);
+  }
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int add_rowvec(const void* a, const float* b, void* out, int64_t M, int N, int in_dtype, int out_dtype, cudaStream_t st) {
+  M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "add_rowvec: empty input");
+  const int threads = 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  int64_t blocks = (M * N + threads - 1) / threads;
+  const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+  if (in_dtype == M3AE_F32 && out_dtype == M3AE_F32) add_rowvec_kernel<float, float><<<grid, threads, 0, st>>>((const float*)a, b, (float*)out, M, N);
+  else if (in_dtype == M3AE_F32 && out_dtype == M3AE_BF16) add_rowvec_kernel<float, bf16><<<grid, threads, 0, st>>>((const float*)a, b, (bf16*)out, M, N);
+  else if (in_dtype == M3AE_BF16 && out_dtype == M3AE_BF16) add_rowvec_kernel<bf16, bf16><<<grid, threads, 0, st>>>((const bf16*)a, b, (bf16*)out, M, N);
+  else add_rowvec_kernel<bf16, float><<<grid, threads, 0, st>>>((const bf16*)a, b, (float*)out, M, N);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int dropout_apply(const void* x, void* y, int64_t M, int N, int64_t ld, float p, uint64_t seed, uint64_t stream_id, int dtype,
+                  cudaStream_t st) {
+  M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "dropout_apply: empty input");
+  M3AE_CHECK(p >= 0.f && p < 1.f, M3AE_ERR_INVALID, "dropout probability %f not in [0,1)", p);
+  const int threads = 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  int64_t blocks = (M * N + threads - 1) / threads;
+  const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+  if (dtype == M3AE_BF16) dropout_apply_kernel<bf16><<<grid, threads, 0, st>>>((const bf16*)x, (bf16*)y, M, N, ld, p, seed, stream_id);
+  else dropout_apply_kernel<float><<<grid, threads, 0, st>>>((const float*)x, (float*)y, M, N, ld, p, seed, stream_id);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+}  // namespace m3ae

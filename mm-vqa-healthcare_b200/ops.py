@@ -1,0 +1,240 @@
+"""Tensor-level wrappers over the C-ABI (libm3ae_b200.so).  torch is used for device memory and streams only.
+
+Every function here launches hand-written sm_100a kernels; none has a PyTorch fallback.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, BF16, F32, GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, MAJOR_K, MAJOR_MN  # noqa: F401
+
+
+def _code(dtype):
+    if dtype == torch.float32:
+        return F32
+    if dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"unsupported dtype {dtype}: the M3AE B200 path takes float32 or bfloat16")
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("m3ae_b200 ops need CUDA tensors (sm_100a); there is no CPU path")
+
+
+def launch_count():
+    return int(L.load().m3ae_launch_count())
+
+
+def set_attention_backend(backend):
+    L.check(L.load().m3ae_set_attention_backend(int(backend)), "m3ae_set_attention_backend")
+
+
+class GemmSpec:
+    """One problem of a grouped launch: out (+)= epi(alpha * A[M,K] · B[N,K]^T).
+
+    a: [M,K] (a_major=K) or [K,M] (a_major=MN) 2-D tensor with unit inner stride; likewise b with N.
+    """
+
+    def __init__(self, a, b, out, *, a_major=MAJOR_K, b_major=MAJOR_K, bias=None, act=ACT_NONE, aux_out=None,
+                 aux_in=None, dact=ACT_NONE, residual=None, drop_p=0.0, drop_seed=0, drop_stream=0, accumulate=False,
+                 split_k=1, alpha=1.0):
+        _need_cuda(a, b, out, bias, aux_out, aux_in, residual)
+        assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
+        assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+        assert a.dtype == b.dtype
+        M, K = (a.shape if a_major == MAJOR_K else (a.shape[1], a.shape[0]))
+        N, Kb = (b.shape if b_major == MAJOR_K else (b.shape[1], b.shape[0]))
+        if K != Kb:
+            raise ValueError(f"GEMM contraction mismatch: A gives K={K}, B gives K={Kb}")
+        if tuple(out.shape) != (M, N):
+            raise ValueError(f"GEMM output shape {tuple(out.shape)} != ({M},{N})")
+        if bias is not None:
+            assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
+        for t in (aux_out, aux_in, residual):
+            if t is not None:
+                assert tuple(t.shape) == (M, N) and t.stride(1) == 1
+        if aux_out is not None:
+            assert aux_out.dtype == out.dtype and aux_out.stride(0) == out.stride(0)
+        self.in_dtype = a.dtype
+        self.keep = (a, b, out, bias, aux_out, aux_in, residual)  # keep tensors alive until launch returns
+        p = L.GemmProblem()
+        p.a, p.b = a.data_ptr(), b.data_ptr()
+        p.lda, p.ldb = a.stride(0), b.stride(0)
+        p.a_major, p.b_major = a_major, b_major
+        p.M, p.N, p.K = M, N, K
+        p.split_k = split_k
+        e = p.epi
+        e.out, e.out_dtype, e.ldo = out.data_ptr(), _code(out.dtype), out.stride(0)
+        e.bias = bias.data_ptr() if bias is not None else None
+        e.act = act
+        e.aux_out = aux_out.data_ptr() if aux_out is not None else None
+        if aux_in is not None:
+            e.aux_in, e.aux_in_dtype, e.ld_aux_in = aux_in.data_ptr(), _code(aux_in.dtype), aux_in.stride(0)
+        e.dact = dact
+        if residual is not None:
+            e.residual, e.res_dtype, e.ldr = residual.data_ptr(), _code(residual.dtype), residual.stride(0)
+        e.drop_p, e.drop_seed, e.drop_stream = float(drop_p), int(drop_seed), int(drop_stream)
+        e.accumulate = 1 if accumulate else 0
+        e.alpha = float(alpha)
+        self.problem = p
+
+
+def gemm_group(specs, backend=GEMM_AUTO):
+    """Run 1..4 independent GEMMs in one persistent launch."""
+    n = len(specs)
+    arr = (L.GemmProblem * n)(*[s.problem for s in specs])
+    in_dtype = specs[0].in_dtype
+    assert all(s.in_dtype == in_dtype for s in specs)
+    L.check(L.load().m3ae_gemm(arr, n, _code(in_dtype), backend, _stream()), "m3ae_gemm")
+
+
+def gemm(a, b, out, backend=GEMM_AUTO, **kw):
+    gemm_group([GemmSpec(a, b, out, **kw)], backend)
+    return out
+
+
+def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, scale=None, causal=False, drop_p=0.0,
+                drop_seed=0, drop_stream=0, dout=None, dq=None, dk=None, dv=None, delta=None):
+    _need_cuda(q, k, v, out, lse, mask, probs, dout, dq, dk, dv, delta)
+    for t in (q, k, v, out):
+        assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
+    assert q.shape[0] == B * Lq and k.shape[0] == B * Lk and v.shape[0] == B * Lk and out.shape[0] == B * Lq
+    assert lse.dtype == torch.float32 and lse.numel() == B * H * Lq and lse.is_contiguous()
+    if mask is not None:
+        assert mask.dtype == torch.float32 and mask.numel() == B * Lk and mask.is_contiguous()
+    if probs is not None:
+        assert probs.dtype == torch.float32 and probs.numel() == B * H * Lq * Lk and probs.is_contiguous()
+    p = L.AttnParams()
+    p.q, p.k, p.v = q.data_ptr(), k.data_ptr(), v.data_ptr()
+    p.ldq, p.ldk, p.ldv = q.stride(0), k.stride(0), v.stride(0)
+    p.mask = mask.data_ptr() if mask is not None else None
+    p.out, p.ldo = out.data_ptr(), out.stride(0)
+    p.lse = lse.data_ptr()
+    p.probs = probs.data_ptr() if probs is not None else None
+    p.B, p.H, p.Lq, p.Lk, p.dh = B, H, Lq, Lk, dh
+    p.scale = float(scale if scale is not None else dh ** -0.5)
+    p.causal = 1 if causal else 0
+    p.drop_p, p.drop_seed, p.drop_stream = float(drop_p), int(drop_seed), int(drop_stream)
+    p.dtype = _code(q.dtype)
+    if dout is not None:
+        for t in (dout, dq, dk, dv):
+            assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
+        assert dout.stride(0) == out.stride(0)
+        assert delta.dtype == torch.float32 and delta.numel() == B * H * Lq
+        p.dout, p.dq, p.dk, p.dv = dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
+        p.lddq, p.lddk, p.lddv = dq.stride(0), dk.stride(0), dv.stride(0)
+        p.delta = delta.data_ptr()
+    return p
+
+
+def attn_fwd(q, k, v, out, lse, **kw):
+    p = attn_params(q, k, v, out, lse, **kw)
+    L.check(L.load().m3ae_attn_fwd(C.byref(p), _stream()), "m3ae_attn_fwd")
+    return out
+
+
+def attn_bwd(q, k, v, out, lse, **kw):
+    p = attn_params(q, k, v, out, lse, **kw)
+    L.check(L.load().m3ae_attn_bwd(C.byref(p), _stream()), "m3ae_attn_bwd")
+
+
+def layernorm_fwd(x, gamma, beta, eps, y=None, mean=None, rstd=None):
+    _need_cuda(x, gamma, beta)
+    assert x.is_contiguous() and gamma.dtype == torch.float32 and beta.dtype == torch.float32
+    H = x.shape[-1]
+    M = x.numel() // H
+    y = torch.empty_like(x) if y is None else y
+    mean = torch.empty(M, dtype=torch.float32, device=x.device) if mean is None else mean
+    rstd = torch.empty(M, dtype=torch.float32, device=x.device) if rstd is None else rstd
+    L.check(L.load().m3ae_layernorm_fwd(_ptr(x), _ptr(gamma), _ptr(beta), _ptr(y), _ptr(mean), _ptr(rstd), M, H,
+                                        float(eps), _code(x.dtype), _stream()), "m3ae_layernorm_fwd")
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma=None, dbeta=None, dcolsum=None, dx=None):
+    """dgamma / dbeta / dcolsum are accumulated into (+=); pass zeroed fp32 buffers for plain gradients."""
+    _need_cuda(dy, x, mean, rstd, gamma, dgamma, dbeta, dcolsum)
+    assert dy.is_contiguous() and x.is_contiguous() and dy.dtype == x.dtype
+    H = x.shape[-1]
+    M = x.numel() // H
+    dx = torch.empty_like(x) if dx is None else dx
+    L.check(L.load().m3ae_layernorm_bwd(_ptr(dy), _ptr(x), _ptr(mean), _ptr(rstd), _ptr(gamma), _ptr(dx), _ptr(dgamma),
+                                        _ptr(dbeta), _ptr(dcolsum), M, H, _code(x.dtype), _stream()),
+            "m3ae_layernorm_bwd")
+    return dx
+
+
+def colsum(x, out):
+    """out[N] (fp32) += column sums of the 2-D tensor x[M,N]."""
+    _need_cuda(x, out)
+    assert x.dim() == 2 and x.stride(1) == 1 and out.dtype == torch.float32 and out.numel() == x.shape[1]
+    L.check(L.load().m3ae_colsum(_ptr(x), _ptr(out), x.shape[0], x.shape[1], x.stride(0), _code(x.dtype), _stream()),
+            "m3ae_colsum")
+    return out
+
+
+def cast(src, dst):
+    _need_cuda(src, dst)
+    assert src.is_contiguous() and dst.is_contiguous() and src.numel() == dst.numel()
+    L.check(L.load().m3ae_cast(_ptr(src), _code(src.dtype), _ptr(dst), _code(dst.dtype), src.numel(), _stream()),
+            "m3ae_cast")
+    return dst
+
+
+def add_rowvec(a, b, out):
+    _need_cuda(a, b, out)
+    assert a.is_contiguous() and out.is_contiguous() and b.dtype == torch.float32 and b.is_contiguous()
+    N = a.shape[-1]
+    L.check(L.load().m3ae_add_rowvec(_ptr(a), _ptr(b), _ptr(out), a.numel() // N, N, _code(a.dtype), _code(out.dtype),
+                                     _stream()), "m3ae_add_rowvec")
+    return out
+
+
+def dropout_apply(x, y, p, seed, stream_id):
+    _need_cuda(x, y)
+    assert x.dim() == 2 and x.stride(1) == 1 and y.stride() == x.stride() and x.dtype == y.dtype
+    L.check(L.load().m3ae_dropout_apply(_ptr(x), _ptr(y), x.shape[0], x.shape[1], x.stride(0), float(p), int(seed),
+                                        int(stream_id), _code(x.dtype), _stream()), "m3ae_dropout_apply")
+    return y
+
+
+def decode_attn(q, kcache, vcache, out, *, H, length, dh, scale=None):
+    """q/out: [B, H*dh]; caches: [B, Lmax, H*dh]."""
+    _need_cuda(q, kcache, vcache, out)
+    B = q.shape[0]
+    assert kcache.dim() == 3 and kcache.stride(2) == 1 and vcache.stride(2) == 1
+    L.check(L.load().m3ae_decode_attn(_ptr(q), q.stride(0), _ptr(kcache), _ptr(vcache), kcache.stride(1), vcache.stride(1),
+                                      kcache.stride(0), vcache.stride(0), _ptr(out), out.stride(0), B, H, int(length), dh,
+                                      float(scale if scale is not None else dh ** -0.5), _code(q.dtype), _stream()),
+            "m3ae_decode_attn")
+    return out
+
+
+def argmax_rows(logits, out=None):
+    _need_cuda(logits)
+    assert logits.dim() == 2 and logits.stride(1) == 1
+    out = torch.empty(logits.shape[0], dtype=torch.int64, device=logits.device) if out is None else out
+    L.check(L.load().m3ae_argmax_rows(_ptr(logits), logits.stride(0), _ptr(out), logits.shape[0], logits.shape[1],
+                                      _code(logits.dtype), _stream()), "m3ae_argmax_rows")
+    return out
+
+
+def decoder_embed(ids, pos, table, pe, out):
+    _need_cuda(ids, pos, table, pe, out)
+    assert ids.dtype == torch.int64 and pos.dtype == torch.int32 and table.dtype == torch.float32 and pe.dtype == torch.float32
+    assert table.is_contiguous() and pe.is_contiguous() and out.is_contiguous()
+    D = table.shape[1]
+    L.check(L.load().m3ae_decoder_embed(_ptr(ids), _ptr(pos), _ptr(table), _ptr(pe), _ptr(out), ids.numel(), D,
+                                        _code(out.dtype), _stream()), "m3ae_decoder_embed")
+    return out

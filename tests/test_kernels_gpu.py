@@ -1,0 +1,303 @@
+"""Op-level parity of every C-ABI kernel against plain PyTorch fp32 math on the same (seeded) inputs.
+
+These are the kernel unit tests; layer/model parity against the reference oracle lives in test_parity_gpu.py.
+Tolerances: fp32 path 1e-4 relative (north_star), bf16 path 2e-2 relative, both written next to each check.
+"""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import m3ae_b200  # noqa: E402
+from m3ae_b200 import ops  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def max_rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-12)).item()
+
+
+def rnd(*shape, dtype=torch.float32, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed + sum(shape))
+    return (torch.randn(*shape, generator=g) * scale).to(DEV).to(dtype)
+
+
+# ----------------------------------------------------------------------------- GEMM
+GEMM_SHAPES = [(128, 256, 64), (256, 512, 128), (2048, 768, 768), (2600, 2304, 768), (300, 498, 768), (20800 // 8, 768, 3072)]
+
+
+def _gemm_ref(a, b, a_major, b_major):
+    A = a.float() if a_major == ops.MAJOR_K else a.float().t()
+    B = b.float() if b_major == ops.MAJOR_K else b.float().t()
+    return A @ B.t()
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_TCGEN05])
+@pytest.mark.parametrize("shape", GEMM_SHAPES)
+def test_gemm_bf16_kmajor(backend, shape):
+    M, N, K = shape
+    a, b = rnd(M, K, dtype=torch.bfloat16), rnd(N, K, dtype=torch.bfloat16, seed=1)
+    out = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    ops.gemm(a, b, out, backend=backend)
+    ref = _gemm_ref(a, b, 0, 0)
+    assert max_rel(out, ref) < 1e-4, f"fp32-out bf16 GEMM {shape}: max_rel {max_rel(out, ref):.3e}"  # fp32 accumulate of exact bf16 products
+    outb = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    ops.gemm(a, b, outb, backend=backend)
+    assert rel_err(outb, ref) < 4e-3  # bf16 output rounding only (2^-9)
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_TCGEN05])
+@pytest.mark.parametrize("majors", [(0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("shape", [(128, 256, 64), (2048, 768, 2304), (768, 3072, 2600), (2304, 768, 2048)])
+def test_gemm_bf16_mn_major(backend, majors, shape):
+    M, N, K = shape
+    am, bm = majors
+    a = rnd(M, K, dtype=torch.bfloat16) if am == 0 else rnd(K, M, dtype=torch.bfloat16)
+    b = rnd(N, K, dtype=torch.bfloat16, seed=1) if bm == 0 else rnd(K, N, dtype=torch.bfloat16, seed=1)
+    out = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    ops.gemm(a, b, out, backend=backend, a_major=am, b_major=bm)
+    ref = _gemm_ref(a, b, am, bm)
+    assert max_rel(out, ref) < 1e-4, f"majors {majors} shape {shape}: max_rel {max_rel(out, ref):.3e}"
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_TCGEN05])
+def test_gemm_splitk_accumulate(backend):
+    # wgrad shape: dW[N_w, K_w] += dY^T X over 2600 tokens, accumulated onto an existing gradient
+    tokens, Nw, Kw = 2600, 768, 3072
+    dy, x = rnd(tokens, Nw, dtype=torch.bfloat16), rnd(tokens, Kw, dtype=torch.bfloat16, seed=1)
+    base = rnd(Nw, Kw, seed=2)
+    out = base.clone()
+    ops.gemm(dy, x, out, backend=backend, a_major=1, b_major=1, accumulate=True, split_k=4)
+    ref = base + dy.float().t() @ x.float()
+    assert max_rel(out, ref) < 1e-4, f"split-K accumulate: {max_rel(out, ref):.3e}"
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_TCGEN05])
+def test_gemm_epilogues(backend):
+    M, N, K = 650, 3072, 768
+    a, w = rnd(M, K, dtype=torch.bfloat16), rnd(N, K, dtype=torch.bfloat16, scale=0.05, seed=1)
+    bias = rnd(N, seed=2)
+    res = rnd(M, N, dtype=torch.bfloat16, seed=3)
+    pre = a.float() @ w.float().t() + bias
+    # bias + GELU with pre-activation side output (BertIntermediate)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    aux = torch.empty_like(out)
+    ops.gemm(a, w, out, backend=backend, bias=bias, act=ops.ACT_GELU, aux_out=aux)
+    assert rel_err(aux, pre) < 4e-3
+    assert rel_err(out, torch.nn.functional.gelu(pre)) < 4e-3
+    # bias + residual (BertSelfOutput / BertOutput before the LayerNorm)
+    ops.gemm(a, w, out, backend=backend, bias=bias, residual=res)
+    assert rel_err(out, pre + res.float()) < 4e-3
+    # relu
+    ops.gemm(a, w, out, backend=backend, bias=bias, act=ops.ACT_RELU)
+    assert rel_err(out, torch.relu(pre)) < 4e-3
+    # backward through GELU: (dY W) * gelu'(u) + residual   (dgrad epilogue)
+    u = rnd(M, K, dtype=torch.bfloat16, seed=4)
+    dy = rnd(M, N, dtype=torch.bfloat16, seed=5)
+    r2 = rnd(M, K, dtype=torch.bfloat16, seed=6)
+    o2 = torch.empty(M, K, dtype=torch.bfloat16, device=DEV)
+    ops.gemm(dy, w, o2, backend=backend, b_major=1, aux_in=u, dact=ops.ACT_GELU, residual=r2)
+    uf = u.float().requires_grad_(True)
+    torch.nn.functional.gelu(uf).sum().backward()
+    ref2 = (dy.float() @ w.float()) * uf.grad + r2.float()
+    assert rel_err(o2, ref2) < 4e-3, f"dgelu epilogue: {rel_err(o2, ref2):.3e}"
+
+
+def test_gemm_group_two_streams():
+    # text (M=32*B) and image (M=325*B) problems of one layer pair in a single launch
+    B = 8
+    xa, xb = rnd(B * 32, 768, dtype=torch.bfloat16), rnd(B * 325, 768, dtype=torch.bfloat16, seed=1)
+    wa, wb = rnd(2304, 768, dtype=torch.bfloat16, scale=0.05, seed=2), rnd(2304, 768, dtype=torch.bfloat16, scale=0.05, seed=3)
+    oa = torch.empty(B * 32, 2304, dtype=torch.bfloat16, device=DEV)
+    ob = torch.empty(B * 325, 2304, dtype=torch.bfloat16, device=DEV)
+    ops.gemm_group([ops.GemmSpec(xa, wa, oa), ops.GemmSpec(xb, wb, ob)])
+    assert rel_err(oa, xa.float() @ wa.float().t()) < 4e-3
+    assert rel_err(ob, xb.float() @ wb.float().t()) < 4e-3
+
+
+@pytest.mark.parametrize("majors", [(0, 0), (0, 1), (1, 1)])
+def test_gemm_fp32_simt(majors):
+    M, N, K = 300, 498, 1536
+    am, bm = majors
+    a = rnd(M, K) if am == 0 else rnd(K, M)
+    b = rnd(N, K, seed=1) if bm == 0 else rnd(K, N, seed=1)
+    bias = rnd(N, seed=2)
+    out = torch.empty(M, N, device=DEV)
+    ops.gemm(a, b, out, a_major=am, b_major=bm, bias=bias)
+    ref = (_gemm_ref(a.double(), b.double(), am, bm) + bias.double()).float()
+    assert max_rel(out, ref) < 1e-5, f"fp32 SIMT GEMM: {max_rel(out, ref):.3e}"
+
+
+def test_gemm_dropout_epilogue_statistics():
+    M, N, K = 1024, 768, 64
+    a, w = rnd(M, K, dtype=torch.bfloat16), rnd(N, K, dtype=torch.bfloat16, seed=1)
+    full = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    drop = torch.empty_like(full)
+    ops.gemm(a, w, full, backend=ops.GEMM_SIMT)
+    ops.gemm(a, w, drop, backend=ops.GEMM_SIMT, drop_p=0.1, drop_seed=123, drop_stream=7)
+    kept = drop != 0
+    assert abs(kept.float().mean().item() - 0.9) < 5e-3
+    assert torch.allclose(drop[kept], full[kept] / 0.9, rtol=1e-5, atol=1e-6)
+    # the standalone dropout kernel regenerates the same mask (used by the backward pass)
+    again = torch.empty_like(full)
+    ops.dropout_apply(full, again, 0.1, 123, 7)
+    assert torch.equal(again != 0, kept)
+
+
+# ----------------------------------------------------------------------------- LayerNorm
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 8e-3)])
+@pytest.mark.parametrize("H", [768, 1536])
+def test_layernorm_fwd_bwd(dtype, tol, H):
+    M = 650 if H == 768 else 64
+    x = rnd(M, H, dtype=dtype, scale=2.0)
+    gamma, beta = rnd(H, seed=1) * 0.1 + 1.0, rnd(H, seed=2) * 0.1
+    dy = rnd(M, H, dtype=dtype, seed=3)
+    y, mean, rstd = ops.layernorm_fwd(x, gamma, beta, 1e-12)
+    xf = x.float().requires_grad_(True)
+    gf, bf = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    yr = torch.nn.functional.layer_norm(xf, (H,), gf, bf, 1e-12)
+    assert rel_err(y, yr) < tol
+    yr.backward(dy.float())
+    dgamma, dbeta, dcol = (torch.zeros(H, device=DEV) for _ in range(3))
+    dx = ops.layernorm_bwd(dy, x, mean, rstd, gamma, dgamma, dbeta, dcol)
+    assert rel_err(dx, xf.grad) < tol
+    assert rel_err(dgamma, gf.grad) < max(tol, 1e-4)
+    assert rel_err(dbeta, bf.grad) < max(tol, 1e-4)
+    assert rel_err(dcol, dx.float().sum(0)) < 1e-4
+
+
+def test_elementwise_helpers():
+    x = rnd(1000, 768)
+    xb = torch.empty_like(x, dtype=torch.bfloat16)
+    ops.cast(x, xb)
+    assert torch.equal(xb, x.to(torch.bfloat16))
+    xo = torch.empty(1003, dtype=torch.bfloat16, device=DEV)
+    ops.cast(rnd(1003), xo)  # odd length -> scalar path
+    assert torch.equal(xo, rnd(1003).to(torch.bfloat16))
+    v = rnd(768, seed=5)
+    o = torch.empty_like(xb)
+    ops.add_rowvec(x, v, o)
+    assert torch.equal(o, (x + v).to(torch.bfloat16))
+    cs = torch.zeros(768, device=DEV)
+    ops.colsum(xb, cs)
+    assert rel_err(cs, xb.float().sum(0)) < 1e-5
+    lg = rnd(128, 30522)
+    assert torch.equal(ops.argmax_rows(lg), lg.argmax(dim=1))
+
+
+# ----------------------------------------------------------------------------- attention
+def _attn_ref(q, k, v, mask, B, H, Lq, Lk, dh, causal):
+    qf = q.float().view(B, Lq, H, dh).transpose(1, 2)
+    kf = k.float().view(B, Lk, H, dh).transpose(1, 2)
+    vf = v.float().view(B, Lk, H, dh).transpose(1, 2)
+    s = qf @ kf.transpose(-1, -2) / math.sqrt(dh)
+    if mask is not None:
+        s = s + mask.view(B, 1, 1, Lk)
+    if causal:
+        s = s.masked_fill(torch.ones(Lq, Lk, dtype=torch.bool, device=q.device).triu(1), float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    o = (p @ vf).transpose(1, 2).reshape(B * Lq, H * dh)
+    return o, p
+
+
+ATT_CASES = [  # (B, H, Lq, Lk, dh, masked, causal)
+    (3, 12, 32, 32, 64, True, False),
+    (2, 12, 32, 325, 64, False, False),
+    (2, 12, 325, 325, 64, False, False),
+    (2, 12, 325, 32, 64, True, False),
+    (2, 12, 577, 577, 64, False, False),
+    (3, 8, 12, 12, 96, False, True),
+    (3, 8, 12, 359, 96, False, False),
+]
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("case", ATT_CASES)
+def test_attention_fwd_bwd(backend, dtype, tol, case):
+    B, H, Lq, Lk, dh, masked, causal = case
+    ops.set_attention_backend(backend)
+    try:
+        # q,k,v live inside one fused projection buffer (row stride 3*H*dh), as in the layer
+        qkv_q = rnd(B * Lq, 3 * H * dh, dtype=dtype)
+        qkv_k = rnd(B * Lk, 3 * H * dh, dtype=dtype, seed=1)
+        q, k, v = qkv_q[:, : H * dh], qkv_k[:, H * dh: 2 * H * dh], qkv_k[:, 2 * H * dh:]
+        mask = None
+        if masked:
+            lens = torch.randint(max(1, Lk // 4), Lk + 1, (B,), generator=torch.Generator().manual_seed(3))
+            mask = ((torch.arange(Lk)[None, :] >= lens[:, None]).float() * -10000.0).to(DEV).contiguous()
+        out = torch.empty(B * Lq, H * dh, dtype=dtype, device=DEV)
+        lse = torch.empty(B, H, Lq, device=DEV)
+        probs = torch.empty(B, H, Lq, Lk, device=DEV)
+        kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal)
+        ops.attn_fwd(q, k, v, out, lse, probs=probs, **kw)
+        qr, kr, vr = (t.float().detach().clone().requires_grad_(True) for t in (q, k, v))
+        oref, pref = _attn_ref(qr, kr, vr, mask, B, H, Lq, Lk, dh, causal)
+        assert rel_err(out, oref) < tol, f"attn fwd {case}: {rel_err(out, oref):.3e}"
+        assert rel_err(probs, pref) < tol
+        dout = rnd(B * Lq, H * dh, dtype=dtype, seed=9)
+        oref.backward(dout.float())
+        dqkv_q = torch.zeros_like(qkv_q)
+        dqkv_k = torch.zeros_like(qkv_k)
+        dq, dk, dv = dqkv_q[:, : H * dh], dqkv_k[:, H * dh: 2 * H * dh], dqkv_k[:, 2 * H * dh:]
+        delta = torch.empty(B, H, Lq, device=DEV)
+        ops.attn_bwd(q, k, v, out, lse, dout=dout, dq=dq, dk=dk, dv=dv, delta=delta, **kw)
+        for name, got, ref in (("dq", dq, qr.grad), ("dk", dk, kr.grad), ("dv", dv, vr.grad)):
+            assert rel_err(got, ref) < 2 * tol, f"attn bwd {name} {case}: {rel_err(got, ref):.3e}"
+    finally:
+        ops.set_attention_backend(ops.GEMM_AUTO)
+
+
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO])
+def test_attention_dropout_consistency(backend):
+    """Dropout cannot be bit-matched to PyTorch's Philox stream; check keep-rate, scaling and fwd/bwd mask agreement."""
+    B, H, Lq, Lk, dh, p = 2, 12, 64, 325, 64, 0.1
+    ops.set_attention_backend(backend)
+    try:
+        q, k, v = (rnd(B * L, H * dh, dtype=torch.bfloat16, seed=i) for i, L in ((0, Lq), (1, Lk), (2, Lk)))
+        out = torch.empty(B * Lq, H * dh, dtype=torch.bfloat16, device=DEV)
+        lse = torch.empty(B, H, Lq, device=DEV)
+        probs = torch.empty(B, H, Lq, Lk, device=DEV)
+        kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, drop_p=p, drop_seed=99, drop_stream=3)
+        ops.attn_fwd(q, k, v, out, lse, probs=probs, **kw)
+        _, pref = _attn_ref(q, k, v, None, B, H, Lq, Lk, dh, False)
+        keep = probs != 0
+        assert abs(keep.float().mean().item() - (1 - p)) < 5e-3
+        assert rel_err(probs[keep], pref[keep] / (1 - p)) < 1e-2
+        # forward output equals (dropped probs) @ V
+        vf = v.float().view(B, Lk, H, dh).transpose(1, 2)
+        oref = (probs @ vf).transpose(1, 2).reshape(B * Lq, H * dh)
+        assert rel_err(out, oref) < 1e-2
+        # backward with the same mask: compare with autograd through the fixed mask
+        qr, kr, vr = (t.float().detach().clone().requires_grad_(True) for t in (q, k, v))
+        _, p2 = _attn_ref(qr, kr, vr, None, B, H, Lq, Lk, dh, False)
+        o2 = ((p2 * keep / (1 - p)) @ vr.view(B, Lk, H, dh).transpose(1, 2)).transpose(1, 2).reshape(B * Lq, H * dh)
+        dout = rnd(B * Lq, H * dh, dtype=torch.bfloat16, seed=9)
+        o2.backward(dout.float())
+        dq, dk, dv = (torch.empty_like(t) for t in (q, k, v))
+        delta = torch.empty(B, H, Lq, device=DEV)
+        ops.attn_bwd(q, k, v, out, lse, dout=dout, dq=dq, dk=dk, dv=dv, delta=delta, **kw)
+        for name, got, ref in (("dq", dq, qr.grad), ("dk", dk, kr.grad), ("dv", dv, vr.grad)):
+            assert rel_err(got, ref) < 2e-2, f"dropout bwd {name}: {rel_err(got, ref):.3e}"
+    finally:
+        ops.set_attention_backend(ops.GEMM_AUTO)
+
+
+def test_decode_attention_step():
+    B, H, dh, Lmax, length = 5, 8, 96, 359, 359
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 1e-2)):
+        q = rnd(B, H * dh, dtype=dtype)
+        kc, vc = rnd(B, Lmax, H * dh, dtype=dtype, seed=1), rnd(B, Lmax, H * dh, dtype=dtype, seed=2)
+        out = torch.empty_like(q)
+        ops.decode_attn(q, kc, vc, out, H=H, length=length, dh=dh)
+        ref, _ = _attn_ref(q, kc[:, :length].reshape(B * length, H * dh), vc[:, :length].reshape(B * length, H * dh), None, B, H, 1, length, dh, False)
+        assert rel_err(out, ref) < tol
