@@ -1,0 +1,396 @@
+"""Forward/backward of BertCrossLayer (reference bert_model.py:445-503) as ONE autograd node per layer — or per
+text/image layer PAIR — built from the C-ABI kernels in `ops`.
+
+A "stream" is one BertCrossLayer application: hidden [B,Lq,768] attends to itself, then to `encoder` [B,Lk,768], then
+the FFN.  The text and image layers of one fusion index both read the pre-update x, y (m3ae_module.py:276-277), so
+they are independent: `cross_layers_apply` takes 1 or 2 streams and issues every GEMM stage as one grouped persistent
+launch covering both streams (the tiny text GEMMs, M = 32·B, ride in the tail wave of the image GEMMs, M = 325·B).
+
+Kernel schedule per stream (forward):            saved for backward
+  qkv  = x·Wqkv^T + b                  [M,2304]   qkv
+  ctx  = flash_attn(qkv, self mask)    [M,768]    ctx, lse1
+  h1   = drop(ctx·Wo^T + b) + x                   h1, mean1, rstd1
+  a1   = LN(h1)                                   a1
+  qc   = a1·Wq2^T + b ; kvc = y·Wkv2^T + b        qc, kvc
+  ctx2 = flash_attn(qc, kvc, cross mask)          ctx2, lse2
+  h2   = drop(ctx2·Wo2^T + b) + a1 ; a2 = LN(h2)  h2, mean2, rstd2, a2
+  u    = a2·W1^T + b ; g = gelu(u)     [M,3072]   u, g   (one GEMM, two outputs)
+  h3   = drop(g·W2^T + b) + a2 ; out = LN(h3)     h3, mean3, rstd3
+Backward runs the mirror image: LN-bwd (+bias-grad column sums) -> dgrad GEMMs (B operand MN-major, residual and
+GELU' fused in the epilogue) and wgrad GEMMs (both operands MN-major, split-K atomics into fp32) grouped per stage.
+"""
+import itertools
+
+import torch
+
+from . import ops
+
+_seed_counter = itertools.count(1)
+
+PARAM_NAMES = [
+    "attention.self.query.weight", "attention.self.query.bias",
+    "attention.self.key.weight", "attention.self.key.bias",
+    "attention.self.value.weight", "attention.self.value.bias",
+    "attention.output.dense.weight", "attention.output.dense.bias",
+    "attention.output.LayerNorm.weight", "attention.output.LayerNorm.bias",
+    "crossattention.self.query.weight", "crossattention.self.query.bias",
+    "crossattention.self.key.weight", "crossattention.self.key.bias",
+    "crossattention.self.value.weight", "crossattention.self.value.bias",
+    "crossattention.output.dense.weight", "crossattention.output.dense.bias",
+    "crossattention.output.LayerNorm.weight", "crossattention.output.LayerNorm.bias",
+    "intermediate.dense.weight", "intermediate.dense.bias",
+    "output.dense.weight", "output.dense.bias",
+    "output.LayerNorm.weight", "output.LayerNorm.bias",
+]
+NP = len(PARAM_NAMES)  # 26
+(WQ, BQ, WK, BK, WV, BV, WO, BO, G1, B1, WQ2, BQ2, WK2, BK2, WV2, BV2, WO2, BO2, G2, B2, W1, BI, W2, BO3, G3, B3) = range(NP)
+
+
+class LayerOperands:
+    """Compute-dtype operand cache of one layer's fp32 master parameters: fused [Wq;Wk;Wv] and [Wk2;Wv2] weights
+    (one N=2304 / N=1536 GEMM instead of three / two) cast to bf16 (product path) or copied as fp32 (parity path).
+    Refreshed whenever a parameter's version counter moves (i.e. after every optimizer step)."""
+
+    def __init__(self):
+        self.key = None
+
+    def get(self, params, dtype):
+        key = (dtype,) + tuple((p.data_ptr(), p._version) for p in params)
+        if key == self.key:
+            return self
+        dev = params[0].device
+        H = params[WQ].shape[1]
+        FF = params[W1].shape[0]
+
+        def buf(rows, cols):
+            return torch.empty(rows, cols, dtype=dtype, device=dev)
+
+        with torch.no_grad():
+            self.wqkv = buf(3 * H, H)
+            for i, idx in enumerate((WQ, WK, WV)):
+                ops.cast(params[idx].detach(), self.wqkv[i * H:(i + 1) * H])
+            self.bqkv = torch.empty(3 * H, dtype=torch.float32, device=dev)
+            for i, idx in enumerate((BQ, BK, BV)):
+                ops.cast(params[idx].detach(), self.bqkv[i * H:(i + 1) * H])
+            self.wkv2 = buf(2 * H, H)
+            for i, idx in enumerate((WK2, WV2)):
+                ops.cast(params[idx].detach(), self.wkv2[i * H:(i + 1) * H])
+            self.bkv2 = torch.empty(2 * H, dtype=torch.float32, device=dev)
+            for i, idx in enumerate((BK2, BV2)):
+                ops.cast(params[idx].detach(), self.bkv2[i * H:(i + 1) * H])
+            self.wo = ops.cast(params[WO].detach(), buf(H, H))
+            self.wq2 = ops.cast(params[WQ2].detach(), buf(H, H))
+            self.wo2 = ops.cast(params[WO2].detach(), buf(H, H))
+            self.w1 = ops.cast(params[W1].detach(), buf(FF, H))
+            self.w2 = ops.cast(params[W2].detach(), buf(H, FF))
+        self.key = key
+        return self
+
+
+class LayerConfig:
+    def __init__(self, num_heads=12, eps=1e-12, hidden_dropout=0.0, attn_dropout=0.0, compute_dtype=torch.bfloat16,
+                 gemm_backend=ops.GEMM_AUTO):
+        self.num_heads = num_heads
+        self.eps = eps
+        self.hidden_dropout = hidden_dropout
+        self.attn_dropout = attn_dropout
+        self.compute_dtype = compute_dtype
+        self.gemm_backend = gemm_backend
+
+
+def _wgrad_split(tokens, n_out, n_in):
+    """split-K factor for dW[n_out,n_in] += dY^T X over `tokens`: aim at ~1 wave of 148 CTAs of 128x256 tiles."""
+    tiles = ((n_out + 127) // 128) * ((n_in + 255) // 256)
+    kblocks = (tokens + 63) // 64
+    return max(1, min(kblocks, 148 // tiles if tiles <= 148 else 1))
+
+
+def _as2d(t):
+    return t.reshape(-1, t.shape[-1])
+
+
+def _mask2d(mask, B, L):
+    if mask is None:
+        return None
+    if mask.numel() != B * L:
+        raise ValueError(f"attention mask must broadcast as [B,1,1,L]=[{B},1,1,{L}], got {tuple(mask.shape)}")
+    m = mask.reshape(B, L)
+    if m.dtype != torch.float32:
+        m = m.float()
+    return m.contiguous()
+
+
+class _Stream:
+    """Per-stream forward state (activations kept for backward)."""
+    pass
+
+
+def _forward_streams(cfg, training, streams, want_probs):
+    """streams: list of dicts(hidden, encoder, mask, enc_mask, params(list of 26), operands(LayerOperands))."""
+    dt = cfg.compute_dtype
+    be = cfg.gemm_backend
+    nh = cfg.num_heads
+    pa = cfg.attn_dropout if training else 0.0
+    ph = cfg.hidden_dropout if training else 0.0
+    S = []
+    for s in streams:
+        st = _Stream()
+        h, e = s["hidden"], s["encoder"]
+        st.B, st.Lq, st.H = h.shape
+        st.Lk = e.shape[1]
+        st.dh = st.H // nh
+        st.M, st.Mk = st.B * st.Lq, st.B * st.Lk
+        dev = h.device
+        st.x = _as2d(h) if h.dtype == dt and h.is_contiguous() else ops.cast(h.contiguous(), torch.empty(st.M, st.H, dtype=dt, device=dev))
+        st.y = _as2d(e) if e.dtype == dt and e.is_contiguous() else ops.cast(e.contiguous(), torch.empty(st.Mk, st.H, dtype=dt, device=dev))
+        st.mask = _mask2d(s["mask"], st.B, st.Lq)
+        st.enc_mask = _mask2d(s["enc_mask"], st.B, st.Lk)
+        st.p = s["params"]
+        st.w = s["operands"].get(st.p, dt)
+        st.seed = (torch.initial_seed() + 0x9E3779B97F4A7C15 * next(_seed_counter)) & 0xFFFFFFFFFFFFFFFF if training else 0
+        st.FF = st.p[W1].shape[0]
+        S.append(st)
+
+    def new(st, rows, cols, dtype=None):
+        return torch.empty(rows, cols, dtype=dtype or dt, device=st.x.device)
+
+    def f32(st, *shape):
+        return torch.empty(*shape, dtype=torch.float32, device=st.x.device)
+
+    # 1. fused QKV projection
+    for st in S:
+        st.qkv = new(st, st.M, 3 * st.H)
+    ops.gemm_group([ops.GemmSpec(st.x, st.w.wqkv, st.qkv, bias=st.w.bqkv) for st in S], be)
+    # 2. self attention
+    for st in S:
+        H = st.H
+        st.ctx = new(st, st.M, H)
+        st.lse1 = f32(st, st.B, nh, st.Lq)
+        st.probs1 = f32(st, st.B, nh, st.Lq, st.Lq) if want_probs else None
+        ops.attn_fwd(st.qkv[:, :H], st.qkv[:, H:2 * H], st.qkv[:, 2 * H:], st.ctx, st.lse1, B=st.B, H=nh, Lq=st.Lq,
+                     Lk=st.Lq, dh=st.dh, mask=st.mask, probs=st.probs1, drop_p=pa, drop_seed=st.seed, drop_stream=0)
+    # 3. out-proj + dropout + residual, 4. LayerNorm
+    for st in S:
+        st.h1 = new(st, st.M, st.H)
+    ops.gemm_group([ops.GemmSpec(st.ctx, st.w.wo, st.h1, bias=st.p[BO], residual=st.x, drop_p=ph, drop_seed=st.seed,
+                                 drop_stream=1) for st in S], be)
+    for st in S:
+        st.a1, st.mean1, st.rstd1 = ops.layernorm_fwd(st.h1, st.p[G1], st.p[B1], cfg.eps)
+    # 5. cross-attention projections: Q from own stream, fused K|V from the other stream
+    specs = []
+    for st in S:
+        st.qc = new(st, st.M, st.H)
+        st.kvc = new(st, st.Mk, 2 * st.H)
+        specs.append(ops.GemmSpec(st.a1, st.w.wq2, st.qc, bias=st.p[BQ2]))
+        specs.append(ops.GemmSpec(st.y, st.w.wkv2, st.kvc, bias=st.w.bkv2))
+    ops.gemm_group(specs, be)
+    # 6. cross attention
+    for st in S:
+        H = st.H
+        st.ctx2 = new(st, st.M, H)
+        st.lse2 = f32(st, st.B, nh, st.Lq)
+        st.probs2 = f32(st, st.B, nh, st.Lq, st.Lk) if want_probs else None
+        ops.attn_fwd(st.qc, st.kvc[:, :H], st.kvc[:, H:], st.ctx2, st.lse2, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lk, dh=st.dh,
+                     mask=st.enc_mask, probs=st.probs2, drop_p=pa, drop_seed=st.seed, drop_stream=2)
+    # 7/8. cross out-proj + residual, LayerNorm
+    for st in S:
+        st.h2 = new(st, st.M, st.H)
+    ops.gemm_group([ops.GemmSpec(st.ctx2, st.w.wo2, st.h2, bias=st.p[BO2], residual=st.a1, drop_p=ph, drop_seed=st.seed,
+                                 drop_stream=3) for st in S], be)
+    for st in S:
+        st.a2, st.mean2, st.rstd2 = ops.layernorm_fwd(st.h2, st.p[G2], st.p[B2], cfg.eps)
+    # 9. FFN up + GELU (pre-activation kept for backward)
+    for st in S:
+        st.u = new(st, st.M, st.FF)
+        st.g = new(st, st.M, st.FF)
+    ops.gemm_group([ops.GemmSpec(st.a2, st.w.w1, st.g, bias=st.p[BI], act=ops.ACT_GELU, aux_out=st.u) for st in S], be)
+    # 10/11. FFN down + residual, LayerNorm
+    for st in S:
+        st.h3 = new(st, st.M, st.H)
+    ops.gemm_group([ops.GemmSpec(st.g, st.w.w2, st.h3, bias=st.p[BO3], residual=st.a2, drop_p=ph, drop_seed=st.seed,
+                                 drop_stream=4) for st in S], be)
+    for st in S:
+        st.out, st.mean3, st.rstd3 = ops.layernorm_fwd(st.h3, st.p[G3], st.p[B3], cfg.eps)
+        st.pa, st.ph = pa, ph
+    return S
+
+
+def _backward_streams(cfg, S, douts):
+    """S: forward states; douts: list of [M,H] compute-dtype grads. Returns per stream (dx, dy, [26 param grads])."""
+    dt = cfg.compute_dtype
+    be = cfg.gemm_backend
+    nh = cfg.num_heads
+    MN, K = ops.MAJOR_MN, ops.MAJOR_K
+    dev = S[0].x.device
+
+    def zeros(*shape):
+        return torch.zeros(*shape, dtype=torch.float32, device=dev)
+
+    def new(rows, cols):
+        return torch.empty(rows, cols, dtype=dt, device=dev)
+
+    def dropped(st, d, site):
+        # gradient through hidden dropout: same Philox stream as the forward epilogue
+        if st.ph <= 0.0:
+            return d
+        return ops.dropout_apply(d, torch.empty_like(d), st.ph, st.seed, site)
+
+    def wgrad(dy, x, dw):
+        return ops.GemmSpec(dy, x, dw, a_major=MN, b_major=MN, accumulate=True,
+                            split_k=_wgrad_split(dy.shape[0], dw.shape[0], dw.shape[1]))
+
+    for st, d in zip(S, douts):
+        st.g_ = [None] * NP
+        H, FF = st.H, st.FF
+        # ---- output LayerNorm + FFN
+        st.g_[G3], st.g_[B3], st.g_[BO3] = zeros(H), zeros(H), zeros(H)
+        st.dh3 = ops.layernorm_bwd(d, st.h3, st.mean3, st.rstd3, st.p[G3], st.g_[G3], st.g_[B3], None if st.ph > 0 else st.g_[BO3])
+        st.dh3d = dropped(st, st.dh3, 4)
+        if st.ph > 0:
+            ops.colsum(st.dh3d, st.g_[BO3])
+        st.du = new(st.M, FF)
+        st.g_[W2] = zeros(H, FF)
+    ops.gemm_group([ops.GemmSpec(st.dh3d, st.w.w2, st.du, b_major=MN, aux_in=st.u, dact=ops.ACT_GELU) for st in S] +
+                   [wgrad(st.dh3d, st.g, st.g_[W2]) for st in S], be)
+    for st in S:
+        st.g_[BI] = ops.colsum(st.du, zeros(st.FF))
+        st.da2 = new(st.M, st.H)
+        st.g_[W1] = zeros(st.FF, st.H)
+    ops.gemm_group([ops.GemmSpec(st.du, st.w.w1, st.da2, b_major=MN, residual=st.dh3) for st in S] +
+                   [wgrad(st.du, st.a2, st.g_[W1]) for st in S], be)
+    # ---- cross-attention block
+    for st in S:
+        H = st.H
+        st.g_[G2], st.g_[B2], st.g_[BO2] = zeros(H), zeros(H), zeros(H)
+        st.dh2 = ops.layernorm_bwd(st.da2, st.h2, st.mean2, st.rstd2, st.p[G2], st.g_[G2], st.g_[B2], None if st.ph > 0 else st.g_[BO2])
+        st.dh2d = dropped(st, st.dh2, 3)
+        if st.ph > 0:
+            ops.colsum(st.dh2d, st.g_[BO2])
+        st.dctx2 = new(st.M, H)
+        st.g_[WO2] = zeros(H, H)
+    ops.gemm_group([ops.GemmSpec(st.dh2d, st.w.wo2, st.dctx2, b_major=MN) for st in S] +
+                   [wgrad(st.dh2d, st.ctx2, st.g_[WO2]) for st in S], be)
+    for st in S:
+        H = st.H
+        st.dqc = new(st.M, H)
+        st.dkvc = new(st.Mk, 2 * H)
+        delta = torch.empty(st.B, nh, st.Lq, dtype=torch.float32, device=dev)
+        ops.attn_bwd(st.qc, st.kvc[:, :H], st.kvc[:, H:], st.ctx2, st.lse2, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lk, dh=st.dh,
+                     mask=st.enc_mask, drop_p=st.pa, drop_seed=st.seed, drop_stream=2, dout=st.dctx2, dq=st.dqc,
+                     dk=st.dkvc[:, :H], dv=st.dkvc[:, H:], delta=delta)
+        st.g_[BQ2] = ops.colsum(st.dqc, zeros(H))
+        bkv = ops.colsum(st.dkvc, zeros(2 * H))
+        st.g_[BK2], st.g_[BV2] = bkv[:H], bkv[H:]
+        st.da1 = new(st.M, H)
+        st.dy = new(st.Mk, H)
+        st.g_wq2 = zeros(H, H)
+        st.g_wkv2 = zeros(2 * H, H)
+    ops.gemm_group([ops.GemmSpec(st.dqc, st.w.wq2, st.da1, b_major=MN, residual=st.dh2) for st in S] +
+                   [ops.GemmSpec(st.dkvc, st.w.wkv2, st.dy, b_major=MN) for st in S], be)
+    ops.gemm_group([wgrad(st.dqc, st.a1, st.g_wq2) for st in S] + [wgrad(st.dkvc, st.y, st.g_wkv2) for st in S], be)
+    # ---- self-attention block
+    for st in S:
+        H = st.H
+        st.g_[WQ2] = st.g_wq2
+        st.g_[WK2], st.g_[WV2] = st.g_wkv2[:H], st.g_wkv2[H:]
+        st.g_[G1], st.g_[B1], st.g_[BO] = zeros(H), zeros(H), zeros(H)
+        st.dh1 = ops.layernorm_bwd(st.da1, st.h1, st.mean1, st.rstd1, st.p[G1], st.g_[G1], st.g_[B1], None if st.ph > 0 else st.g_[BO])
+        st.dh1d = dropped(st, st.dh1, 1)
+        if st.ph > 0:
+            ops.colsum(st.dh1d, st.g_[BO])
+        st.dctx = new(st.M, H)
+        st.g_[WO] = zeros(H, H)
+    ops.gemm_group([ops.GemmSpec(st.dh1d, st.w.wo, st.dctx, b_major=MN) for st in S] +
+                   [wgrad(st.dh1d, st.ctx, st.g_[WO]) for st in S], be)
+    for st in S:
+        H = st.H
+        st.dqkv = new(st.M, 3 * H)
+        delta = torch.empty(st.B, nh, st.Lq, dtype=torch.float32, device=dev)
+        ops.attn_bwd(st.qkv[:, :H], st.qkv[:, H:2 * H], st.qkv[:, 2 * H:], st.ctx, st.lse1, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lq,
+                     dh=st.dh, mask=st.mask, drop_p=st.pa, drop_seed=st.seed, drop_stream=0, dout=st.dctx,
+                     dq=st.dqkv[:, :H], dk=st.dqkv[:, H:2 * H], dv=st.dqkv[:, 2 * H:], delta=delta)
+        bq = ops.colsum(st.dqkv, zeros(3 * H))
+        st.g_[BQ], st.g_[BK], st.g_[BV] = bq[:H], bq[H:2 * H], bq[2 * H:]
+        st.dx = new(st.M, H)
+        st.g_wqkv = zeros(3 * H, H)
+    ops.gemm_group([ops.GemmSpec(st.dqkv, st.w.wqkv, st.dx, b_major=MN, residual=st.dh1) for st in S] +
+                   [wgrad(st.dqkv, st.x, st.g_wqkv) for st in S], be)
+    res = []
+    for st in S:
+        H = st.H
+        st.g_[WQ], st.g_[WK], st.g_[WV] = st.g_wqkv[:H], st.g_wqkv[H:2 * H], st.g_wqkv[2 * H:]
+        res.append((st.dx, st.dy, st.g_))
+    return res
+
+
+class _CrossLayersFn(torch.autograd.Function):
+    """inputs: cfg, training, want_probs, operands(list), n_streams, then per stream: hidden, encoder, mask, enc_mask,
+    26 params.  outputs: per stream out [B,Lq,H] (+ self_probs, cross_probs when want_probs)."""
+
+    @staticmethod
+    def forward(ctx, cfg, training, want_probs, operands, n_streams, *flat):
+        per = 4 + NP
+        streams = []
+        for i in range(n_streams):
+            c = flat[i * per:(i + 1) * per]
+            streams.append(dict(hidden=c[0], encoder=c[1], mask=c[2], enc_mask=c[3], params=list(c[4:]), operands=operands[i]))
+        S = _forward_streams(cfg, training, streams, want_probs)
+        ctx.cfg = cfg
+        ctx.S = S
+        ctx.in_dtypes = [(s["hidden"].dtype, s["encoder"].dtype) for s in streams]
+        outs = []
+        nondiff = []
+        for st, s in zip(S, streams):
+            o = st.out.view(st.B, st.Lq, st.H)
+            if o.dtype != s["hidden"].dtype:
+                o = ops.cast(st.out, torch.empty(st.B, st.Lq, st.H, dtype=s["hidden"].dtype, device=o.device))
+            outs.append(o)
+            if want_probs:
+                outs += [st.probs1, st.probs2]
+                nondiff += [st.probs1, st.probs2]
+        if nondiff:
+            ctx.mark_non_differentiable(*nondiff)
+        ctx.want_probs = want_probs
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        cfg, S = ctx.cfg, ctx.S
+        dt = cfg.compute_dtype
+        step = 3 if ctx.want_probs else 1
+        douts = []
+        for i, st in enumerate(S):
+            g = grads[i * step]
+            if g is None:
+                g = torch.zeros(st.M, st.H, dtype=dt, device=st.x.device)
+            g = g.reshape(st.M, st.H)
+            if g.dtype != dt or not g.is_contiguous():
+                g = ops.cast(g.contiguous(), torch.empty(st.M, st.H, dtype=dt, device=g.device))
+            douts.append(g)
+        res = _backward_streams(cfg, S, douts)
+        flat = [None, None, None, None, None]
+        for (dx, dy, pg), st, (hd, ed) in zip(res, S, ctx.in_dtypes):
+            dx = dx.view(st.B, st.Lq, st.H)
+            dy = dy.view(st.B, st.Lk, st.H)
+            if dx.dtype != hd:
+                dx = ops.cast(dx, torch.empty_like(dx, dtype=hd))
+            if dy.dtype != ed:
+                dy = ops.cast(dy, torch.empty_like(dy, dtype=ed))
+            flat += [dx, dy, None, None] + pg
+        ctx.S = None
+        return tuple(flat)
+
+
+def cross_layers_apply(cfg, training, streams, want_probs=False):
+    """streams: list (1 or 2) of dicts(hidden, encoder, mask, enc_mask, params, operands).
+    Returns per stream a tuple (out,) or (out, self_probs, cross_probs)."""
+    if not 1 <= len(streams) <= 2:
+        raise ValueError("cross_layers_apply takes one layer or one text/image layer pair")
+    flat = []
+    for s in streams:
+        if not s["hidden"].is_cuda:
+            raise RuntimeError("BertCrossLayer (B200) needs CUDA tensors: the fusion path has no CPU fallback")
+        flat += [s["hidden"], s["encoder"], s["mask"], s["enc_mask"]] + list(s["params"])
+    outs = _CrossLayersFn.apply(cfg, training, want_probs, [s["operands"] for s in streams], len(streams), *flat)
+    step = 3 if want_probs else 1
+    return [tuple(outs[i * step:(i + 1) * step]) for i in range(len(streams))]

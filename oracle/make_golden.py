@@ -1,0 +1,148 @@
+"""ORACLE — test infrastructure only.  Generates tests/golden/*.pt by running the UNMODIFIED reference modules
+(imported from /root/reference through oracle/ref_shim.py) on seeded weights and inputs.
+
+Run in the build container:  python oracle/make_golden.py
+The fixtures hold only outputs (inputs/weights are regenerated from seeds by oracle/m3ae_oracle.py helpers), so they
+stay small.  tests/test_oracle_golden.py pins oracle/m3ae_oracle.py against them; the GPU parity tests compare the
+CUDA path with both.
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import m3ae_oracle as O  # noqa: E402
+from oracle import ref_shim  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def probe(shape, seed):
+    """Fixed random projection used as the scalar 'loss' for gradient fixtures (a loss that reads only
+    post-LayerNorm token-0 energy is degenerate)."""
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed))
+
+
+def cross_layer_cases():
+    # (name, seed, B, Lq, Lk, ragged mask on queries?, ragged mask on keys?)
+    return [("text_like", 11, 2, 32, 325, True, False), ("image_like", 12, 1, 325, 32, False, True)]
+
+
+def cross_layer_inputs(seed, B, Lq, Lk, q_masked, k_masked):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, Lq, 768, generator=g)
+    y = torch.randn(B, Lk, 768, generator=g)
+
+    def mk(L, ragged):
+        lens = torch.randint(max(1, L // 4), L + 1, (B,), generator=g) if ragged else torch.full((B,), L)
+        return (torch.arange(L)[None, :] < lens[:, None]).long()
+
+    return x, y, mk(Lq, q_masked), mk(Lk, k_masked)
+
+
+def gen_cross_layer(ref):
+    out = {}
+    for name, seed, B, Lq, Lk, qm, km in cross_layer_cases():
+        sd = O.make_cross_layer_state(seed)
+        layer = ref.BertCrossLayer(ref_shim.fusion_config()).eval()
+        layer.load_state_dict(sd, strict=True)
+        x, y, mq, mk = cross_layer_inputs(seed, B, Lq, Lk, qm, km)
+        x.requires_grad_(True)
+        y.requires_grad_(True)
+        r = layer(x, y, O.extended_attention_mask(mq), O.extended_attention_mask(mk), output_attentions=True)
+        loss = (r[0] * probe(r[0].shape, seed + 100)).sum()
+        loss.backward()
+        out[name] = {
+            "tok_stride": 1 if Lq <= 32 else 5,  # image-like case keeps every 5th token to stay small
+            "layer_out": r[0].detach()[:, :: (1 if Lq <= 32 else 5)].clone(),
+            "self_probs_rowsum": r[1].detach().sum(-1), "self_probs_00": r[1].detach()[:, :, 0].clone(),
+            "cross_probs_00": r[2].detach()[:, :, 0].clone(),
+            "loss": loss.detach().clone(), "dx": x.grad[:, :: (1 if Lq <= 32 else 5)].clone(), "dy_norm": y.grad.norm(),
+            "dy_row0": y.grad[:, 0].clone(),
+            "param_grad_norms": {k: p.grad.norm() for k, p in layer.named_parameters()},
+            "param_grad_samples": {k: p.grad.flatten()[:: max(1, p.numel() // 64)][:64].clone() for k, p in layer.named_parameters()},
+        }
+    torch.save(out, os.path.join(OUT, "cross_layer.pt"))
+    print("cross_layer.pt", {k: float(v["loss"]) for k, v in out.items()})
+
+
+def gen_fusion():
+    mm3, Cls = ref_shim.load_m3ae_module()
+    torch.manual_seed(0)
+    model = Cls(ref_shim.m3ae_config()).eval()
+    sd = O.make_fusion_state(21)
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all(k.startswith(("vision_encoder", "language_encoder")) for k in missing), missing
+    inp = O.make_fusion_inputs(22, B=2)
+    # plug the seeded uni-modal features in; everything from m3ae_module.py:235 on runs as written
+    class Const(torch.nn.Module):
+        def __init__(self, value):
+            super().__init__()
+            self.value = value
+
+        def forward(self, *a, **k):
+            return self.value
+
+    model.language_encoder.embeddings = Const(inp["text_feats"])
+    model.vision_encoder = Const(inp["image_feats"])
+    batch = {"image": [torch.zeros(2, 3, 288, 288)], "text_ids": torch.zeros(2, 32, dtype=torch.long),
+             "text_labels": torch.full((2, 32), -100), "text_masks": inp["text_masks"]}
+    with torch.no_grad():
+        ret = model.infer(batch)
+        logits = model.vqa_head(ret["multi_modal_cls_feats"])
+        loss = torch.nn.functional.binary_cross_entropy_with_logits(logits, inp["targets"]) * inp["targets"].shape[1]
+    out = {"multi_modal_cls_feats": ret["multi_modal_cls_feats"], "multi_modal_text_feats": ret["multi_modal_text_feats"],
+           "multi_modal_image_feats_tok0": ret["multi_modal_image_feats"][:, 0].clone(),
+           "extended_text_masks": ret["extended_text_masks"], "vqa_logits": logits, "vqa_loss": loss,
+           "keys": sorted(ret.keys())}
+    torch.save(out, os.path.join(OUT, "fusion.pt"))
+    print("fusion.pt loss", float(loss), "argmax", logits.argmax(1).tolist())
+
+
+class Tok:
+    cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
+
+
+def decoder_inputs(seed, B, T, Lm=359):
+    g = torch.Generator().manual_seed(seed)
+    mem = torch.randn(B, Lm, 768, generator=g)
+    ids = torch.randint(1000, 30000, (B, T), generator=g)
+    ids[:, 0] = 101
+    lens = torch.randint(2, T + 1, (B,), generator=g)
+    pm = torch.arange(T)[None, :] < lens[:, None]
+    ids = torch.where(pm, ids, torch.zeros_like(ids))
+    return mem, ids, pm
+
+
+def gen_decoder(ref):
+    sd = O.make_decoder_state(31)
+    dec = ref.Decoder(6, 768, 8, 3072, 0.1, 16, 30522).eval()
+    dec.load_state_dict(sd, strict=True)
+    mem, ids, pm = decoder_inputs(32, B=4, T=9)
+    with torch.no_grad():
+        logits, att = dec(ids, pm, mem)
+        greedy = dec.search_path(mem, Tok)
+    # greedy with an early [SEP]: bias the vocab projection towards 102 for a second fixture
+    sd2 = dict(sd)
+    sd2["final_linear.bias"] = sd["final_linear.bias"].clone()
+    sd2["final_linear.bias"][102] += 4.0
+    dec.load_state_dict(sd2, strict=True)
+    with torch.no_grad():
+        greedy_sep = dec.search_path(mem, Tok)
+    out = {"logits_sub": logits[:, :, ::16].clone(), "argmax": logits.argmax(-1), "greedy": greedy, "greedy_sep": greedy_sep,
+           "self_att_l6": att["layer6_dec_self"].clone(), "cross_att_l6_sum": att["layer6_dec_cross"].sum(-1)}
+    torch.save(out, os.path.join(OUT, "decoder.pt"))
+    print("decoder.pt greedy[0]", greedy[0].tolist(), "greedy_sep[0]", greedy_sep[0].tolist())
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    ref = ref_shim.load()
+    gen_cross_layer(ref)
+    gen_decoder(ref)
+    gen_fusion()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")

@@ -115,3 +115,67 @@ def fusion_config(drop_rate=0.0):
     return RobertaConfig(vocab_size=50265, hidden_size=768, num_hidden_layers=6, num_attention_heads=12,
                          intermediate_size=768 * 4, max_position_embeddings=32, hidden_dropout_prob=drop_rate,
                          attention_probs_dropout_prob=drop_rate)
+
+
+def load_m3ae_module():
+    """Imports the reference's m3ae/modules/m3ae_module.py unmodified and returns (module, M3AETransformerSS).
+    The uni-modal encoders need downloaded checkpoints (clip_model.build_model, RobertaModel.from_pretrained) that do
+    not exist offline, so both constructors are replaced by tiny stand-ins; callers then plug seeded uni-modal
+    features in (see oracle/make_golden.py) so that the fusion section of infer() (m3ae_module.py:235,252-297) runs
+    exactly as written."""
+    ns = load()
+    import torch
+    import torch.nn as nn
+    mods = sys.modules["m3ae.modules"]
+    base = os.path.join(REF_ROOT, "m3ae", "modules")
+    # stubs for pieces that need absent third-party packages (torchmetrics, timm)
+    if "m3ae.gadgets" not in sys.modules:
+        _pkg("m3ae.gadgets", os.path.join(REF_ROOT, "m3ae", "gadgets"))
+        mm = types.ModuleType("m3ae.gadgets.my_metrics")
+        for n in ("Accuracy", "Scalar", "VQAScore", "VQARADScore", "VQAExactMatch", "ROUGE1Score", "ROUGE2Score",
+                  "BLEUScore", "ROCScore", "F1Score"):
+            setattr(mm, n, type(n, (nn.Module,), {"forward": lambda self, *a, **k: torch.zeros(())}))
+        sys.modules["m3ae.gadgets.my_metrics"] = mm
+    _pkg("m3ae.modules.vision_encoders", os.path.join(base, "vision_encoders"))
+    for sub in ("swin_transformer", "swin_helpers"):
+        stub = types.ModuleType(f"m3ae.modules.vision_encoders.{sub}")
+        stub.swin_adapt_position_encoding = lambda *a, **k: None
+        sys.modules[f"m3ae.modules.vision_encoders.{sub}"] = stub
+        setattr(sys.modules["m3ae.modules.vision_encoders"], sub, stub)
+    # real objectives / utils / heads (drop the placeholders load() registered for the decoder import)
+    for sub in ("objectives", "m3ae_t5_utils"):
+        sys.modules.pop(f"m3ae.modules.{sub}", None)
+    for sub in ("m3ae_utils", "objectives", "prediction_heads"):
+        m = importlib.import_module(f"m3ae.modules.{sub}")
+        setattr(mods, sub, m)
+    mm3 = importlib.import_module("m3ae.modules.m3ae_module")
+
+    class _TinyVision(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.dummy = nn.Parameter(torch.zeros(1))
+
+    class _TinyText(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embeddings = nn.Identity()
+            self.encoder = nn.Module()
+            self.encoder.layer = nn.ModuleList()
+
+        def get_extended_attention_mask(self, mask, shape, device):  # HF 4.6.0 semantics (pinned version)
+            return (1.0 - mask[:, None, None, :].to(torch.float32)) * -10000.0
+
+    mm3.build_model = lambda *a, **k: _TinyVision()
+    mm3.RobertaModel = types.SimpleNamespace(from_pretrained=lambda *a, **k: _TinyText())
+    return mm3, mm3.M3AETransformerSS
+
+
+def m3ae_config(drop_rate=0.0, image_size=288):
+    """config.py defaults (:19-119) + task_finetune_vqa_vqa_rad (:176-198) + clip16 (:245-251) + text_roberta (:256-259)."""
+    return {
+        "vit": "ViT-B/16", "tokenizer": "roberta-base", "vocab_size": 50265, "hidden_size": 768, "num_layers": 6,
+        "num_heads": 12, "mlp_ratio": 4, "max_text_len": 32, "drop_rate": drop_rate, "image_size": image_size,
+        "patch_size": 16, "input_text_embed_size": 768, "input_image_embed_size": 768, "num_top_layer": 6,
+        "loss_names": {"mlm": 0, "mim": 0, "itm": 0, "vqa": 1, "cls": 0, "irtr": 0}, "load_path": "", "test_only": False,
+        "vqa_label_size": 498, "mim_prob": 0.75, "mim_layer": 3,
+    }
