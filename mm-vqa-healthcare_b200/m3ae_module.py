@@ -1,0 +1,405 @@
+"""Host-side mirror of the reference's `M3AETransformerSS` (m3ae/modules/m3ae_module.py) with the multimodal fusion
+path running on the sm_100a kernels.
+
+`M3AEFusion`       everything on the hot path: modality projections (+type embeddings), 6+6 co-attention layers
+                   (text/image layer pairs co-scheduled), poolers, `vqa_head`, VQA loss.  Parameter names are the
+                   reference's (`multi_modal_language_proj.*`, `multi_modal_vision_layers.{i}.*`, `vqa_head.*`, ...)
+                   so reference checkpoints load and the optimizer's name-based parameter groups
+                   (m3ae_utils.py:121-200: `multi_modal` substring -> lr x5, `vqa_head` -> lr x100) still apply.
+`M3AETransformerSS` adds the uni-modal encoders (CLIP ViT-B/16 visual tower and RoBERTa-base — plain PyTorch for now:
+                   they are SURVEY §8(f) "next" rows, not part of the hot path) and the reference's public surface:
+                   `infer(batch, ...) -> dict`, `forward(batch, test)`, the pytorch_lightning step hooks and
+                   `configure_optimizers`.
+`patch_m3ae(model)` swaps the 12 BertCrossLayer instances of an EXISTING reference model for the B200 ones, re-using
+                   its Parameter objects.
+"""
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import functional as Fn
+from . import ops
+from .bert_cross_layer import BertCrossLayer, fused_layer_pair
+
+try:  # pytorch_lightning is not installed in this image; the hooks below follow PL 1.3.2's calling convention
+    import pytorch_lightning as pl
+    _Base = pl.LightningModule
+except Exception:  # pragma: no cover
+    class _Base(nn.Module):
+        """Minimal stand-in for pl.LightningModule: hparams capture, log(), device."""
+
+        def save_hyperparameters(self, config):
+            self.hparams = type("HParams", (), {})()
+            self.hparams.config = config
+
+        def log(self, name, value, **kw):
+            self.logged = getattr(self, "logged", {})
+            self.logged[name] = float(value) if torch.is_tensor(value) and value.numel() == 1 else value
+
+        @property
+        def device(self):
+            return next(self.parameters()).device
+
+
+def init_weights(module):
+    """Same distribution as the reference's init_weights (m3ae_utils.py:101-109): Linear/Embedding N(0,0.02),
+    bias 0, LayerNorm weight 1 / bias 0."""
+    if isinstance(module, (nn.Linear, nn.Embedding)):
+        module.weight.data.normal_(mean=0.0, std=0.02)
+    elif isinstance(module, nn.LayerNorm):
+        module.bias.data.zero_()
+        module.weight.data.fill_(1.0)
+    if isinstance(module, nn.Linear) and module.bias is not None:
+        module.bias.data.zero_()
+
+
+class Pooler(nn.Module):
+    """prediction_heads.Pooler (prediction_heads.py:9-19): tanh(dense(token 0)).  M = B rows: stays PyTorch."""
+
+    def __init__(self, hidden_size):
+        super().__init__()
+        self.dense = nn.Linear(hidden_size, hidden_size)
+        self.activation = nn.Tanh()
+
+    def forward(self, hidden_states):
+        return self.activation(self.dense(hidden_states[:, 0].float()))
+
+
+def extended_attention_mask(mask):
+    """HF 4.6.0 get_extended_attention_mask as used at m3ae_module.py:232,255 -> additive [B,1,1,L] fp32."""
+    return (1.0 - mask[:, None, None, :].to(torch.float32)) * -10000.0
+
+
+DEFAULT_CONFIG = {  # config.py:19-119 + task_finetune_vqa_vqa_rad (:176-198) + clip16 (:245-251) + text_roberta (:256-259)
+    "vit": "ViT-B/16", "tokenizer": "roberta-base", "vocab_size": 50265, "hidden_size": 768, "num_layers": 6,
+    "num_heads": 12, "mlp_ratio": 4, "max_text_len": 32, "drop_rate": 0.1, "image_size": 288, "patch_size": 16,
+    "input_text_embed_size": 768, "input_image_embed_size": 768, "num_top_layer": 6,
+    "loss_names": {"mlm": 0, "mim": 0, "itm": 0, "vqa": 1, "cls": 0, "irtr": 0}, "load_path": "", "test_only": False,
+    "vqa_label_size": 498, "precision": 16, "learning_rate": 5e-6, "weight_decay": 0.01, "lr_multiplier_head": 50,
+    "lr_multiplier_multi_modal": 5, "end_lr": 0, "decay_power": 1, "optim_type": "adamw", "warmup_steps": 0.1,
+    "max_steps": None, "max_epoch": 50,
+}
+
+
+def _bert_config(config):
+    from transformers import RobertaConfig
+    return RobertaConfig(  # m3ae_module.py:24-33
+        vocab_size=config["vocab_size"], hidden_size=config["hidden_size"], num_hidden_layers=config["num_layers"],
+        num_attention_heads=config["num_heads"], intermediate_size=config["hidden_size"] * config["mlp_ratio"],
+        max_position_embeddings=config["max_text_len"], hidden_dropout_prob=config["drop_rate"],
+        attention_probs_dropout_prob=config["drop_rate"])
+
+
+class M3AEFusion(_Base):
+    def __init__(self, config=None, compute_dtype=None):
+        super().__init__()
+        config = dict(DEFAULT_CONFIG, **(config or {}))
+        self.save_hyperparameters(config)
+        if compute_dtype is None:
+            compute_dtype = torch.float32 if config.get("precision", 32) == 32 else torch.bfloat16
+        self.compute_dtype = compute_dtype
+        bert_config = _bert_config(config)
+        hs = config["hidden_size"]
+        self.multi_modal_language_proj = nn.Linear(config["input_text_embed_size"], hs)
+        self.multi_modal_vision_proj = nn.Linear(config["input_image_embed_size"], hs)
+        self.modality_type_embeddings = nn.Embedding(2, hs)
+        self.multi_modal_vision_layers = nn.ModuleList(
+            [BertCrossLayer(bert_config, compute_dtype) for _ in range(config["num_top_layer"])])
+        self.multi_modal_language_layers = nn.ModuleList(
+            [BertCrossLayer(bert_config, compute_dtype) for _ in range(config["num_top_layer"])])
+        self.multi_modal_vision_pooler = Pooler(hs)
+        self.multi_modal_language_pooler = Pooler(hs)
+        if config["loss_names"].get("vqa", 0) > 0:
+            vs = config["vqa_label_size"]
+            self.vqa_head = nn.Sequential(nn.Linear(hs * 2, hs * 2), nn.LayerNorm(hs * 2), nn.GELU(), nn.Linear(hs * 2, vs))
+        self.apply(init_weights)
+        self.current_tasks = list()
+
+    def set_compute_dtype(self, dtype):
+        self.compute_dtype = dtype
+        for l in list(self.multi_modal_vision_layers) + list(self.multi_modal_language_layers):
+            l.set_compute_dtype(dtype)
+        return self
+
+    def fuse(self, uni_modal_text_feats, uni_modal_image_feats, text_masks, image_token_type_idx=1, output_attentions=False):
+        """m3ae_module.py:235,252-297: modality projections + type embeddings, 6 co-attention layer pairs, poolers."""
+        ret = {}
+        dt = self.compute_dtype
+        tte = self.modality_type_embeddings.weight
+        # projection + bias + type-embedding row in one GEMM epilogue (:235,:252,:260-263)
+        x = Fn.linear(uni_modal_text_feats, self.multi_modal_language_proj.weight, self.multi_modal_language_proj.bias,
+                      extra_bias=tte[0], dtype=dt)
+        y = Fn.linear(uni_modal_image_feats, self.multi_modal_vision_proj.weight, self.multi_modal_vision_proj.bias,
+                      extra_bias=tte[image_token_type_idx], dtype=dt)
+        device = x.device
+        extended_text_masks = extended_attention_mask(text_masks.to(device))
+        image_masks = torch.ones((y.size(0), y.size(1)), dtype=torch.long, device=device)
+        extended_image_masks = extended_attention_mask(image_masks)
+        ret["attentions"] = {"text2image_attns": [], "image2text_attns": []} if output_attentions else None
+        for text_layer, image_layer in zip(self.multi_modal_language_layers, self.multi_modal_vision_layers):
+            x1, y1 = fused_layer_pair(text_layer, image_layer, x, y, extended_text_masks, extended_image_masks,
+                                      output_attentions=output_attentions)
+            x, y = x1[0], y1[0]
+            if output_attentions:
+                ret["attentions"]["text2image_attns"].append(x1[1:])
+                ret["attentions"]["image2text_attns"].append(y1[1:])
+        multi_modal_text_feats, multi_modal_image_feats = x.float(), y.float()
+        cls_text = self.multi_modal_language_pooler(multi_modal_text_feats)
+        cls_image = self.multi_modal_vision_pooler(multi_modal_image_feats)
+        ret.update({
+            "extended_image_masks": extended_image_masks,
+            "extended_text_masks": extended_text_masks,
+            "multi_modal_text_feats": multi_modal_text_feats,
+            "multi_modal_image_feats": multi_modal_image_feats,
+            "multi_modal_cls_feats": torch.cat([cls_text, cls_image], dim=-1),
+        })
+        return ret
+
+    def vqa_loss_from_feats(self, uni_modal_text_feats, uni_modal_image_feats, text_masks, vqa_targets):
+        """compute_vqa_m3ae restricted to tensors (objectives.py:177-178,201)."""
+        ret = self.fuse(uni_modal_text_feats, uni_modal_image_feats, text_masks)
+        logits = self.vqa_head(ret["multi_modal_cls_feats"])
+        loss = F.binary_cross_entropy_with_logits(logits, vqa_targets) * vqa_targets.shape[1]
+        return loss, logits, ret
+
+
+# ----------------------------------------------------------------------------- uni-modal encoders (plain PyTorch, "next" rows)
+class _LayerNormF32(nn.LayerNorm):
+    def forward(self, x):
+        return super().forward(x.float()).to(x.dtype)
+
+
+class _ResBlock(nn.Module):
+    """CLIP ResidualAttentionBlock (clip_model.py:41-63): pre-LN MHA + QuickGELU MLP; parameter names kept."""
+
+    def __init__(self, d_model, n_head):
+        super().__init__()
+        self.attn = nn.MultiheadAttention(d_model, n_head)
+        self.ln_1 = _LayerNormF32(d_model)
+        self.mlp = nn.Sequential(OrderedDict([("c_fc", nn.Linear(d_model, d_model * 4)), ("gelu", nn.Identity()),
+                                              ("c_proj", nn.Linear(d_model * 4, d_model))]))
+        self.ln_2 = _LayerNormF32(d_model)
+        self.n_head = n_head
+
+    def forward(self, x):  # x: [B, L, D]
+        B, L, D = x.shape
+        h = self.ln_1(x)
+        qkv = F.linear(h, self.attn.in_proj_weight, self.attn.in_proj_bias).view(B, L, 3, self.n_head, D // self.n_head)
+        q, k, v = qkv.permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, L, D)
+        x = x + self.attn.out_proj(a)
+        h = self.mlp.c_fc(self.ln_2(x))
+        return x + self.mlp.c_proj(h * torch.sigmoid(1.702 * h))
+
+
+class _Transformer(nn.Module):
+    def __init__(self, width, layers, heads):
+        super().__init__()
+        self.width, self.layers = width, layers
+        self.resblocks = nn.Sequential(*[_ResBlock(width, heads) for _ in range(layers - 1)])  # clip_model.py:71
+
+    def forward(self, x):
+        return self.resblocks(x)
+
+
+class _VisualTransformer(nn.Module):
+    """clip_model.VisualTransformer (:79-128), batch-first."""
+
+    def __init__(self, patch_size, width, layers, heads, resolution_after):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, width, kernel_size=patch_size, stride=patch_size, bias=False)
+        scale = width ** -0.5
+        self.class_embedding = nn.Parameter(scale * torch.randn(width))
+        self.positional_embedding = nn.Parameter(scale * torch.randn((resolution_after // patch_size) ** 2 + 1, width))
+        self.ln_pre = _LayerNormF32(width)
+        self.transformer = _Transformer(width, layers, heads)
+        self.ln_post = _LayerNormF32(width)
+
+    def forward(self, x):
+        x = self.conv1(x).flatten(2).transpose(1, 2)
+        cls = self.class_embedding.to(x.dtype).expand(x.shape[0], 1, -1)
+        x = torch.cat([cls, x], dim=1) + self.positional_embedding.to(x.dtype)
+        return self.ln_post(self.transformer(self.ln_pre(x)))
+
+
+class _ClipVisionEncoder(nn.Module):
+    """`vision_encoder` of the reference = CLIP whose forward is visual(image) (clip_model.py:186-187)."""
+
+    def __init__(self, resolution_after, patch_size=16, width=768, layers=12, heads=12):
+        super().__init__()
+        self.visual = _VisualTransformer(patch_size, width, layers, heads, resolution_after)
+        proj_std = (width ** -0.5) * ((2 * layers) ** -0.5)
+        for b in self.visual.transformer.resblocks:  # clip_model.py:172-180
+            nn.init.normal_(b.attn.in_proj_weight, std=width ** -0.5)
+            nn.init.normal_(b.attn.out_proj.weight, std=proj_std)
+            nn.init.normal_(b.mlp.c_fc.weight, std=(2 * width) ** -0.5)
+            nn.init.normal_(b.mlp.c_proj.weight, std=proj_std)
+
+    def forward(self, image):
+        return self.visual(image.to(self.visual.conv1.weight.dtype))
+
+
+class M3AETransformerSS(M3AEFusion):
+    """Drop-in for the reference class of the same name (VQA fine-tune / test surface)."""
+
+    def __init__(self, config=None, compute_dtype=None):
+        super().__init__(config, compute_dtype)
+        config = self.hparams.config
+        from transformers import RobertaConfig, RobertaModel
+        self.is_clip = "swin" not in config["vit"]
+        if not self.is_clip:
+            raise NotImplementedError("Swin backbones are outside the B200 hot-path scope (SURVEY §2 #10)")
+        # The reference downloads pretrained CLIP / RoBERTa weights (m3ae_module.py:60-68); offline they are random-init
+        # modules of the same architecture whose state_dict keys match, so a reference checkpoint restores them.
+        self.vision_encoder = _ClipVisionEncoder(config["image_size"], config["patch_size"])
+        rc = RobertaConfig(vocab_size=config["vocab_size"], hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
+                           intermediate_size=3072, max_position_embeddings=514, type_vocab_size=1, pad_token_id=1,
+                           layer_norm_eps=1e-5)
+        self.language_encoder = RobertaModel(rc)
+        if config["load_path"]:
+            sd = torch.load(config["load_path"], map_location="cpu")["state_dict"]
+            self.load_state_dict(sd, strict=False)
+
+    def patchify(self, imgs):
+        p = self.hparams.config["patch_size"]  # m3ae_module.py:185-192
+        h = w = imgs.shape[2] // p
+        x = imgs.reshape(imgs.shape[0], 3, h, p, w, p)
+        return torch.einsum("nchpwq->nhwpqc", x).reshape(imgs.shape[0], h * w, p ** 2 * 3)
+
+    def encode_text(self, text_ids, text_masks):
+        """m3ae_module.py:230-234: RoBERTa embeddings + 12 layers driven one by one with the additive mask."""
+        h = self.language_encoder.embeddings(input_ids=text_ids)
+        ext = extended_attention_mask(text_masks)
+        for layer in self.language_encoder.encoder.layer:
+            out = layer(h, ext)
+            h = out[0] if isinstance(out, (tuple, list)) else out
+        return h
+
+    def infer(self, batch, mask_text=False, mask_image=False, image_token_type_idx=1, img=None, output_attentions=False,
+              unimodal=False):
+        if mask_text or mask_image:
+            raise NotImplementedError("MLM/MIM pre-training paths are outside the B200 hot-path scope (SURVEY §8)")
+        if img is None:
+            key = f"image_{image_token_type_idx - 1}"
+            img = batch[key if key in batch else "image"][0]
+        text_ids, text_labels, text_masks = batch["text_ids"], batch["text_labels"], batch["text_masks"]
+        autocast = self.compute_dtype == torch.bfloat16
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            uni_text = self.encode_text(text_ids, text_masks)
+            uni_image = self.vision_encoder(img)
+        ret = self.fuse(uni_text, uni_image, text_masks, image_token_type_idx, output_attentions)
+        ret.update({"images": img, "patched_images": self.patchify(img), "text_labels": text_labels, "text_ids": text_ids,
+                    "text_masks": text_masks})
+        return ret
+
+    def compute_vqa(self, batch, test=False):
+        """objectives.compute_vqa_m3ae (objectives.py:176-234) minus the CPU string metrics."""
+        infer = self.infer(batch)
+        logits = self.vqa_head(infer["multi_modal_cls_feats"])
+        n = self.hparams.config["vqa_label_size"]
+        targets = torch.zeros(len(logits), n, device=logits.device)
+        rows, cols, vals = [], [], []
+        for i, (labels, scores) in enumerate(zip(batch["vqa_labels"], batch["vqa_scores"])):
+            for l, s in zip(labels, scores):
+                rows.append(i), cols.append(l), vals.append(s)
+        if rows:
+            targets[torch.tensor(rows, device=logits.device), torch.tensor(cols, device=logits.device)] = torch.tensor(vals, device=logits.device)
+        loss = F.binary_cross_entropy_with_logits(logits, targets) * targets.shape[1]
+        phase = "test" if test else ("train" if self.training else "val")
+        self.log(f"{phase}/vqa/loss", loss.detach())
+        return {"vqa_loss": loss, "vqa_logits": logits, "vqa_targets": targets, "vqa_labels": batch["vqa_labels"],
+                "vqa_scores": batch["vqa_scores"], "vqa_predictions": logits.argmax(dim=1),
+                "vqa_answer_types": torch.tensor(batch.get("answer_types", [0] * len(logits)), device=logits.device)}
+
+    def forward(self, batch, test=False):
+        ret = dict()
+        if len(self.current_tasks) == 0:
+            ret.update(self.infer(batch))
+            return ret
+        if "vqa" in self.current_tasks:
+            ret.update(self.compute_vqa(batch, test=test))
+        return ret
+
+    # ---- pytorch_lightning hooks (m3ae_module.py:347-373)
+    def _set_task(self):
+        self.current_tasks = [k for k, v in self.hparams.config["loss_names"].items() if v > 0]
+
+    def training_step(self, batch, batch_idx):
+        self._set_task()
+        output = self(batch)
+        return sum(v * self.hparams.config["loss_names"][k.replace("_loss", "")] for k, v in output.items() if "loss" in k)
+
+    def validation_step(self, batch, batch_idx):
+        self._set_task()
+        return self(batch)
+
+    def test_step(self, batch, batch_idx):
+        self._set_task()
+        return self(batch, test=True)
+
+    def training_epoch_end(self, outs):
+        pass
+
+    validation_epoch_end = test_epoch_end = training_epoch_end
+
+    def configure_optimizers(self, max_steps=1000):
+        """m3ae_utils.set_schedule (:112-242): 6 AdamW groups by parameter name, polynomial decay with warm-up."""
+        c = self.hparams.config
+        lr, wd = c["learning_rate"], c["weight_decay"]
+        no_decay = ["bias", "LayerNorm.bias", "LayerNorm.weight", "norm.bias", "norm.weight", "norm1.bias", "norm1.weight",
+                    "norm2.bias", "norm2.weight"]
+        heads = ["mlm_head", "mim_head", "itm_head", "vqa_head", "cls_head", "irtr_head"]
+        groups = {}
+        for n, p in self.named_parameters():
+            nd = any(t in n for t in no_decay)
+            kind = "head" if any(t in n for t in heads) else ("mm" if "multi_modal" in n else "base")
+            groups.setdefault((kind, nd), []).append(p)
+        mult = {"base": 1.0, "head": c["lr_multiplier_head"], "mm": c["lr_multiplier_multi_modal"]}
+        param_groups = [{"params": ps, "weight_decay": 0.0 if nd else wd, "lr": lr * mult[kind]} for (kind, nd), ps in groups.items()]
+        opt = torch.optim.AdamW(param_groups, lr=lr, eps=1e-8, betas=(0.9, 0.98), fused=next(self.parameters()).is_cuda)
+        max_steps = c["max_steps"] or max_steps
+        warm = c["warmup_steps"]
+        warm = int(max_steps * warm) if isinstance(warm, float) else warm
+        end_lr, power = c["end_lr"], c["decay_power"]
+
+        def lr_lambda(step):  # HF get_polynomial_decay_schedule_with_warmup
+            if step < warm:
+                return step / max(1, warm)
+            if step > max_steps:
+                return end_lr / lr
+            rem = 1 - (step - warm) / max(1, max_steps - warm)
+            return ((lr - end_lr) * rem ** power + end_lr) / lr
+
+        sched = torch.optim.lr_scheduler.LambdaLR(opt, lr_lambda)
+        return [opt], [{"scheduler": sched, "interval": "step"}]
+
+
+def patch_m3ae(model, compute_dtype=torch.bfloat16):
+    """Swap the BertCrossLayer instances of an existing (reference) M3AETransformerSS for the B200 ones in place,
+    re-using the Parameter objects so checkpoints, optimizer param groups and DDP keep working."""
+    for name in ("multi_modal_vision_layers", "multi_modal_language_layers"):
+        layers = getattr(model, name)
+        for i, old in enumerate(layers):
+            cfg = type("Cfg", (), {})()
+            a = old.attention.self
+            cfg.hidden_size = a.query.in_features
+            cfg.num_attention_heads = a.num_attention_heads
+            cfg.intermediate_size = old.intermediate.dense.out_features
+            cfg.hidden_act = "gelu"
+            cfg.layer_norm_eps = old.output.LayerNorm.eps
+            cfg.hidden_dropout_prob = old.output.dropout.p
+            cfg.attention_probs_dropout_prob = a.dropout.p
+            cfg.chunk_size_feed_forward = 0
+            cfg.is_decoder = False
+            cfg.add_cross_attention = False
+            new = BertCrossLayer(cfg, compute_dtype)
+            old_params = dict(old.named_parameters())
+            for k, _ in list(new.named_parameters()):
+                mod, _, leaf = k.rpartition(".")
+                setattr(new.get_submodule(mod), leaf, old_params[k])
+            new.train(old.training)
+            layers[i] = new
+    return model
