@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const m3ae_attn_params_t 
       m[r] = m_new;
       float pd = p;
       if (P.drop_p > 0.f && key < P.Lk) {
-        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
-        pd = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? p * keep_scale : 0.f;
+        const uint64_t rl = ((uint64_t)b * P.H + h) * P.Lq + qi;
+        pd = attn_dropout_keep(P.drop_seed, P.drop_stream, rl, key, P.drop_p) ? p * keep_scale : 0.f;
       }
 #pragma unroll
       for (int i = 0; i < ND; ++i) o[r][i] *= corr;
@@ -119,8 +119,8 @@ __global__ void __launch_bounds__(128) attn_probs_kernel(const m3ae_attn_params_
     s = s * P.scale + (P.mask ? P.mask[(size_t)b * P.Lk + key] : 0.f);
     float p = (P.causal && key > qi) ? 0.f : expf(s - lse);
     if (P.drop_p > 0.f) {
-      const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
-      p = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? p * keep_scale : 0.f;
+      const uint64_t rl = ((uint64_t)b * P.H + h) * P.Lq + qi;
+      p = attn_dropout_keep(P.drop_seed, P.drop_stream, rl, key, P.drop_p) ? p * keep_scale : 0.f;
     }
     out[key] = p;
   }
@@ -200,8 +200,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params
       if (P.causal && key > qi) s = -INFINITY;
       const float p = expf(s - lse[r]);
       if (P.drop_p > 0.f && key < P.Lk) {
-        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
-        dp = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p) ? dp * keep_scale : 0.f;
+        const uint64_t rl = ((uint64_t)b * P.H + h) * P.Lq + qi;
+        dp = attn_dropout_keep(P.drop_seed, P.drop_stream, rl, key, P.drop_p) ? dp * keep_scale : 0.f;
       }
       const float ds = p * (dp - dl[r]) * P.scale;
 #pragma unroll 8
@@ -286,8 +286,8 @@ __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const m3ae_attn_param
       float p = (q_ok && !(P.causal && key > qi)) ? expf(s - sLse[lane]) : 0.f;
       float pd = p;
       if (P.drop_p > 0.f && q_ok) {
-        const uint64_t e = (((uint64_t)b * P.H + h) * P.Lq + qi) * (uint64_t)P.Lk + key;
-        const bool keep = dropout_keep(P.drop_seed, P.drop_stream, e, P.drop_p);
+        const uint64_t rl = ((uint64_t)b * P.H + h) * P.Lq + qi;
+        const bool keep = attn_dropout_keep(P.drop_seed, P.drop_stream, rl, key, P.drop_p);
         pd = keep ? p * keep_scale : 0.f;
         dp = keep ? dp * keep_scale : 0.f;
       }
@@ -414,6 +414,14 @@ __global__ void decoder_embed_kernel(const int64_t* __restrict__ ids, const int3
 }
 
 template <typename T>
+void launch_probs(const m3ae_attn_params_t* p, cudaStream_t st) {
+  dim3 g2((p->Lq + 3) / 4, p->H, p->B);
+  if (p->dh == 64) attn_probs_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
+  else attn_probs_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
+  count_launch();
+}
+
+template <typename T>
 int launch_generic_fwd(const m3ae_attn_params_t* p, cudaStream_t st) {
   if (p->dh == 64) {
     dim3 grid((p->Lq + 31) / 32, p->H, p->B);
@@ -423,12 +431,7 @@ int launch_generic_fwd(const m3ae_attn_params_t* p, cudaStream_t st) {
     attn_fwd_kernel<T, 96, 4><<<grid, 128, 0, st>>>(*p);
   }
   count_launch();
-  if (p->probs) {
-    dim3 g2((p->Lq + 3) / 4, p->H, p->B);
-    if (p->dh == 64) attn_probs_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
-    else attn_probs_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
-    count_launch();
-  }
+  if (p->probs) launch_probs<T>(p, st);
   return M3AE_OK;
 }
 
@@ -463,11 +466,21 @@ int validate(const m3ae_attn_params_t* p, bool bwd) {
 
 }  // namespace
 
+void launch_delta_bf16_64(const m3ae_attn_params_t* p, cudaStream_t st) {
+  dim3 g0((p->Lq + 3) / 4, p->H, p->B);
+  attn_delta_kernel<bf16, 64><<<g0, 128, 0, st>>>(*p);
+  count_launch();
+}
+
 int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, false);
   if (rc) return rc;
   if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
     rc = attn_fwd_mma(p, st);
+    if (rc == M3AE_OK && p->probs) {
+      launch_probs<bf16>(p, st);
+      M3AE_CUDA(cudaGetLastError());
+    }
     if (rc != M3AE_ERR_UNSUPPORTED) return rc;
   }
   if (p->dtype == M3AE_BF16) launch_generic_fwd<bf16>(p, st);

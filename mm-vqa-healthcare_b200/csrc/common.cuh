@@ -112,6 +112,23 @@ __device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream
   return m;
 }
 
+// Attention-probability dropout: element (row_lin = (b*H+h)*Lq+i, key) -> Philox counter (row_lin, stream | key/4),
+// lane key%4, so the two adjacent keys a tensor-core accumulator fragment holds share one Philox evaluation.
+__device__ __forceinline__ uint32_t attn_dropout_keep4(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key, float p) {
+  Philox ph(seed);
+  const uint4 r = ph(row_lin, (stream_id << 32) | (uint64_t)(uint32_t)(key >> 2));
+  const float s = 1.0f / 16777216.0f;
+  uint32_t m = 0;
+  m |= ((float)(r.x >> 8) * s >= p) ? 1u : 0u;
+  m |= ((float)(r.y >> 8) * s >= p) ? 2u : 0u;
+  m |= ((float)(r.z >> 8) * s >= p) ? 4u : 0u;
+  m |= ((float)(r.w >> 8) * s >= p) ? 8u : 0u;
+  return m;
+}
+__device__ __forceinline__ bool attn_dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key, float p) {
+  return (attn_dropout_keep4(seed, stream_id, row_lin, key, p) >> (key & 3)) & 1u;
+}
+
 // ---------------------------------------------------------------- warp helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
