@@ -149,11 +149,13 @@ int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream);
 int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                        int64_t M, int32_t H, float eps, int32_t dtype, void* stream);
 /* dx = LN'(dy); dgamma/dbeta (+)= column reductions (atomic accumulate into caller-zeroed or
- * grad-accumulating fp32 buffers); dcolsum (optional, fp32 [H]) += column sums of dx, which is the
- * bias gradient of the Linear that produced x. */
+ * grad-accumulating fp32 buffers).  When the Linear that produced x applied hidden dropout in its epilogue
+ * (drop_p > 0), dx_drop receives dx pushed back through that dropout (same Philox stream, element = row*H+col) —
+ * the operand of that Linear's dgrad/wgrad GEMMs — while dx stays the residual-branch gradient.
+ * dcolsum (optional, fp32 [H]) += column sums of dx_drop (or dx when drop_p == 0): the Linear's bias gradient. */
 int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
                        void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype,
-                       void* stream);
+                       void* dx_drop, float drop_p, uint64_t drop_seed, uint64_t drop_stream, void* stream);
 
 /* out[N] (fp32) += column sums of x[M,N] (ld elements).  Bias gradients of the projections. */
 int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int32_t dtype, void* stream);

@@ -82,7 +82,9 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restri
                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
                                                               const float* __restrict__ gamma, T* __restrict__ dx,
                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                              float* __restrict__ dcolsum, int64_t M, int H) {
+                                                              float* __restrict__ dcolsum, int64_t M, int H,
+                                                              T* __restrict__ dx_drop, float drop_p, uint64_t drop_seed,
+                                                              uint64_t drop_stream) {
   constexpr int VN = Vec<T>::N;
   extern __shared__ float red[];  // [LN_WARPS][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -122,11 +124,21 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restri
       const int c = (i * 32 + lane) * VN;
       float o[VN];
 #pragma unroll
-      for (int j = 0; j < VN; ++j) {
-        o[j] = rs * (gd[i][j] - c1 - xh[i][j] * c2);
-        pc[i][j] += to_f32<T>(from_f32<T>(o[j]));  // column sum of what downstream consumers actually read
-      }
+      for (int j = 0; j < VN; ++j) o[j] = rs * (gd[i][j] - c1 - xh[i][j] * c2);
       Vec<T>::store(dx + row * H + c, o);
+      if (dx_drop != nullptr) {
+        // gradient through the hidden dropout of the producing GEMM epilogue: same Philox stream, element = row*H+col
+        const float inv = 1.0f / (1.0f - drop_p);
+#pragma unroll
+        for (int q = 0; q < VN / 4; ++q) {
+          const uint32_t m4 = dropout_keep4(drop_seed, drop_stream, (uint64_t)(row * H + c + 4 * q), drop_p);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[4 * q + j] = ((m4 >> j) & 1u) ? o[4 * q + j] * inv : 0.f;
+        }
+        Vec<T>::store(dx_drop + row * H + c, o);
+      }
+#pragma unroll
+      for (int j = 0; j < VN; ++j) pc[i][j] += to_f32<T>(from_f32<T>(o[j]));  // column sum of what the GEMMs read
     }
   }
   // CTA reduction of the three column partials, one at a time through the same smem buffer.
@@ -226,7 +238,10 @@ int layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
 }
 
 int layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx,
-                  float* dgamma, float* dbeta, float* dcolsum, int64_t M, int H, int dtype, cudaStream_t st) {
+                  float* dgamma, float* dbeta, float* dcolsum, int64_t M, int H, int dtype, void* dx_drop, float drop_p,
+                  uint64_t drop_seed, uint64_t drop_stream, cudaStream_t st) {
+  M3AE_CHECK(drop_p >= 0.f && drop_p < 1.f, M3AE_ERR_INVALID, "layernorm_bwd: dropout %f not in [0,1)", drop_p);
+  if (drop_p == 0.f) dx_drop = nullptr;
   M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
   int64_t want = (M + LN_WARPS - 1) / LN_WARPS;
   const int64_t cap = (int64_t)sm_count() * 4;
@@ -234,7 +249,7 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
 #define LN_BWD(T, HV)                                                                                                     \
   ln_bwd_kernel<T, HV><<<grid, LN_WARPS * 32, smem, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
-                                                          dbeta, dcolsum, M, H)
+                                                          dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream)
   if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3);
   else if (dtype == M3AE_BF16 && H == 1536) LN_BWD(bf16, 6);
   else if (dtype == M3AE_F32 && H == 768) LN_BWD(float, 6);

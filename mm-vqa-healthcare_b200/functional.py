@@ -229,11 +229,13 @@ def _backward_streams(cfg, S, douts):
     def new(rows, cols):
         return torch.empty(rows, cols, dtype=dt, device=dev)
 
-    def dropped(st, d, site):
-        # gradient through hidden dropout: same Philox stream as the forward epilogue
-        if st.ph <= 0.0:
-            return d
-        return ops.dropout_apply(d, torch.empty_like(d), st.ph, st.seed, site)
+    def ln_bwd(st, d, h, mean, rstd, gamma, dg, db, dbias, site):
+        """LayerNorm backward; also returns the gradient pushed back through the hidden dropout of the GEMM that
+        produced h (same Philox stream as the forward epilogue) and accumulates that GEMM's bias gradient."""
+        if st.ph > 0.0:
+            return ops.layernorm_bwd(d, h, mean, rstd, gamma, dg, db, dbias, drop_p=st.ph, drop_seed=st.seed, drop_stream=site)
+        dx = ops.layernorm_bwd(d, h, mean, rstd, gamma, dg, db, dbias)
+        return dx, dx
 
     def wgrad(dy, x, dw):
         return ops.GemmSpec(dy, x, dw, a_major=MN, b_major=MN, accumulate=True,
@@ -244,10 +246,7 @@ def _backward_streams(cfg, S, douts):
         H, FF = st.H, st.FF
         # ---- output LayerNorm + FFN
         st.g_[G3], st.g_[B3], st.g_[BO3] = zeros(H), zeros(H), zeros(H)
-        st.dh3 = ops.layernorm_bwd(d, st.h3, st.mean3, st.rstd3, st.p[G3], st.g_[G3], st.g_[B3], None if st.ph > 0 else st.g_[BO3])
-        st.dh3d = dropped(st, st.dh3, 4)
-        if st.ph > 0:
-            ops.colsum(st.dh3d, st.g_[BO3])
+        st.dh3, st.dh3d = ln_bwd(st, d, st.h3, st.mean3, st.rstd3, st.p[G3], st.g_[G3], st.g_[B3], st.g_[BO3], 4)
         st.du = new(st.M, FF)
         st.g_[W2] = zeros(H, FF)
     ops.gemm_group([ops.GemmSpec(st.dh3d, st.w.w2, st.du, b_major=MN, aux_in=st.u, dact=ops.ACT_GELU) for st in S] +
@@ -262,10 +261,7 @@ def _backward_streams(cfg, S, douts):
     for st in S:
         H = st.H
         st.g_[G2], st.g_[B2], st.g_[BO2] = zeros(H), zeros(H), zeros(H)
-        st.dh2 = ops.layernorm_bwd(st.da2, st.h2, st.mean2, st.rstd2, st.p[G2], st.g_[G2], st.g_[B2], None if st.ph > 0 else st.g_[BO2])
-        st.dh2d = dropped(st, st.dh2, 3)
-        if st.ph > 0:
-            ops.colsum(st.dh2d, st.g_[BO2])
+        st.dh2, st.dh2d = ln_bwd(st, st.da2, st.h2, st.mean2, st.rstd2, st.p[G2], st.g_[G2], st.g_[B2], st.g_[BO2], 3)
         st.dctx2 = new(st.M, H)
         st.g_[WO2] = zeros(H, H)
     ops.gemm_group([ops.GemmSpec(st.dh2d, st.w.wo2, st.dctx2, b_major=MN) for st in S] +
@@ -294,10 +290,7 @@ def _backward_streams(cfg, S, douts):
         st.g_[WQ2] = st.g_wq2
         st.g_[WK2], st.g_[WV2] = st.g_wkv2[:H], st.g_wkv2[H:]
         st.g_[G1], st.g_[B1], st.g_[BO] = zeros(H), zeros(H), zeros(H)
-        st.dh1 = ops.layernorm_bwd(st.da1, st.h1, st.mean1, st.rstd1, st.p[G1], st.g_[G1], st.g_[B1], None if st.ph > 0 else st.g_[BO])
-        st.dh1d = dropped(st, st.dh1, 1)
-        if st.ph > 0:
-            ops.colsum(st.dh1d, st.g_[BO])
+        st.dh1, st.dh1d = ln_bwd(st, st.da1, st.h1, st.mean1, st.rstd1, st.p[G1], st.g_[G1], st.g_[B1], st.g_[BO], 1)
         st.dctx = new(st.M, H)
         st.g_[WO] = zeros(H, H)
     ops.gemm_group([ops.GemmSpec(st.dh1d, st.w.wo, st.dctx, b_major=MN) for st in S] +

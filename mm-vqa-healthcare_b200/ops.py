@@ -162,17 +162,21 @@ def layernorm_fwd(x, gamma, beta, eps, y=None, mean=None, rstd=None):
     return y, mean, rstd
 
 
-def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma=None, dbeta=None, dcolsum=None, dx=None):
-    """dgamma / dbeta / dcolsum are accumulated into (+=); pass zeroed fp32 buffers for plain gradients."""
+def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma=None, dbeta=None, dcolsum=None, dx=None, drop_p=0.0, drop_seed=0,
+                  drop_stream=0):
+    """dgamma / dbeta / dcolsum are accumulated into (+=); pass zeroed fp32 buffers for plain gradients.
+    Returns dx, or (dx, dx_drop) when drop_p > 0 (dx_drop = dx pushed back through the producing GEMM's dropout)."""
     _need_cuda(dy, x, mean, rstd, gamma, dgamma, dbeta, dcolsum)
     assert dy.is_contiguous() and x.is_contiguous() and dy.dtype == x.dtype
     H = x.shape[-1]
     M = x.numel() // H
     dx = torch.empty_like(x) if dx is None else dx
+    dx_drop = torch.empty_like(x) if drop_p > 0 else None
     L.check(L.load().m3ae_layernorm_bwd(_ptr(dy), _ptr(x), _ptr(mean), _ptr(rstd), _ptr(gamma), _ptr(dx), _ptr(dgamma),
-                                        _ptr(dbeta), _ptr(dcolsum), M, H, _code(x.dtype), _stream()),
+                                        _ptr(dbeta), _ptr(dcolsum), M, H, _code(x.dtype), _ptr(dx_drop), float(drop_p),
+                                        int(drop_seed), int(drop_stream), _stream()),
             "m3ae_layernorm_bwd")
-    return dx
+    return (dx, dx_drop) if drop_p > 0 else dx
 
 
 def colsum(x, out):

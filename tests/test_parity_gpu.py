@@ -93,18 +93,19 @@ def test_fused_text_image_pair_equals_separate_layers(dtype):
     x1 = lt(xs, ys, emx, emy)[0]
     y1 = li(ys, xs, emy, emx)[0]
     (x1.sum() + (y1 * y1).sum()).backward()
-    gs = [p.grad.clone() for p in list(lt.parameters()) + list(li.parameters())]
-    for p in list(lt.parameters()) + list(li.parameters()):
+    named = [(k, p) for l in (lt, li) for k, p in l.named_parameters()]
+    gs = [p.grad.clone() for _, p in named]
+    for _, p in named:
         p.grad = None
     xp, yp = x.clone().requires_grad_(True), y.clone().requires_grad_(True)
     (x2,), (y2,) = fused_layer_pair(lt, li, xp, yp, emx, emy)
     (x2.sum() + (y2 * y2).sum()).backward()
     assert torch.equal(x1, x2) and torch.equal(y1, y2)
     assert rel(xp.grad, xs.grad) < 1e-5 and rel(yp.grad, ys.grad) < 1e-5
-    for p, gref in zip(list(lt.parameters()) + list(li.parameters()), gs):
-        if gref.norm() < 1e-6:
-            continue  # key biases: identically-zero gradient, rounding noise only
-        assert rel(p.grad, gref) < 1e-3  # split-K atomics reorder fp32 sums
+    for (k, p), gref in zip(named, gs):
+        if k.endswith("self.key.bias"):
+            continue  # identically-zero gradient (softmax shift invariance): rounding noise only
+        assert rel(p.grad, gref) < 1e-3, k  # split-K atomics reorder fp32 sums
 
 
 def test_training_mode_dropout_is_consistent():
