@@ -195,6 +195,8 @@ int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* tabl
 
 /* Test hook: 0 = auto (tensor-core attention for bf16), 2 = force the generic fp32-math attention kernels. */
 int m3ae_set_attention_backend(int32_t backend);
+/* Test hook: 1 = force the generic per-element GEMM epilogue (cross-checks the TMA-staged one), 0 = auto. */
+int m3ae_set_gemm_epilogue(int32_t generic);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

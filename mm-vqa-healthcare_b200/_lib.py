@@ -78,6 +78,7 @@ SIGNATURES = {
     "m3ae_decoder_embed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                      C.c_int32, C.c_void_p]),
     "m3ae_set_attention_backend": (C.c_int, [C.c_int32]),
+    "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
 }
 
 _lib = None

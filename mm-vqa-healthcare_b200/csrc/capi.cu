@@ -74,6 +74,7 @@ int decode_attn(const void*, int64_t, const void*, const void*, int64_t, int64_t
 int argmax_rows(const void*, int64_t, int64_t*, int64_t, int, int, cudaStream_t);
 int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, void*, int64_t, int, int, cudaStream_t);
 
+extern bool force_generic_epilogue;
 static int g_attn_backend = M3AE_GEMM_AUTO;
 
 }  // namespace m3ae
@@ -115,6 +116,7 @@ int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n, int32_t in_dtype, 
 
 /* Test hook: 0 = auto (tensor-core kernels for bf16), 2 = force the generic fp32-math attention kernels. */
 int m3ae_set_attention_backend(int32_t backend) { g_attn_backend = backend; return M3AE_OK; }
+int m3ae_set_gemm_epilogue(int32_t generic) { force_generic_epilogue = generic != 0; return M3AE_OK; }
 
 int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_fwd(p, g_attn_backend, (cudaStream_t)stream); }
 int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_bwd(p, g_attn_backend, (cudaStream_t)stream); }

@@ -1,7 +1,9 @@
 // Persistent, warp-specialised bf16 GEMM for sm_100a:
-//   TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> 4-stage smem ring -> tcgen05.mma (cta_group::1, 128x256x16,
-//   fp32 accumulators double-buffered in TMEM) -> tcgen05.ld epilogue (bias / GELU / act' / dropout /
-//   residual / split-K atomics) -> global.
+//   TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> 3-stage smem ring -> tcgen05.mma (cta_group::1, 128x256x16,
+//   fp32 accumulators double-buffered in TMEM) -> tcgen05.ld epilogue (bias / GELU / act' / dropout / residual).
+//   bf16 outputs leave through swizzled 32x32 smem staging tiles and TMA stores, residual / pre-activation inputs
+//   arrive through TMA loads into the same kind of tile (each lane owns one accumulator ROW, so direct global
+//   accesses would touch 32 different lines per instruction); fp32 / split-K outputs use per-element atomics.
 // One launch runs up to M3AE_MAX_GROUP independent problems (the text and image streams of a fusion
 // layer pair, reference m3ae_module.py:276-277), each with K-major or MN-major operands so the same kernel
 // serves forward (A K-major, B K-major), dgrad (B MN-major) and wgrad (A and B MN-major, split-K).
@@ -21,19 +23,31 @@ constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 constexpr int B_STAGE_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4..11 epilogue
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+// Epilogue staging: every epilogue warp owns 4 buffers of 32 rows x 32 bf16 (64-byte rows, SWIZZLE_64B):
+// in[0..1] (TMA-loaded residual / pre-activation, double-buffered) and out[0..1] (TMA-stored results).
+constexpr int EPI_BUF_BYTES = 32 * 64;
+constexpr int EPI_WARP_BYTES = 4 * EPI_BUF_BYTES;
+constexpr int EPI_BYTES = NUM_EPI_WARPS * EPI_WARP_BYTES;
+constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
 constexpr int MAX_GROUP = 4;
 
 struct alignas(64) TcProblem {
   CUtensorMap map_a;
   CUtensorMap map_b;
+  CUtensorMap map_out;   // fast epilogue only: bf16 [M,N], box 32x32, SWIZZLE_64B
+  CUtensorMap map_aux;   // aux_out (same geometry as out)
+  CUtensorMap map_in;    // residual or aux_in
+  int epi_fast;          // 1: TMA-staged bf16 epilogue; 0: generic per-element epilogue
+  int in_is_residual;    // fast path: which operand map_in describes (0 = none/aux_in)
+  int has_in;
   EpiDev epi;
   int M, N, K;
   int a_major, b_major;
@@ -79,12 +93,14 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& P, int unit) {
 __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ TcParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = (uint64_t*)(smem + STAGES * STAGE_BYTES);
+  uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
+  uint64_t* bars = (uint64_t*)(epi_smem + EPI_BYTES);
   uint64_t* full_bar = bars;                  // [STAGES]
   uint64_t* empty_bar = bars + STAGES;        // [STAGES]
   uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;  // [2]
-  uint32_t* tmem_ptr_smem = (uint32_t*)(bars + 2 * STAGES + 4);
+  uint64_t* in_bar = bars + 2 * STAGES + 4;   // [NUM_EPI_WARPS][2]
+  uint32_t* tmem_ptr_smem = (uint32_t*)(bars + NUM_BARS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -93,6 +109,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     for (int i = 0; i < P.n_problems; ++i) {
       tma_prefetch_desc(&P.p[i].map_a);
       tma_prefetch_desc(&P.p[i].map_b);
+      if (P.p[i].epi_fast) {
+        tma_prefetch_desc(&P.p[i].map_out);
+        if (P.p[i].epi.aux_out) tma_prefetch_desc(&P.p[i].map_aux);
+        if (P.p[i].has_in) tma_prefetch_desc(&P.p[i].map_in);
+      }
     }
   }
   if (warp == 1 && lane == 0) {
@@ -104,6 +125,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], NUM_EPI_WARPS);
     }
+    for (int s = 0; s < 2 * NUM_EPI_WARPS; ++s) mbar_init(&in_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_ptr_smem);
@@ -186,10 +208,124 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     const int half = e >> 2;    // which 128-column half of the accumulator
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t iph0 = 0, iph1 = 0;  // phases of this warp's two in-buffer barriers
     for (int unit = blockIdx.x; unit < P.total_units; unit += gridDim.x) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
       const EpiDev& epi = q.epi;
+      if (q.epi_fast) {
+        // ---- TMA-staged bf16 epilogue: coalesced in/out through swizzled smem sub-tiles of 32 rows x 32 columns
+        uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
+        uint64_t* ibar = in_bar + 2 * e;
+        const int row0 = u.m_blk * BM + quad * 32;
+        const int col_base = u.n_blk * BN + half * 128;
+        const int nchunks = min(4, (q.N - col_base + 31) / 32);  // <= 0: this warp's half lies outside N
+        const int64_t row = (int64_t)row0 + lane;
+        const uint32_t sw = (uint32_t)((lane >> 1) & 3);           // SWIZZLE_64B: 16-byte chunk ^= (row/2)%4
+        const bool aux = epi.aux_out != nullptr;
+        if (q.has_in && lane == 0 && nchunks > 0) {
+          mbar_expect_tx(&ibar[0], EPI_BUF_BYTES);
+          tma_load_2d(wbuf, &q.map_in, &ibar[0], col_base, row0);
+        }
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tcgen05_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < nchunks; ++c) {
+          const int col = col_base + c * 32;
+          if (q.has_in && lane == 0 && c + 1 < nchunks) {
+            mbar_expect_tx(&ibar[(c + 1) & 1], EPI_BUF_BYTES);
+            tma_load_2d(wbuf + ((c + 1) & 1) * EPI_BUF_BYTES, &q.map_in, &ibar[(c + 1) & 1], col + 32, row0);
+          }
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 128 + c * 32);
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr, r);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (epi.bias) {
+            const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 t4 = __ldg(b4 + j);
+              v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
+            }
+          }
+          uint8_t* obuf = wbuf + (2 + (aux ? 0 : (c & 1))) * EPI_BUF_BYTES;
+          uint8_t* abuf = wbuf + 3 * EPI_BUF_BYTES;
+          // previous TMA stores must have finished READING the staging buffers we are about to overwrite
+          if (lane == 0) { if (aux) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          __syncwarp();
+          if (aux) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 w;
+              w.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]); w.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+              w.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]); w.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+            }
+          }
+          if (epi.act == M3AE_ACT_GELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fast_gelu(v[j]);
+          } else if (epi.act == M3AE_ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          float in[32];
+          if (q.has_in) {
+            if (c & 1) { mbar_wait(&ibar[1], iph1); iph1 ^= 1; } else { mbar_wait(&ibar[0], iph0); iph0 ^= 1; }
+            const uint8_t* ib = wbuf + (c & 1) * EPI_BUF_BYTES;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 w = *reinterpret_cast<const uint4*>(ib + lane * 64 + (((uint32_t)j ^ sw) << 4));
+              float2 f;
+              f = unpack_bf16x2(w.x); in[8 * j + 0] = f.x; in[8 * j + 1] = f.y;
+              f = unpack_bf16x2(w.y); in[8 * j + 2] = f.x; in[8 * j + 3] = f.y;
+              f = unpack_bf16x2(w.z); in[8 * j + 4] = f.x; in[8 * j + 5] = f.y;
+              f = unpack_bf16x2(w.w); in[8 * j + 6] = f.x; in[8 * j + 7] = f.y;
+            }
+            __syncwarp();  // all lanes done with in[c&1] before lane 0 re-arms it two chunks later
+          }
+          if (epi.dact != M3AE_ACT_NONE) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= (epi.dact == M3AE_ACT_GELU) ? fast_gelu_grad(in[j]) : (in[j] > 0.f ? 1.f : 0.f);
+          }
+          if (epi.drop_p > 0.f) {
+            const float inv = 1.0f / (1.0f - epi.drop_p);
+            const uint64_t e0 = (uint64_t)(row * epi.ldo + col);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t m4 = dropout_keep4(epi.drop_seed, epi.drop_stream, e0 + 4 * j, epi.drop_p);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) v[4 * j + k] = ((m4 >> k) & 1u) ? v[4 * j + k] * inv : 0.f;
+            }
+          }
+          if (q.in_is_residual) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += in[j];
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 w;
+            w.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]); w.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+            w.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]); w.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            *reinterpret_cast<uint4*>(obuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&q.map_out, obuf, col, row0);
+            if (aux) tma_store_2d(&q.map_aux, abuf, col, row0);
+            tma_store_commit();
+          }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
       const int64_t row = (int64_t)u.m_blk * BM + quad * 32 + lane;
@@ -249,6 +385,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) tma_store_wait_all();  // staged output tiles must be drained before the CTA's smem goes away
   }
 
   tcgen05_fence_before();
@@ -290,10 +427,45 @@ int encode_map(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, i
   return M3AE_OK;
 }
 
+// bf16 [rows, cols] row-major (ld) viewed through 32x32 boxes with SWIZZLE_64B: the epilogue staging geometry.
+int encode_epi_map(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld) {
+  auto fn = get_encode_fn();
+  M3AE_CHECK(fn != nullptr, M3AE_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)(ld * 2)};
+  cuuint32_t box[2] = {32u, 32u};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  M3AE_CHECK(r == CUDA_SUCCESS, M3AE_ERR_CUDA, "cuTensorMapEncodeTiled (epilogue) failed with CUresult %d", (int)r);
+  return M3AE_OK;
+}
+
+bool tma_ok(const void* p, int64_t ld) { return p != nullptr && (((uintptr_t)p) & 15) == 0 && (ld % 8) == 0; }
+
+// The TMA-staged epilogue covers the layer's bf16 cases: bf16 out (no atomics), N % 32 == 0, alpha == 1, at most one
+// bf16 input operand (residual or aux_in), optional bf16 aux_out.  Everything else uses the generic per-element path.
+bool epilogue_is_fast(const m3ae_gemm_problem_t& g) {
+  const m3ae_gemm_epilogue_t& e = g.epi;
+  if (e.out_dtype != M3AE_BF16 || e.accumulate || e.alpha != 1.0f || (g.N % 32) != 0) return false;
+  if (!tma_ok(e.out, e.ldo)) return false;
+  if (e.aux_out && !tma_ok(e.aux_out, e.ldo)) return false;
+  if (e.bias && (((uintptr_t)e.bias) & 15)) return false;
+  if (e.residual && e.aux_in) return false;
+  if (e.residual && (e.res_dtype != M3AE_BF16 || !tma_ok(e.residual, e.ldr))) return false;
+  if (e.aux_in && (e.aux_in_dtype != M3AE_BF16 || !tma_ok(e.aux_in, e.ld_aux_in))) return false;
+  if (e.dact != M3AE_ACT_NONE && !e.aux_in) return false;
+  if (e.drop_p > 0.f && (e.ldo % 4) != 0) return false;
+  return true;
+}
+
 }  // namespace
 
 void epi_to_dev(const m3ae_gemm_epilogue_t& e, EpiDev* d);
 void count_launch();
+
+bool force_generic_epilogue = false;  // test hook (m3ae_set_gemm_epilogue): run the per-element epilogue everywhere
 
 int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t stream) {
   M3AE_CHECK(n >= 1 && n <= MAX_GROUP, M3AE_ERR_INVALID, "gemm group size %d not in [1,%d]", n, MAX_GROUP);
@@ -324,6 +496,25 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     else rc = encode_map(&q.map_b, g.b, g.K, g.N, g.ldb, BK);
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
+    q.epi_fast = (!force_generic_epilogue && epilogue_is_fast(g)) ? 1 : 0;
+    q.has_in = 0;
+    q.in_is_residual = 0;
+    if (q.epi_fast) {
+      rc = encode_epi_map(&q.map_out, g.epi.out, g.M, g.N, g.epi.ldo);
+      if (rc) return rc;
+      if (g.epi.aux_out) {
+        rc = encode_epi_map(&q.map_aux, g.epi.aux_out, g.M, g.N, g.epi.ldo);
+        if (rc) return rc;
+      }
+      if (g.epi.residual) {
+        rc = encode_epi_map(&q.map_in, g.epi.residual, g.M, g.N, g.epi.ldr);
+        q.has_in = 1; q.in_is_residual = 1;
+      } else if (g.epi.aux_in) {
+        rc = encode_epi_map(&q.map_in, g.epi.aux_in, g.M, g.N, g.epi.ld_aux_in);
+        q.has_in = 1;
+      }
+      if (rc) return rc;
+    }
     q.M = g.M; q.N = g.N; q.K = g.K;
     q.a_major = g.a_major; q.b_major = g.b_major;
     q.tiles_m = (g.M + BM - 1) / BM;

@@ -40,6 +40,11 @@ def set_attention_backend(backend):
     L.check(L.load().m3ae_set_attention_backend(int(backend)), "m3ae_set_attention_backend")
 
 
+def set_gemm_epilogue(generic):
+    """Test hook: True forces the generic per-element epilogue of the tcgen05 GEMM."""
+    L.check(L.load().m3ae_set_gemm_epilogue(1 if generic else 0), "m3ae_set_gemm_epilogue")
+
+
 class GemmSpec:
     """One problem of a grouped launch: out (+)= epi(alpha * A[M,K] · B[N,K]^T).
 

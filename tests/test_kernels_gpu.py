@@ -301,3 +301,34 @@ def test_decode_attention_step():
         ops.decode_attn(q, kc, vc, out, H=H, length=length, dh=dh)
         ref, _ = _attn_ref(q, kc[:, :length].reshape(B * length, H * dh), vc[:, :length].reshape(B * length, H * dh), None, B, H, 1, length, dh, False)
         assert rel_err(out, ref) < tol
+
+
+def test_gemm_tma_staged_epilogue_matches_generic_epilogue():
+    """The tcgen05 kernel has two epilogues (TMA-staged bf16 tiles vs per-element); same inputs must agree, including
+    the dropout mask (same Philox element mapping) and ragged M / N < 256 tails."""
+    for (M, N, K) in [(650, 3072, 768), (333, 96, 128), (2048, 768, 3072)]:
+        a, w = rnd(M, K, dtype=torch.bfloat16), rnd(N, K, dtype=torch.bfloat16, scale=0.05, seed=1)
+        bias, res = rnd(N, seed=2), rnd(M, N, dtype=torch.bfloat16, seed=3)
+        u = rnd(M, N, dtype=torch.bfloat16, seed=4)
+        cases = [dict(bias=bias, residual=res, drop_p=0.1, drop_seed=5, drop_stream=2),
+                 dict(bias=bias, act=ops.ACT_GELU, want_aux=True),
+                 dict(aux_in=u, dact=ops.ACT_GELU),
+                 dict(bias=bias, act=ops.ACT_RELU), dict()]
+        for kw in cases:
+            outs = []
+            for generic in (False, True):
+                ops.set_gemm_epilogue(generic)
+                try:
+                    kw2 = dict(kw)
+                    out = torch.full((M, N), 7.0, dtype=torch.bfloat16, device=DEV)
+                    aux = torch.full((M, N), 7.0, dtype=torch.bfloat16, device=DEV) if kw2.pop("want_aux", False) else None
+                    ops.gemm(a, w, out, backend=ops.GEMM_TCGEN05, aux_out=aux, **kw2)
+                    outs.append((out, aux))
+                finally:
+                    ops.set_gemm_epilogue(False)
+            (o_fast, a_fast), (o_gen, a_gen) = outs
+            assert rel_err(o_fast, o_gen) < 3e-3, f"{(M, N, K)} {list(kw)}: {rel_err(o_fast, o_gen):.3e}"
+            if "drop_p" in kw:
+                assert torch.equal(o_fast == res, o_gen == res)  # dropped positions hold exactly the residual
+            if a_fast is not None:
+                assert torch.equal(a_fast, a_gen)
