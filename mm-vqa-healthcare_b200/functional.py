@@ -447,3 +447,116 @@ def linear(x, weight, bias=None, extra_bias=None, act=ops.ACT_NONE, dtype=torch.
     if not x.is_cuda:
         raise RuntimeError("m3ae_b200.functional.linear needs CUDA tensors: there is no CPU fallback")
     return _LinearFn.apply(x, weight, bias, extra_bias, act, dtype, out_dtype or dtype)
+
+
+# ----------------------------------------------------------------------------- composable autograd pieces (decoder head)
+class _LayerNormFn(torch.autograd.Function):
+    """nn.LayerNorm (m3ae_decoder.py:46-49) on the C-ABI kernels; x [.., H] in fp32 or bf16, affine fp32."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        y, mean, rstd = ops.layernorm_fwd(x2, weight.detach(), bias.detach(), eps)
+        ctx.save_for_backward(x2, mean, rstd, weight)
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, mean, rstd, weight = ctx.saved_tensors
+        H = x2.shape[-1]
+        d2 = dy.reshape(-1, H).contiguous()
+        if d2.dtype != x2.dtype:
+            d2 = ops.cast(d2, torch.empty_like(x2))
+        dg = torch.zeros(H, dtype=torch.float32, device=x2.device)
+        db = torch.zeros(H, dtype=torch.float32, device=x2.device)
+        dx = ops.layernorm_bwd(d2, x2, mean, rstd, weight.detach(), dg, db)
+        return dx.view(ctx.shape), dg, db, None
+
+
+def layernorm(x, weight, bias, eps):
+    return _LayerNormFn.apply(x, weight, bias, eps)
+
+
+class _AttentionFn(torch.autograd.Function):
+    """Multi-head attention core on packed projections: q [B*Lq, H*dh], k/v [B*Lk, H*dh] (may be column slices of a fused
+    projection buffer), additive key mask [B,Lk] or None, optional causal mask.  Returns ctx [B*Lq, H*dh]."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, mask, B, H, Lq, Lk, dh, causal):
+        out = torch.empty(B * Lq, H * dh, dtype=q.dtype, device=q.device)
+        lse = torch.empty(B, H, Lq, dtype=torch.float32, device=q.device)
+        ops.attn_fwd(q, k, v, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal)
+        ctx.save_for_backward(q, k, v, out, lse, mask)
+        ctx.dims = (B, H, Lq, Lk, dh, causal)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, k, v, out, lse, mask = ctx.saved_tensors
+        B, H, Lq, Lk, dh, causal = ctx.dims
+        dout = dout.contiguous()
+        dq = torch.empty(B * Lq, H * dh, dtype=q.dtype, device=q.device)
+        dk = torch.empty(B * Lk, H * dh, dtype=q.dtype, device=q.device)
+        dv = torch.empty(B * Lk, H * dh, dtype=q.dtype, device=q.device)
+        delta = torch.empty(B, H, Lq, dtype=torch.float32, device=q.device)
+        ops.attn_bwd(q, k, v, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal, dout=dout, dq=dq, dk=dk,
+                     dv=dv, delta=delta)
+        return dq, dk, dv, None, None, None, None, None, None, None
+
+
+def attention(q, k, v, mask, B, H, Lq, Lk, dh, causal=False):
+    return _AttentionFn.apply(q, k, v, mask, B, H, Lq, Lk, dh, causal)
+
+
+class _FFNFn(torch.autograd.Function):
+    """y = act(x W0^T + b0) W2^T + b2 (+ residual): the decoder FFN (ReLU, m3ae_decoder.py:45,85-87).  The activation's
+    backward is fused into the dgrad epilogue of the second GEMM (needs the saved pre-activation)."""
+
+    @staticmethod
+    def forward(ctx, x, w0, b0, w2, b2, residual, act, dtype):
+        M, K = x.shape
+        F = w0.shape[0]
+        dev = x.device
+        xc = x if (x.dtype == dtype and x.is_contiguous()) else ops.cast(x.contiguous(), torch.empty(M, K, dtype=dtype, device=dev))
+        w0c = w0.detach() if w0.dtype == dtype else ops.cast(w0.detach(), torch.empty_like(w0, dtype=dtype))
+        w2c = w2.detach() if w2.dtype == dtype else ops.cast(w2.detach(), torch.empty_like(w2, dtype=dtype))
+        u = torch.empty(M, F, dtype=dtype, device=dev)
+        h = torch.empty(M, F, dtype=dtype, device=dev)
+        ops.gemm(xc, w0c, h, bias=b0.detach(), act=act, aux_out=u)
+        y = torch.empty(M, w2.shape[0], dtype=dtype, device=dev)
+        rc = None
+        if residual is not None:
+            rc = residual if (residual.dtype == dtype and residual.is_contiguous()) else ops.cast(residual.contiguous(), torch.empty_like(y))
+        ops.gemm(h, w2c, y, bias=b2.detach(), residual=rc)
+        ctx.save_for_backward(xc, w0c, w2c, u, h)
+        ctx.meta = (act, dtype, residual is not None, x.dtype, w0.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, w0c, w2c, u, h = ctx.saved_tensors
+        act, dtype, has_res, xdtype, wdtype = ctx.meta
+        M, K = xc.shape
+        F = w0c.shape[0]
+        N = w2c.shape[0]
+        dev = dy.device
+        dyc = dy if (dy.dtype == dtype and dy.is_contiguous()) else ops.cast(dy.contiguous(), torch.empty(M, N, dtype=dtype, device=dev))
+        du = torch.empty(M, F, dtype=dtype, device=dev)
+        dw2 = torch.zeros(N, F, dtype=torch.float32, device=dev)
+        MN = ops.MAJOR_MN
+        ops.gemm_group([ops.GemmSpec(dyc, w2c, du, b_major=MN, aux_in=u, dact=act),
+                        ops.GemmSpec(dyc, h, dw2, a_major=MN, b_major=MN, accumulate=True, split_k=_wgrad_split(M, N, F))])
+        dx = torch.empty(M, K, dtype=dtype, device=dev)
+        dw0 = torch.zeros(F, K, dtype=torch.float32, device=dev)
+        ops.gemm_group([ops.GemmSpec(du, w0c, dx, b_major=MN),
+                        ops.GemmSpec(du, xc, dw0, a_major=MN, b_major=MN, accumulate=True, split_k=_wgrad_split(M, F, K))])
+        db2 = ops.colsum(dyc, torch.zeros(N, dtype=torch.float32, device=dev))
+        db0 = ops.colsum(du, torch.zeros(F, dtype=torch.float32, device=dev))
+        if dx.dtype != xdtype:
+            dx = ops.cast(dx, torch.empty(M, K, dtype=xdtype, device=dev))
+        return dx, dw0.to(wdtype), db0, dw2.to(wdtype), db2, (dy if has_res else None), None, None
+
+
+def ffn(x, w0, b0, w2, b2, residual=None, act=ops.ACT_RELU, dtype=torch.bfloat16):
+    return _FFNFn.apply(x, w0, b0, w2, b2, residual, act, dtype)
