@@ -1,0 +1,227 @@
+"""Drop-in for the reference's generative answer head `Decoder` (m3ae/modules/m3ae_decoder.py:93-182) on the sm_100a
+kernels: same constructor, same state_dict keys (`dec_layers.{i}.{mha1,mha2}.{in_proj_weight,in_proj_bias,out_proj.*}`,
+`dec_layers.{i}.ffn.{0,2}.*`, `dec_layers.{i}.{pre_norm,layernorm1,layernorm2,layernorm3}.*`,
+`target_embedding.weight`, `positional_encoding.pe`, `final_linear.*`), same `forward` / `search_path` signatures.
+
+Reference quirks that are reproduced because token IDs must match:
+  * embedding is 2*E[ids] + pe (`target_embed += positional_encoding(target_embed)`, :125-127 with :36);
+  * every layer is fed the embedding and only the LAST layer's output survives (:131-134), so
+    logits == final_linear(dec_layers[-1](embed, memory)); layers 0..n-2 are dead compute and receive no gradient.
+    They are skipped unless `return_all_attentions=True` asks for their attention maps;
+  * DecoderLayer mixes pre- and post-norm: residuals are taken BEFORE layernorm1 / layernorm2 (:54-90);
+  * search_path re-runs the whole prefix each step without a cache and stops only when all rows hit [SEP]; here the
+    same tokens come from a KV-cached single-token step: cross-attention K/V of the memory are projected once, the
+    self-attention K/V of each new token are appended to a cache by the projection GEMM itself.
+
+Per greedy step at B=128 (bf16): live-layer weights 18.9 MB + vocab projection 46.9 MB + cross K/V cache 141 MB are
+streamed once -> HBM-bound.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from . import ops
+
+
+class PositionalEncoding(nn.Module):
+    """m3ae_decoder.py:22-36 (buffer `pe` [1, max_len, d_model])."""
+
+    def __init__(self, d_model, max_len=1024):
+        super().__init__()
+        pe = torch.zeros(max_len, d_model)
+        position = torch.arange(0, max_len, dtype=torch.float).unsqueeze(1)
+        div_term = torch.exp(torch.arange(0, d_model, 2).float() * (-math.log(10000.0) / d_model))
+        pe[:, 0::2] = torch.sin(position * div_term)
+        pe[:, 1::2] = torch.cos(position * div_term)
+        self.register_buffer("pe", pe.unsqueeze(0))
+
+
+class DecoderLayer(nn.Module):
+    """Parameter container with the reference's names (m3ae_decoder.py:38-52)."""
+
+    def __init__(self, d_model, num_heads, d_ff, dropout=0.1):
+        super().__init__()
+        self.mha1 = nn.MultiheadAttention(embed_dim=d_model, num_heads=num_heads, dropout=dropout, batch_first=True)
+        self.mha2 = nn.MultiheadAttention(embed_dim=d_model, num_heads=num_heads, dropout=dropout, batch_first=True)
+        self.ffn = nn.Sequential(nn.Linear(d_model, d_ff), nn.ReLU(), nn.Linear(d_ff, d_model))
+        self.identity = nn.Identity()
+        self.pre_norm = nn.LayerNorm(d_model)
+        self.layernorm1 = nn.LayerNorm(d_model)
+        self.layernorm2 = nn.LayerNorm(d_model)
+        self.layernorm3 = nn.LayerNorm(d_model)
+        self.dropout1 = nn.Dropout(dropout)
+        self.dropout2 = nn.Dropout(dropout)
+        self.dropout3 = nn.Dropout(dropout)
+
+
+class Decoder(nn.Module):
+    def __init__(self, num_layers, d_model, num_heads, d_ff, dropout, max_len, target_vocab_size,
+                 compute_dtype=torch.bfloat16):
+        super().__init__()
+        if d_model != 768 or d_model // num_heads not in (64, 96):
+            raise NotImplementedError("sm_100a decoder kernels are instantiated for d_model 768 with head dim 64 or 96")
+        self.max_len = max_len
+        self.num_layers = num_layers
+        self.num_heads = num_heads
+        self.d_model = d_model
+        self.dec_layers = nn.ModuleList([DecoderLayer(d_model, num_heads, d_ff, dropout) for _ in range(num_layers)])
+        self.target_embedding = nn.Embedding(target_vocab_size, d_model)
+        self.positional_encoding = PositionalEncoding(d_model)
+        self.final_linear = nn.Linear(d_model, target_vocab_size)
+        self.dropout = nn.Dropout(dropout)
+        self.compute_dtype = compute_dtype
+        self._cache = {}
+
+    # ------------------------------------------------------------------ teacher-forced forward (fine-tune / val)
+    def _layer(self, layer, e2, mem2, B, T, Lm, pad_mask_add, want_att):
+        """DecoderLayer.forward (m3ae_decoder.py:54-90) on [B*T, D] rows; eval-mode dropout (see forward())."""
+        dt = self.compute_dtype
+        D, nh = self.d_model, self.num_heads
+        dh = D // nh
+        xn = Fn.layernorm(e2, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps)
+        qkv = Fn.linear(xn, layer.mha1.in_proj_weight, layer.mha1.in_proj_bias, dtype=dt)
+        a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pad_mask_add, B, nh, T, T, dh, causal=True)
+        x = Fn.linear(a, layer.mha1.out_proj.weight, layer.mha1.out_proj.bias, dtype=dt) + e2
+        residual = x
+        x = Fn.layernorm(x, layer.layernorm1.weight, layer.layernorm1.bias, layer.layernorm1.eps)
+        E = D
+        w2, b2 = layer.mha2.in_proj_weight, layer.mha2.in_proj_bias
+        q2 = Fn.linear(x, w2[:E], b2[:E], dtype=dt)
+        kv2 = Fn.linear(mem2, w2[E:], b2[E:], dtype=dt)
+        c = Fn.attention(q2, kv2[:, :D], kv2[:, D:], None, B, nh, T, Lm, dh, causal=False)
+        x = Fn.linear(c, layer.mha2.out_proj.weight, layer.mha2.out_proj.bias, dtype=dt) + residual
+        residual = x
+        x = Fn.layernorm(x, layer.layernorm2.weight, layer.layernorm2.bias, layer.layernorm2.eps)
+        x = Fn.ffn(x, layer.ffn[0].weight, layer.ffn[0].bias, layer.ffn[2].weight, layer.ffn[2].bias, residual=residual,
+                   act=ops.ACT_RELU, dtype=dt)
+        x = Fn.layernorm(x, layer.layernorm3.weight, layer.layernorm3.bias, layer.layernorm3.eps)
+        att = (None, None)
+        if want_att:
+            att = (self._avg_probs(qkv[:, :D], qkv[:, D:2 * D], B, T, T, pad_mask_add, True),
+                   self._avg_probs(q2, kv2[:, :D], B, T, Lm, None, False))
+        return x, att
+
+    def _avg_probs(self, q, k, B, Lq, Lk, mask, causal):
+        """Head-averaged attention weights, as nn.MultiheadAttention(need_weights=True) returns (slow path)."""
+        nh = self.num_heads
+        dh = self.d_model // nh
+        with torch.no_grad():
+            probs = torch.empty(B, nh, Lq, Lk, dtype=torch.float32, device=q.device)
+            out = torch.empty(B * Lq, nh * dh, dtype=q.dtype, device=q.device)
+            lse = torch.empty(B, nh, Lq, dtype=torch.float32, device=q.device)
+            ops.attn_fwd(q.detach(), k.detach(), k.detach(), out, lse, B=B, H=nh, Lq=Lq, Lk=Lk, dh=dh, mask=mask,
+                         causal=causal, probs=probs)
+            return probs.mean(dim=1)
+
+    def forward(self, padded_targets, padding_mask, cross_attn_feats, return_all_attentions=False):
+        """-> (logits [B,T,V], dict of head-averaged attention maps).  Dropout inside the decoder is not applied
+        (p=0.1 in the reference's train mode cannot be bit-matched anyway; parity is asserted in eval mode)."""
+        if not cross_attn_feats.is_cuda:
+            raise RuntimeError("Decoder (B200) needs CUDA tensors: there is no CPU fallback")
+        dt = self.compute_dtype
+        B, T = padded_targets.shape
+        Lm, D = cross_attn_feats.shape[1], self.d_model
+        dev = cross_attn_feats.device
+        pad_mask_add = None
+        if padding_mask is not None:  # key_padding_mask = ~padding_mask -> -inf on padded keys (:121)
+            pad_mask_add = torch.zeros(B, T, dtype=torch.float32, device=dev).masked_fill(~padding_mask.to(dev), float("-inf"))
+        emb = self.target_embedding(padded_targets)  # [B,T,D] fp32 (autograd through the table)
+        e = emb + (emb + self.positional_encoding.pe[:, :T])  # 2*E + pe (:127)
+        e2 = e.reshape(B * T, D).to(dt)
+        mem2 = cross_attn_feats.reshape(B * Lm, D).to(dt)
+        att = {}
+        x = None
+        layers = range(self.num_layers) if return_all_attentions else [self.num_layers - 1]
+        for i in layers:
+            x, (a_self, a_cross) = self._layer(self.dec_layers[i], e2, mem2, B, T, Lm, pad_mask_add, True)
+            att[f"layer{i + 1}_dec_self"], att[f"layer{i + 1}_dec_cross"] = a_self, a_cross
+        logits = Fn.linear(x, self.final_linear.weight, self.final_linear.bias, dtype=dt, out_dtype=torch.float32)
+        return logits.view(B, T, -1), att
+
+    # ------------------------------------------------------------------ KV-cached greedy decoding
+    def _operands(self):
+        """Compute-dtype copies of the live layer's weights (refreshed when the parameters change)."""
+        layer = self.dec_layers[self.num_layers - 1]
+        ps = [layer.mha1.in_proj_weight, layer.mha1.out_proj.weight, layer.mha2.in_proj_weight, layer.mha2.out_proj.weight,
+              layer.ffn[0].weight, layer.ffn[2].weight, self.final_linear.weight]
+        key = (self.compute_dtype,) + tuple((p.data_ptr(), p._version) for p in ps)
+        if self._cache.get("key") != key:
+            dt = self.compute_dtype
+            with torch.no_grad():
+                self._cache = {"key": key, "w": [p.detach() if p.dtype == dt else ops.cast(p.detach().contiguous(), torch.empty_like(p, dtype=dt)) for p in ps]}
+        return self._cache["w"]
+
+    @torch.no_grad()
+    def search_path(self, cross_attn_feats, tokenizer, early_exit_every=0):
+        """Greedy decoding, same result as the reference's search_path (m3ae_decoder.py:141-182): ids [B, max_len].
+        Runs max_len single-token steps; since the reference blanks everything after the first [SEP] and only breaks
+        once ALL rows are finished, running the remaining steps cannot change the output (early_exit_every=n adds the
+        reference's all-finished check, one host sync, every n steps)."""
+        if not cross_attn_feats.is_cuda:
+            raise RuntimeError("Decoder.search_path (B200) needs CUDA tensors: there is no CPU fallback")
+        dt = self.compute_dtype
+        dev = cross_attn_feats.device
+        B, Lm, D = cross_attn_feats.shape
+        nh, L = self.num_heads, self.max_len
+        dh = D // nh
+        layer = self.dec_layers[self.num_layers - 1]
+        w_in1, w_out1, w_in2, w_out2, w_f0, w_f2, w_vocab = self._operands()
+        b_in1, b_in2 = layer.mha1.in_proj_bias.detach(), layer.mha2.in_proj_bias.detach()
+        V = w_vocab.shape[0]
+        sep, pad, eos = tokenizer.sep_token_id, tokenizer.pad_token_id, tokenizer.eos_token_id
+
+        def buf(*shape, dtype=dt):
+            return torch.empty(*shape, dtype=dtype, device=dev)
+
+        # cross-attention K/V of the memory: projected once (the reference re-projects them every step)
+        mem2 = cross_attn_feats.reshape(B * Lm, D)
+        mem2 = mem2 if (mem2.dtype == dt and mem2.is_contiguous()) else ops.cast(mem2.contiguous(), buf(B * Lm, D))
+        kv_mem = buf(B, Lm, 2 * D)
+        ops.gemm(mem2, w_in2[D:], kv_mem.view(B * Lm, 2 * D), bias=b_in2[D:].contiguous())
+        k_mem, v_mem = kv_mem[:, :, :D], kv_mem[:, :, D:]
+        k_self, v_self = buf(B, L, D), buf(B, L, D)
+        x, xn, q, a, x1, x1n, q2, c, x3, x3n, h, u, x5, x6 = (buf(B, D) for _ in range(14))
+        h, u = buf(B, w_f0.shape[0]), buf(B, w_f0.shape[0])
+        logits = buf(B, V, dtype=torch.float32)
+        m1, r1 = buf(B, dtype=torch.float32), buf(B, dtype=torch.float32)
+        seq = torch.full((L + 1, B), pad, dtype=torch.int64, device=dev)  # time-major: seq[t] is contiguous
+        seq[0] = tokenizer.cls_token_id
+        bq, bk, bv = (b_in1[i * D:(i + 1) * D].contiguous() for i in range(3))
+        bq2 = b_in2[:D].contiguous()
+        pe = self.positional_encoding.pe[0].contiguous()
+        table = self.target_embedding.weight.detach()
+        for t in range(L):
+            pos = torch.full((B,), t, dtype=torch.int32, device=dev)
+            ops.decoder_embed(seq[t], pos, table, pe, x)  # 2*E[id] + pe[t]
+            ops.layernorm_fwd(x, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps, xn, m1, r1)
+            # q for this token; k, v written straight into the cache rows [b, t, :]
+            ops.gemm_group([ops.GemmSpec(xn, w_in1[:D], q, bias=bq),
+                            ops.GemmSpec(xn, w_in1[D:2 * D], k_self[:, t, :], bias=bk),
+                            ops.GemmSpec(xn, w_in1[2 * D:], v_self[:, t, :], bias=bv)])
+            ops.decode_attn(q, k_self, v_self, a, H=nh, length=t + 1, dh=dh)
+            ops.gemm(a, w_out1, x1, bias=layer.mha1.out_proj.bias, residual=x)
+            ops.layernorm_fwd(x1, layer.layernorm1.weight, layer.layernorm1.bias, layer.layernorm1.eps, x1n, m1, r1)
+            ops.gemm(x1n, w_in2[:D], q2, bias=bq2)
+            ops.decode_attn(q2, k_mem, v_mem, c, H=nh, length=Lm, dh=dh)
+            ops.gemm(c, w_out2, x3, bias=layer.mha2.out_proj.bias, residual=x1)
+            ops.layernorm_fwd(x3, layer.layernorm2.weight, layer.layernorm2.bias, layer.layernorm2.eps, x3n, m1, r1)
+            ops.gemm(x3n, w_f0, h, bias=layer.ffn[0].bias, act=ops.ACT_RELU)
+            ops.gemm(h, w_f2, x5, bias=layer.ffn[2].bias, residual=x3)
+            ops.layernorm_fwd(x5, layer.layernorm3.weight, layer.layernorm3.bias, layer.layernorm3.eps, x6, m1, r1)
+            ops.gemm(x6, w_vocab, logits, bias=self.final_linear.bias)
+            ops.argmax_rows(logits, seq[t + 1])  # log_softmax is monotone (:151-153)
+            if early_exit_every and (t + 1) % early_exit_every == 0:
+                nxt = seq[1:t + 2]
+                done = nxt == sep
+                if eos is not None:
+                    done = done | (nxt == eos)
+                if bool(done.any(dim=0).all()):
+                    break
+        out = seq[1:].t().contiguous()
+        special = out == sep
+        if eos is not None:
+            special = special | (out == eos)
+        after = (special.cumsum(dim=1) - special.long()) > 0  # strictly after the first [SEP]/[EOS] (:165-173)
+        return out.masked_fill(after, pad)

@@ -1,0 +1,123 @@
+"""Generative decoder head on the CUDA path vs the oracle restatement of the reference Decoder and vs golden vectors
+from the unmodified reference (tests/golden/decoder.pt)."""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import m3ae_b200  # noqa: E402,F401
+from m3ae_b200.decoder import Decoder  # noqa: E402
+from oracle import m3ae_oracle as O  # noqa: E402
+from oracle import make_golden as G  # noqa: E402
+
+DEV = "cuda"
+GOLD = os.path.join(ROOT, "tests", "golden", "decoder.pt")
+
+
+def rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def make_decoder(sd, dtype, max_len=16):
+    d = Decoder(6, 768, 8, 3072, 0.1, max_len, 30522, compute_dtype=dtype)
+    d.load_state_dict(sd, strict=True)
+    return d.to(DEV).eval()
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+def test_teacher_forced_logits_match_oracle_and_golden(dtype, tol):
+    gold = torch.load(GOLD)
+    sd = O.make_decoder_state(31)
+    mem, ids, pm = G.decoder_inputs(32, B=4, T=9)
+    with torch.no_grad():
+        ref, att_ref = O.decoder_forward(ids, pm, mem, sd)
+    dec = make_decoder(sd, dtype)
+    logits, att = dec(ids.to(DEV), pm.to(DEV), mem.to(DEV))
+    assert logits.shape == ref.shape and logits.dtype == torch.float32
+    assert rel(logits, ref) < tol, f"logits: {rel(logits, ref):.3e}"
+    assert rel(logits[:, :, ::16], gold["logits_sub"]) < tol
+    assert rel(att["layer6_dec_self"], att_ref["layer6_dec_self"]) < tol
+    assert rel(att["layer6_dec_cross"], att_ref["layer6_dec_cross"]) < tol
+    if dtype == torch.float32:
+        assert torch.equal(logits.argmax(-1).cpu(), gold["argmax"])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_teacher_forced_backward_matches_oracle(dtype):
+    tol = 1e-4 if dtype == torch.float32 else 3e-2
+    sd = O.make_decoder_state(31)
+    mem, ids, pm = G.decoder_inputs(33, B=3, T=7)
+    tgt = torch.randint(0, 30522, (3, 7), generator=torch.Generator().manual_seed(1))
+    sdo = {k: v.clone().requires_grad_(v.dtype.is_floating_point and k != "positional_encoding.pe") for k, v in sd.items()}
+    mo = mem.clone().requires_grad_(True)
+    lo, _ = O.decoder_forward(ids, pm, mo, sdo)
+    torch.nn.functional.cross_entropy(lo.reshape(-1, lo.shape[-1]), tgt.reshape(-1)).backward()
+    dec = make_decoder(sd, dtype).train()
+    mc = mem.to(DEV).requires_grad_(True)
+    lc, _ = dec(ids.to(DEV), pm.to(DEV), mc)
+    torch.nn.functional.cross_entropy(lc.reshape(-1, lc.shape[-1]), tgt.to(DEV).reshape(-1)).backward()
+    assert rel(mc.grad, mo.grad) < tol, f"d memory: {rel(mc.grad, mo.grad):.3e}"
+    live = "dec_layers.5."
+    for k, p in dec.named_parameters():
+        if k.startswith("dec_layers.") and not k.startswith(live):
+            assert p.grad is None, f"{k}: dead layers must receive no gradient"
+            continue
+        if k.endswith("mha1.in_proj_bias") or k.endswith("mha2.in_proj_bias"):
+            # the key-bias third of the packed bias has an identically zero gradient: compare q and v parts
+            g, go = p.grad.view(3, -1), sdo[k].grad.view(3, -1)
+            assert rel(g[0], go[0]) < tol and rel(g[2], go[2]) < tol, k
+            continue
+        assert rel(p.grad, sdo[k].grad) < tol, f"{k}: {rel(p.grad, sdo[k].grad):.3e}"
+
+
+class Tok:
+    cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_greedy_kv_cached_ids_match_reference_golden(dtype):
+    gold = torch.load(GOLD)
+    sd = O.make_decoder_state(31)
+    mem, _, _ = G.decoder_inputs(32, B=4, T=9)
+    dec = make_decoder(sd, dtype)
+    ids = dec.search_path(mem.to(DEV), Tok).cpu()
+    assert ids.shape == (4, 16) and ids.dtype == torch.int64
+    if dtype == torch.float32:
+        assert torch.equal(ids, gold["greedy"])
+    else:  # bf16: a near-tie may flip one argmax; once a token differs the suffix diverges, so compare prefixes
+        assert (ids[:, 0] == gold["greedy"][:, 0]).all()
+    sd2 = dict(sd)
+    sd2["final_linear.bias"] = sd["final_linear.bias"].clone()
+    sd2["final_linear.bias"][102] += 4.0
+    dec2 = make_decoder(sd2, dtype)
+    ids2 = dec2.search_path(mem.to(DEV), Tok).cpu()
+    ids3 = dec2.search_path(mem.to(DEV), Tok, early_exit_every=2).cpu()
+    if dtype == torch.float32:
+        assert torch.equal(ids2, gold["greedy_sep"])
+    assert torch.equal(ids2, ids3), "the all-finished early exit must not change the result"
+
+
+def test_greedy_batch128_matches_oracle_fp32_and_bf16_agreement():
+    """BASELINE config 3 shape: B=128 memories of 359 tokens, up to 16 tokens.  fp32 CUDA path must reproduce the oracle's
+    ids exactly; the bf16 path is reported as per-sample agreement (north_star: >= 99.9% identical greedy IDs is
+    the target for trained weights; with random-init weights logit gaps are tiny, so the bf16 figure is informational)."""
+    sd = O.make_decoder_state(41, live_only=True)
+    full = O.make_decoder_state(41)
+    g = torch.Generator().manual_seed(5)
+    mem = torch.randn(128, 359, 768, generator=g)
+    with torch.no_grad():
+        ref = O.search_path(mem[:16], sd, 16)
+    dec = make_decoder(full, torch.float32)
+    ids = dec.search_path(mem.to(DEV), Tok).cpu()
+    assert torch.equal(ids[:16], ref)
+    dec16 = make_decoder(full, torch.bfloat16)
+    ids16 = dec16.search_path(mem.to(DEV), Tok).cpu()
+    agree = (ids16 == ids).all(dim=1).float().mean().item()
+    first = (ids16[:, 0] == ids[:, 0]).float().mean().item()
+    print(f"bf16 vs fp32 greedy: identical sequences {agree:.3f}, identical first token {first:.3f}")
+    assert first > 0.9
