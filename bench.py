@@ -127,12 +127,16 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_ms = [0.0]
+
     def timed(fn, n):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        t0 = time.perf_counter()
         for i in range(n):
             fn(i)
+        host_ms[0] = (time.perf_counter() - t0) * 1e3 / n  # CPU time to ISSUE a step (launch-bound if ~ ms/step)
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -151,6 +155,7 @@ def run_ours(args):
         sampler.start()
     l0 = ops.launch_count()
     ms = timed(lambda i: step(batches[i % 2]), args.steps)
+    host_issue_ms = host_ms[0]
     launches = ops.launch_count() - l0
     # ---- end-to-end: pinned host inputs -> H2D -> step -> loss D2H, every step
     host = [synth_batch(B, dev, 2000 + rank * 100 + i, pin=True) for i in range(2)]
@@ -212,7 +217,7 @@ def run_ours(args):
             "clocks": sampler.summary() if sampler else None,
             "e2e": {"value": round(sps_e2e, 2), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches), "host_issue_ms_per_step": round(host_issue_ms, 3),
             "roofline": {"bound": "tensor", "achieved": round(achieved, 1) if achieved else None, "peak": pk["tflops"], "unit": "TFLOP/s",
                          "frac": round(achieved / pk["tflops"], 4) if achieved else None, "traffic": None,
                          "kernel": "gemm_tcgen05_kernel", "launches_per_step": gemm_n, "peak_source": pk["source"],

@@ -74,14 +74,24 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
 // Branch-free GELU for the bf16 tensor-core epilogue: erfc(|z|) ~ poly(t) exp(-z^2), t = 1/(1+p|z|)
 // (Abramowitz-Stegun 7.1.26, |abs err| < 1.5e-7 — far below bf16 resolution).  ~16 instructions, 2 MUFU.
 // The fp32 parity path keeps erff().  fast_gelu_terms returns (cdf, pdf) of the standard normal at x.
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ void fast_gelu_terms(float x, float& cdf, float& pdf) {
   const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
   float poly = fmaf(1.061405429f, t, -1.453152027f);
   poly = fmaf(poly, t, 1.421413741f);
   poly = fmaf(poly, t, -0.284496736f);
   poly = fmaf(poly, t, 0.254829592f);
-  const float e = exp2f(z * z * -1.4426950408889634f);  // exp(-x^2/2)
+  const float e = ex2_approx(z * z * -1.4426950408889634f);  // exp(-x^2/2)
   const float half_erfc = 0.5f * poly * t * e;           // 0.5*erfc(|z|)
   cdf = x >= 0.f ? 1.0f - half_erfc : half_erfc;
   pdf = 0.39894228040143268f * e;

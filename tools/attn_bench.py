@@ -1,0 +1,33 @@
+"""Times the attention kernels at the fusion-stack shapes (B=64, 12 heads x 64). Usage: python tools/attn_bench.py"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from m3ae_b200 import ops
+dev = "cuda"
+B, H, dh = int(os.environ.get("B", "64")), 12, 64
+reps = int(os.environ.get("REPS", "10"))
+def run(Lq, Lk, drop=0.0):
+    q = torch.randn(B * Lq, 3 * H * dh, device=dev).to(torch.bfloat16)
+    kv = torch.randn(B * Lk, 3 * H * dh, device=dev).to(torch.bfloat16)
+    Q, K, V = q[:, :768], kv[:, 768:1536], kv[:, 1536:]
+    out = torch.empty(B * Lq, 768, device=dev, dtype=torch.bfloat16)
+    lse = torch.empty(B, H, Lq, device=dev)
+    dout = torch.randn_like(out)
+    dq = torch.empty_like(q); dkv = torch.empty_like(kv)
+    delta = torch.empty(B, H, Lq, device=dev)
+    kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, drop_p=drop, drop_seed=1, drop_stream=0)
+    def f(): ops.attn_fwd(Q, K, V, out, lse, **kw)
+    def b(): ops.attn_bwd(Q, K, V, out, lse, dout=dout, dq=dq[:, :768], dk=dkv[:, 768:1536], dv=dkv[:, 1536:], delta=delta, **kw)
+    for name, fn, mult in (("fwd", f, 4), ("bwd", b, 10)):
+        for _ in range(2): fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps): fn()
+        e1.record(); torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / reps
+        flops = mult * B * H * Lq * Lk * dh
+        print(f"attn {name} Lq={Lq:4d} Lk={Lk:4d} drop={drop}: {us:8.1f} us  {flops / us / 1e6:7.1f} TFLOP/s (algorithmic {mult}*B*H*Lq*Lk*dh)")
+for (Lq, Lk) in [(325, 325), (325, 32), (32, 325), (32, 32)]:
+    for drop in (0.0, 0.1):
+        run(Lq, Lk, drop)

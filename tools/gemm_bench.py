@@ -14,7 +14,13 @@ bf = torch.bfloat16
 def t(*s, dtype=bf):
     return (torch.randn(*s, device=dev) * 0.05).to(dtype)
 
-def bench(name, mk_specs, reps=20):
+ONLY = os.environ.get("ONLY", "")
+REPS = int(os.environ.get("REPS", "20"))
+
+def bench(name, mk_specs, reps=None):
+    if ONLY and ONLY not in name:
+        return
+    reps = reps or REPS
     specs = mk_specs()
     flops = sum(2.0 * s.problem.M * s.problem.N * s.problem.K for s in specs)
     for _ in range(3):
@@ -56,6 +62,8 @@ for which in (["i"], ["t"], ["t", "i"]):
 # big square reference point
 a, b = t(8192, 8192), t(8192, 8192)
 bench("8192^3 plain bf16 out", lambda: [ops.GemmSpec(a, b, out(8192, 8192))], reps=5)
+if ONLY:
+    sys.exit(0)
 c = torch.empty(8192, 8192, device=dev, dtype=bf)
 torch.matmul(a, b.t(), out=c); torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
