@@ -135,6 +135,9 @@ typedef struct m3ae_attn_params_t {
   void* dv;
   int64_t lddq, lddk, lddv;
   float* delta;      /* workspace [B,H,Lq] fp32: rowsum(dO*O) */
+  /* optional dropout keep-bit cache [B,H,Lq, 8*ceil(Lk/64)] bytes (bit k%8 of byte k/8 = key k kept): the tensor-core
+   * forward writes it, the tensor-core backward reads it instead of re-evaluating Philox.  NULL: bits are recomputed. */
+  uint8_t* drop_mask;
 } m3ae_attn_params_t;
 
 int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream);

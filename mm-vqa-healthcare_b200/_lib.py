@@ -48,7 +48,7 @@ class AttnParams(C.Structure):
         ("dtype", C.c_int32),
         ("dout", C.c_void_p), ("dq", C.c_void_p), ("dk", C.c_void_p), ("dv", C.c_void_p),
         ("lddq", C.c_int64), ("lddk", C.c_int64), ("lddv", C.c_int64),
-        ("delta", C.c_void_p),
+        ("delta", C.c_void_p), ("drop_mask", C.c_void_p),
     ]
 
 

@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const m3ae_attn_params_t 
 #pragma unroll
     for (int i = 0; i < ND; ++i) o[r][i] = 0.f;
   }
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
 
   for (int k0 = 0; k0 < P.Lk; k0 += KC) {
     __syncthreads();
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(128) attn_probs_kernel(const m3ae_attn_params_
   const T* __restrict__ Q = (const T*)P.q + (size_t)(b * P.Lq + qi) * P.ldq + (size_t)h * DH;
   const T* __restrict__ K = (const T*)P.k + (size_t)b * P.Lk * P.ldk + (size_t)h * DH;
   const float lse = P.lse[((size_t)b * P.H + h) * P.Lq + qi];
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
   float* out = P.probs + (((size_t)b * P.H + h) * P.Lq + qi) * (size_t)P.Lk;
   for (int key = lane; key < P.Lk; key += 32) {
     float s = 0.f;
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params
 #pragma unroll
     for (int i = 0; i < ND; ++i) dq[r][i] = 0.f;
   }
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
   for (int k0 = 0; k0 < P.Lk; k0 += KC) {
     __syncthreads();
     for (int idx = threadIdx.x; idx < KC * DH; idx += 128) {
@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const m3ae_attn_param
 #pragma unroll
     for (int i = 0; i < ND; ++i) { dk[r][i] = 0.f; dv[r][i] = 0.f; }
   }
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
   for (int i0 = 0; i0 < P.Lq; i0 += KC) {
     __syncthreads();
     for (int idx = threadIdx.x; idx < KC * DH; idx += 128) {

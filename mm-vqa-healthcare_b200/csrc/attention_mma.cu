@@ -71,10 +71,32 @@ __device__ __forceinline__ float quad_sum(float v) {
   return v + __shfl_xor_sync(0xffffffffu, v, 2);
 }
 
-// keep-mask bits for keys (key, key+1), key even, of attention row `row_lin`
-__device__ __forceinline__ uint32_t keep_pair(const m3ae_attn_params_t& P, uint64_t row_lin, int key) {
-  const uint32_t m4 = attn_dropout_keep4(P.drop_seed, P.drop_stream, row_lin, key, P.drop_p);
-  return (m4 >> (key & 2)) & 3u;
+// ---- dropout keep-bit tiles: sBits[row] holds 64 bits = keys k0..k0+63 of attention row (q0+row).
+// Forward generates the tile cooperatively (one Philox evaluation per 8 keys) and stores it to the global bit cache;
+// backward kernels load it back.  Without a cache (drop_mask == NULL) every kernel regenerates the tile.
+template <int ROWS, int NT>
+__device__ __forceinline__ void gen_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
+  const uint32_t thr = drop_thr16(P.drop_p);
+  uint8_t* sb = reinterpret_cast<uint8_t*>(sBits);
+  for (int i = tid; i < ROWS * 8; i += NT) {
+    const int r = i >> 3, grp = i & 7;
+    const uint64_t row_lin = ((uint64_t)b * P.H + h) * P.Lq + (row0 + r);
+    sb[r * 8 + grp] = (uint8_t)attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, (k0 >> 3) + grp, thr);
+  }
+}
+__device__ __forceinline__ int64_t mask_ld_bytes(const m3ae_attn_params_t& P) { return 8 * (int64_t)((P.Lk + 63) / 64); }
+template <int ROWS, int NT>
+__device__ __forceinline__ void store_keep_tile(const uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
+  // call after a __syncthreads following gen_keep_tile
+  uint8_t* base = P.drop_mask + (((int64_t)b * P.H + h) * P.Lq) * mask_ld_bytes(P);
+  for (int r = tid; r < ROWS; r += NT)
+    if (row0 + r < P.Lq) *reinterpret_cast<uint64_t*>(base + (int64_t)(row0 + r) * mask_ld_bytes(P) + (k0 >> 3)) = sBits[r];
+}
+template <int ROWS, int NT>
+__device__ __forceinline__ void load_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
+  const uint8_t* base = P.drop_mask + (((int64_t)b * P.H + h) * P.Lq) * mask_ld_bytes(P);
+  for (int r = tid; r < ROWS; r += NT)
+    sBits[r] = (row0 + r < P.Lq) ? *reinterpret_cast<const uint64_t*>(base + (int64_t)(row0 + r) * mask_ld_bytes(P) + (k0 >> 3)) : 0ull;
 }
 
 // ------------------------------------------------------------------------------------------------ forward
@@ -85,12 +107,14 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
   __shared__ __align__(16) bf16 sK[BN][LDS];
   __shared__ __align__(16) bf16 sV[BN][LDS];
   __shared__ float sMask[BN];
+  __shared__ uint64_t sBits[BM];
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * BM;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const bf16* __restrict__ Q = (const bf16*)P.q + (int64_t)b * P.Lq * P.ldq + h * D;
   const bf16* __restrict__ K = (const bf16*)P.k + (int64_t)b * P.Lk * P.ldk + h * D;
   const bf16* __restrict__ V = (const bf16*)P.v + (int64_t)b * P.Lk * P.ldv + h * D;
   const float* __restrict__ mask = P.mask ? P.mask + (int64_t)b * P.Lk : nullptr;
+  const bool drop = P.drop_p > 0.f;
 
   load_tile<BM, NT>(sQ, Q, P.ldq, q0, P.Lq, tid);
   __syncthreads();
@@ -102,15 +126,16 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
   for (int j = 0; j < 8; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
   const int qi0 = q0 + warp * 16 + g, qi1 = qi0 + 8;
-  const uint64_t rl0 = ((uint64_t)b * P.H + h) * P.Lq + qi0, rl1 = rl0 + 8;
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
 
   for (int k0 = 0; k0 < P.Lk; k0 += BN) {
     __syncthreads();
     load_tile<BN, NT>(sK, K, P.ldk, k0, P.Lk, tid);
     load_tile<BN, NT>(sV, V, P.ldv, k0, P.Lk, tid);
     for (int i = tid; i < BN; i += NT) sMask[i] = (k0 + i < P.Lk) ? (mask ? mask[k0 + i] : 0.f) : -INFINITY;
+    if (drop) gen_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
     __syncthreads();
+    if (drop && P.drop_mask) store_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
 
     float s[8][4];
 #pragma unroll
@@ -157,11 +182,11 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
     l1 = l1 * c1 + ps1;
 #pragma unroll
     for (int j = 0; j < 8; ++j) { o[j][0] *= c0; o[j][1] *= c0; o[j][2] *= c1; o[j][3] *= c1; }
-    if (P.drop_p > 0.f) {
+    if (drop) {
+      const uint64_t bits0 = sBits[warp * 16 + g] >> (2 * t), bits1 = sBits[warp * 16 + g + 8] >> (2 * t);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int key = k0 + j * 8 + 2 * t;
-        const uint32_t ka = keep_pair(P, rl0, key), kb = keep_pair(P, rl1, key);
+        const uint32_t ka = (uint32_t)(bits0 >> (8 * j)) & 3u, kb = (uint32_t)(bits1 >> (8 * j)) & 3u;
         s[j][0] = (ka & 1) ? s[j][0] * keep_scale : 0.f; s[j][1] = (ka & 2) ? s[j][1] * keep_scale : 0.f;
         s[j][2] = (kb & 1) ? s[j][2] * keep_scale : 0.f; s[j][3] = (kb & 2) ? s[j][3] * keep_scale : 0.f;
       }
@@ -216,6 +241,8 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
   __shared__ __align__(16) bf16 sK[BN][LDS];
   __shared__ __align__(16) bf16 sV[BN][LDS];
   __shared__ float sMask[BN];
+  __shared__ uint64_t sBits[BM];
+  const bool drop = P.drop_p > 0.f;
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * BM;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const bf16* __restrict__ Q = (const bf16*)P.q + (int64_t)b * P.Lq * P.ldq + h * D;
@@ -233,8 +260,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
   const int64_t sbase = ((int64_t)b * P.H + h) * P.Lq;
   const float lse0 = P.lse[sbase + min(qi0, P.Lq - 1)], lse1 = P.lse[sbase + min(qi1, P.Lq - 1)];
   const float dl0 = P.delta[sbase + min(qi0, P.Lq - 1)], dl1 = P.delta[sbase + min(qi1, P.Lq - 1)];
-  const uint64_t rl0 = (uint64_t)sbase + qi0, rl1 = rl0 + 8;
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
   float dq[8][4];
 #pragma unroll
   for (int j = 0; j < 8; ++j) dq[j][0] = dq[j][1] = dq[j][2] = dq[j][3] = 0.f;
@@ -244,7 +270,12 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
     load_tile<BN, NT>(sK, K, P.ldk, k0, P.Lk, tid);
     load_tile<BN, NT>(sV, V, P.ldv, k0, P.Lk, tid);
     for (int i = tid; i < BN; i += NT) sMask[i] = (k0 + i < P.Lk) ? (mask ? mask[k0 + i] : 0.f) : -INFINITY;
+    if (drop) {
+      if (P.drop_mask) load_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
+      else gen_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
+    }
     __syncthreads();
+    const uint64_t bits0 = drop ? sBits[warp * 16 + g] >> (2 * t) : 0ull, bits1 = drop ? sBits[warp * 16 + g + 8] >> (2 * t) : 0ull;
     float s[8][4], dp[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -277,8 +308,8 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
         if (key + 1 > qi1) p3 = 0.f;
       }
       float d0 = dp[j][0], d1 = dp[j][1], d2 = dp[j][2], d3 = dp[j][3];
-      if (P.drop_p > 0.f) {
-        const uint32_t ka = keep_pair(P, rl0, key), kb = keep_pair(P, rl1, key);
+      if (drop) {
+        const uint32_t ka = (uint32_t)(bits0 >> (8 * j)) & 3u, kb = (uint32_t)(bits1 >> (8 * j)) & 3u;
         d0 = (ka & 1) ? d0 * keep_scale : 0.f; d1 = (ka & 2) ? d1 * keep_scale : 0.f;
         d2 = (kb & 1) ? d2 * keep_scale : 0.f; d3 = (kb & 2) ? d3 * keep_scale : 0.f;
       }
@@ -327,6 +358,8 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
   __shared__ __align__(16) bf16 sQ[BN][LDS];
   __shared__ __align__(16) bf16 sdO[BN][LDS];
   __shared__ float sLse[BN], sDl[BN];
+  __shared__ uint64_t sBits[BN];  // [query in tile] -> keep bits of the 64-key group containing this CTA's keys
+  const bool drop = P.drop_p > 0.f;
   const int b = blockIdx.z, h = blockIdx.y, kb0 = blockIdx.x * BM;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const bf16* __restrict__ Q = (const bf16*)P.q + (int64_t)b * P.Lq * P.ldq + h * D;
@@ -343,7 +376,9 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
   const float* mrow = P.mask ? P.mask + (int64_t)b * P.Lk : nullptr;
   const float ma0 = (mrow && key0 < P.Lk) ? mrow[key0] : 0.f, ma1 = (mrow && key1 < P.Lk) ? mrow[key1] : 0.f;
   const int64_t sbase = ((int64_t)b * P.H + h) * P.Lq;
-  const float keep_scale = P.drop_p > 0.f ? 1.0f / (1.0f - P.drop_p) : 1.0f;
+  const float keep_scale = drop_keep_scale(P.drop_p);
+  const int kgrp0 = kb0 & ~63;                       // 64-key group start
+  const int kl0 = (kb0 - kgrp0) + warp * 16 + g, kl1 = kl0 + 8;  // bit positions of this thread's two keys
   float dk[8][4], dv[8][4];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -358,6 +393,10 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
       const bool ok = i0 + i < P.Lq;
       sLse[i] = ok ? P.lse[sbase + i0 + i] : INFINITY;  // exp(s - inf) = 0 for padded queries
       sDl[i] = ok ? P.delta[sbase + i0 + i] : 0.f;
+    }
+    if (drop) {
+      if (P.drop_mask) load_keep_tile<BN, NT>(sBits, P, b, h, i0, kgrp0, tid);
+      else gen_keep_tile<BN, NT>(sBits, P, b, h, i0, kgrp0, tid);
     }
     __syncthreads();
     float s[8][4], dp[8][4];  // S^T[key][query], dP^T[key][query]
@@ -393,11 +432,9 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
       }
       float d0 = dp[j][0], d1 = dp[j][1], d2 = dp[j][2], d3 = dp[j][3];
       float e0 = p0, e1 = p1, e2 = p2, e3 = p3;  // P' (dropped) for dV
-      if (P.drop_p > 0.f) {
-        const bool k00 = attn_dropout_keep(P.drop_seed, P.drop_stream, (uint64_t)sbase + qa_, key0, P.drop_p);
-        const bool k01 = attn_dropout_keep(P.drop_seed, P.drop_stream, (uint64_t)sbase + qb_, key0, P.drop_p);
-        const bool k10 = attn_dropout_keep(P.drop_seed, P.drop_stream, (uint64_t)sbase + qa_, key1, P.drop_p);
-        const bool k11 = attn_dropout_keep(P.drop_seed, P.drop_stream, (uint64_t)sbase + qb_, key1, P.drop_p);
+      if (drop) {
+        const uint64_t ba = sBits[c], bb_ = sBits[c + 1];
+        const bool k00 = (ba >> kl0) & 1ull, k01 = (bb_ >> kl0) & 1ull, k10 = (ba >> kl1) & 1ull, k11 = (bb_ >> kl1) & 1ull;
         d0 = k00 ? d0 * keep_scale : 0.f; d1 = k01 ? d1 * keep_scale : 0.f;
         d2 = k10 ? d2 * keep_scale : 0.f; d3 = k11 ? d3 * keep_scale : 0.f;
         e0 = k00 ? p0 * keep_scale : 0.f; e1 = k01 ? p1 * keep_scale : 0.f;

@@ -148,21 +148,27 @@ __device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream
   return m;
 }
 
-// Attention-probability dropout: element (row_lin = (b*H+h)*Lq+i, key) -> Philox counter (row_lin, stream | key/4),
-// lane key%4, so the two adjacent keys a tensor-core accumulator fragment holds share one Philox evaluation.
-__device__ __forceinline__ uint32_t attn_dropout_keep4(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key, float p) {
+// Attention-probability dropout.  Element (row_lin = (b*H+h)*Lq+i, key) takes the 16-bit lane key%8 of the Philox
+// evaluation with counter (row_lin, site<<32 | key/8): one evaluation covers 8 consecutive keys of a row.  The drop
+// threshold is p quantised to 1/65536 and the keep scale uses the quantised rate, so every kernel (tensor-core tiles
+// that generate 64x64 bit tiles cooperatively, generic per-element kernels) sees exactly the same mask and scale.
+__device__ __forceinline__ uint32_t drop_thr16(float p) { return (uint32_t)(p * 65536.0f + 0.5f); }
+__device__ __forceinline__ float drop_keep_scale(float p) {
+  return p > 0.f ? 65536.0f / (65536.0f - (float)drop_thr16(p)) : 1.0f;
+}
+// keep bits for keys 8*key_group .. 8*key_group+7 of one attention row
+__device__ __forceinline__ uint32_t attn_keep_bits8(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key_group, uint32_t thr16) {
   Philox ph(seed);
-  const uint4 r = ph(row_lin, (stream_id << 32) | (uint64_t)(uint32_t)(key >> 2));
-  const float s = 1.0f / 16777216.0f;
+  const uint4 r = ph(row_lin, (stream_id << 32) | (uint64_t)(uint32_t)key_group);
   uint32_t m = 0;
-  m |= ((float)(r.x >> 8) * s >= p) ? 1u : 0u;
-  m |= ((float)(r.y >> 8) * s >= p) ? 2u : 0u;
-  m |= ((float)(r.z >> 8) * s >= p) ? 4u : 0u;
-  m |= ((float)(r.w >> 8) * s >= p) ? 8u : 0u;
+  m |= ((r.x & 0xFFFFu) >= thr16) ? 1u : 0u;   m |= ((r.x >> 16) >= thr16) ? 2u : 0u;
+  m |= ((r.y & 0xFFFFu) >= thr16) ? 4u : 0u;   m |= ((r.y >> 16) >= thr16) ? 8u : 0u;
+  m |= ((r.z & 0xFFFFu) >= thr16) ? 16u : 0u;  m |= ((r.z >> 16) >= thr16) ? 32u : 0u;
+  m |= ((r.w & 0xFFFFu) >= thr16) ? 64u : 0u;  m |= ((r.w >> 16) >= thr16) ? 128u : 0u;
   return m;
 }
 __device__ __forceinline__ bool attn_dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key, float p) {
-  return (attn_dropout_keep4(seed, stream_id, row_lin, key, p) >> (key & 3)) & 1u;
+  return (attn_keep_bits8(seed, stream_id, row_lin, key >> 3, drop_thr16(p)) >> (key & 7)) & 1u;
 }
 
 // ---------------------------------------------------------------- warp helpers

@@ -157,6 +157,12 @@ def _forward_streams(cfg, training, streams, want_probs):
     def f32(st, *shape):
         return torch.empty(*shape, dtype=torch.float32, device=st.x.device)
 
+    def keep_bits(st, Lq, Lk):
+        """dropout keep-bit cache of one attention site: written by the forward kernel, read by the backward kernels."""
+        if pa <= 0.0 or dt != torch.bfloat16:
+            return None
+        return torch.empty(st.B * nh * Lq * ops.drop_mask_ld(Lk), dtype=torch.uint8, device=st.x.device)
+
     # 1. fused QKV projection
     for st in S:
         st.qkv = new(st, st.M, 3 * st.H)
@@ -167,8 +173,10 @@ def _forward_streams(cfg, training, streams, want_probs):
         st.ctx = new(st, st.M, H)
         st.lse1 = f32(st, st.B, nh, st.Lq)
         st.probs1 = f32(st, st.B, nh, st.Lq, st.Lq) if want_probs else None
+        st.dm1 = keep_bits(st, st.Lq, st.Lq)
         ops.attn_fwd(st.qkv[:, :H], st.qkv[:, H:2 * H], st.qkv[:, 2 * H:], st.ctx, st.lse1, B=st.B, H=nh, Lq=st.Lq,
-                     Lk=st.Lq, dh=st.dh, mask=st.mask, probs=st.probs1, drop_p=pa, drop_seed=st.seed, drop_stream=0)
+                     Lk=st.Lq, dh=st.dh, mask=st.mask, probs=st.probs1, drop_p=pa, drop_seed=st.seed, drop_stream=0,
+                     drop_mask=st.dm1)
     # 3. out-proj + dropout + residual, 4. LayerNorm
     for st in S:
         st.h1 = new(st, st.M, st.H)
@@ -190,8 +198,9 @@ def _forward_streams(cfg, training, streams, want_probs):
         st.ctx2 = new(st, st.M, H)
         st.lse2 = f32(st, st.B, nh, st.Lq)
         st.probs2 = f32(st, st.B, nh, st.Lq, st.Lk) if want_probs else None
+        st.dm2 = keep_bits(st, st.Lq, st.Lk)
         ops.attn_fwd(st.qc, st.kvc[:, :H], st.kvc[:, H:], st.ctx2, st.lse2, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lk, dh=st.dh,
-                     mask=st.enc_mask, probs=st.probs2, drop_p=pa, drop_seed=st.seed, drop_stream=2)
+                     mask=st.enc_mask, probs=st.probs2, drop_p=pa, drop_seed=st.seed, drop_stream=2, drop_mask=st.dm2)
     # 7/8. cross out-proj + residual, LayerNorm
     for st in S:
         st.h2 = new(st, st.M, st.H)
@@ -280,7 +289,7 @@ def _backward_streams(cfg, S, douts):
         delta = torch.empty(st.B, nh, st.Lq, dtype=torch.float32, device=dev)
         ops.attn_bwd(st.qc, st.kvc[:, :H], st.kvc[:, H:], st.ctx2, st.lse2, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lk, dh=st.dh,
                      mask=st.enc_mask, drop_p=st.pa, drop_seed=st.seed, drop_stream=2, dout=st.dctx2, dq=st.dqc,
-                     dk=st.dkvc[:, :H], dv=st.dkvc[:, H:], delta=delta)
+                     dk=st.dkvc[:, :H], dv=st.dkvc[:, H:], delta=delta, drop_mask=st.dm2)
         st.g_[BQ2] = ops.colsum(st.dqc, st.gb["bq2"])
         bkv = ops.colsum(st.dkvc, st.gb["bkv2"])
         st.g_[BK2], st.g_[BV2] = bkv[:H], bkv[H:]
@@ -308,7 +317,7 @@ def _backward_streams(cfg, S, douts):
         delta = torch.empty(st.B, nh, st.Lq, dtype=torch.float32, device=dev)
         ops.attn_bwd(st.qkv[:, :H], st.qkv[:, H:2 * H], st.qkv[:, 2 * H:], st.ctx, st.lse1, B=st.B, H=nh, Lq=st.Lq, Lk=st.Lq,
                      dh=st.dh, mask=st.mask, drop_p=st.pa, drop_seed=st.seed, drop_stream=0, dout=st.dctx,
-                     dq=st.dqkv[:, :H], dk=st.dqkv[:, H:2 * H], dv=st.dqkv[:, 2 * H:], delta=delta)
+                     dq=st.dqkv[:, :H], dk=st.dqkv[:, H:2 * H], dv=st.dqkv[:, 2 * H:], delta=delta, drop_mask=st.dm1)
         bq = ops.colsum(st.dqkv, st.gb["bqkv"])
         st.g_[BQ], st.g_[BK], st.g_[BV] = bq[:H], bq[H:2 * H], bq[2 * H:]
         st.dx = new(st.M, H)
@@ -433,7 +442,13 @@ class _LinearFn(torch.autograd.Function):
         N = wc.shape[0]
         dev = dy.device
         d2 = dy.reshape(M, N)
-        dyc = d2 if (d2.dtype == dtype and d2.is_contiguous()) else ops.cast(d2.contiguous(), torch.empty(M, N, dtype=dtype, device=dev))
+        if dtype == torch.bfloat16 and N % 8 != 0:
+            # TMA needs 16-byte row pitches: stage dY in a buffer whose leading dimension is padded (vocab 30522 -> 30528)
+            pad = torch.zeros(M, (N + 7) // 8 * 8, dtype=dtype, device=dev)
+            pad[:, :N].copy_(d2)
+            dyc = pad[:, :N]
+        else:
+            dyc = d2 if (d2.dtype == dtype and d2.is_contiguous()) else ops.cast(d2.contiguous(), torch.empty(M, N, dtype=dtype, device=dev))
         if act != ops.ACT_NONE:
             # dy * act'(u): run through the dropout-free identity GEMM-less path: reuse dgrad epilogue on a unit problem is
             # wasteful; activations only appear on tiny decoder FFN rows here, so apply via the GEMM epilogue of dgrad below.

@@ -110,8 +110,8 @@ def gemm(a, b, out, backend=GEMM_AUTO, **kw):
 
 
 def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, scale=None, causal=False, drop_p=0.0,
-                drop_seed=0, drop_stream=0, dout=None, dq=None, dk=None, dv=None, delta=None):
-    _need_cuda(q, k, v, out, lse, mask, probs, dout, dq, dk, dv, delta)
+                drop_seed=0, drop_stream=0, dout=None, dq=None, dk=None, dv=None, delta=None, drop_mask=None):
+    _need_cuda(q, k, v, out, lse, mask, probs, dout, dq, dk, dv, delta, drop_mask)
     for t in (q, k, v, out):
         assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
     assert q.shape[0] == B * Lq and k.shape[0] == B * Lk and v.shape[0] == B * Lk and out.shape[0] == B * Lq
@@ -132,6 +132,9 @@ def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, s
     p.causal = 1 if causal else 0
     p.drop_p, p.drop_seed, p.drop_stream = float(drop_p), int(drop_seed), int(drop_stream)
     p.dtype = _code(q.dtype)
+    if drop_mask is not None:
+        assert drop_mask.dtype == torch.uint8 and drop_mask.is_contiguous() and drop_mask.numel() == B * H * Lq * drop_mask_ld(Lk)
+        p.drop_mask = drop_mask.data_ptr()
     if dout is not None:
         for t in (dout, dq, dk, dv):
             assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
@@ -141,6 +144,11 @@ def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, s
         p.lddq, p.lddk, p.lddv = dq.stride(0), dk.stride(0), dv.stride(0)
         p.delta = delta.data_ptr()
     return p
+
+
+def drop_mask_ld(Lk):
+    """bytes per attention row of the dropout keep-bit cache (64-key tiles, 8 bytes each)."""
+    return 8 * ((Lk + 63) // 64)
 
 
 def attn_fwd(q, k, v, out, lse, **kw):

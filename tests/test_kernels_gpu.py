@@ -257,10 +257,12 @@ def test_attention_fwd_bwd(backend, dtype, tol, case):
         ops.set_attention_backend(ops.GEMM_AUTO)
 
 
+@pytest.mark.parametrize("cache", [False, True])
 @pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO])
-def test_attention_dropout_consistency(backend):
-    """Dropout cannot be bit-matched to PyTorch's Philox stream; check keep-rate, scaling and fwd/bwd mask agreement."""
-    B, H, Lq, Lk, dh, p = 2, 12, 64, 325, 64, 0.1
+def test_attention_dropout_consistency(backend, cache):
+    """Dropout cannot be bit-matched to PyTorch's Philox stream; check keep-rate, scaling and fwd/bwd mask agreement
+    (with and without the keep-bit cache the tensor-core forward writes for the backward kernels)."""
+    B, H, Lq, Lk, dh, p = 2, 12, 70, 325, 64, 0.1
     ops.set_attention_backend(backend)
     try:
         q, k, v = (rnd(B * L, H * dh, dtype=torch.bfloat16, seed=i) for i, L in ((0, Lq), (1, Lk), (2, Lk)))
@@ -268,11 +270,17 @@ def test_attention_dropout_consistency(backend):
         lse = torch.empty(B, H, Lq, device=DEV)
         probs = torch.empty(B, H, Lq, Lk, device=DEV)
         kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, drop_p=p, drop_seed=99, drop_stream=3)
+        if cache:
+            kw["drop_mask"] = torch.zeros(B * H * Lq * ops.drop_mask_ld(Lk), dtype=torch.uint8, device=DEV)
         ops.attn_fwd(q, k, v, out, lse, probs=probs, **kw)
         _, pref = _attn_ref(q, k, v, None, B, H, Lq, Lk, dh, False)
         keep = probs != 0
         assert abs(keep.float().mean().item() - (1 - p)) < 5e-3
         assert rel_err(probs[keep], pref[keep] / (1 - p)) < 1e-2
+        if cache and backend == ops.GEMM_AUTO:
+            bits = kw["drop_mask"].view(B, H, Lq, -1)
+            unpacked = ((bits[..., None] >> torch.arange(8, device=DEV, dtype=torch.uint8)) & 1).flatten(-2)[..., :Lk].bool()
+            assert torch.equal(unpacked, keep), "cached keep bits must equal the mask the probabilities show"
         # forward output equals (dropped probs) @ V
         vf = v.float().view(B, Lk, H, dh).transpose(1, 2)
         oref = (probs @ vf).transpose(1, 2).reshape(B * Lq, H * dh)
