@@ -15,8 +15,10 @@ void count_launch();
 namespace {
 
 constexpr int D = 64;     // head dim
-constexpr int BN = 64;    // keys (fwd, dQ) or queries (dKV) per smem tile
 constexpr int LDS = 72;   // padded row length in bf16 (144 B): conflict-free ldmatrix
+// Tile sizes are template parameters: NWARPS x 16 rows per CTA, BN (32 / 48 / 64) columns per smem tile.  L = 325
+// (ViT-B/16 at 288 px) is 7 x 48 - 11, so 3-warp CTAs and 48-wide tiles waste 3% where 64/64 tiling wasted 28%;
+// L = 32 (text) uses 32-wide tiles.
 
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -74,35 +76,37 @@ __device__ __forceinline__ float quad_sum(float v) {
 // ---- dropout keep-bit tiles: sBits[row] holds 64 bits = keys k0..k0+63 of attention row (q0+row).
 // Forward generates the tile cooperatively (one Philox evaluation per 8 keys) and stores it to the global bit cache;
 // backward kernels load it back.  Without a cache (drop_mask == NULL) every kernel regenerates the tile.
-template <int ROWS, int NT>
-__device__ __forceinline__ void gen_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
+__device__ __forceinline__ int64_t mask_ld_bytes(const m3ae_attn_params_t& P) { return 8 * (int64_t)((P.Lk + 63) / 64); }
+// sBits[row] (8 bytes per row) holds the keep bits of keys c0 .. c0+8*GROUPS-1 of attention row row0+row.
+// gen: evaluate Philox (8 keys per evaluation) and, if a global cache is given, store the bytes there as well.
+template <int ROWS, int GROUPS, int NT>
+__device__ __forceinline__ void gen_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int c0, int tid, bool store) {
   const uint32_t thr = drop_thr16(P.drop_p);
   uint8_t* sb = reinterpret_cast<uint8_t*>(sBits);
-  for (int i = tid; i < ROWS * 8; i += NT) {
-    const int r = i >> 3, grp = i & 7;
+  const int64_t ld = mask_ld_bytes(P);
+  for (int i = tid; i < ROWS * GROUPS; i += NT) {
+    const int r = i / GROUPS, grp = i % GROUPS;
     const uint64_t row_lin = ((uint64_t)b * P.H + h) * P.Lq + (row0 + r);
-    sb[r * 8 + grp] = (uint8_t)attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, (k0 >> 3) + grp, thr);
+    const uint8_t bits = (uint8_t)attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, (c0 >> 3) + grp, thr);
+    sb[r * 8 + grp] = bits;
+    if (store && row0 + r < P.Lq && (c0 >> 3) + grp < ld) P.drop_mask[(int64_t)row_lin * ld + (c0 >> 3) + grp] = bits;
   }
 }
-__device__ __forceinline__ int64_t mask_ld_bytes(const m3ae_attn_params_t& P) { return 8 * (int64_t)((P.Lk + 63) / 64); }
-template <int ROWS, int NT>
-__device__ __forceinline__ void store_keep_tile(const uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
-  // call after a __syncthreads following gen_keep_tile
-  uint8_t* base = P.drop_mask + (((int64_t)b * P.H + h) * P.Lq) * mask_ld_bytes(P);
-  for (int r = tid; r < ROWS; r += NT)
-    if (row0 + r < P.Lq) *reinterpret_cast<uint64_t*>(base + (int64_t)(row0 + r) * mask_ld_bytes(P) + (k0 >> 3)) = sBits[r];
-}
-template <int ROWS, int NT>
-__device__ __forceinline__ void load_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int k0, int tid) {
-  const uint8_t* base = P.drop_mask + (((int64_t)b * P.H + h) * P.Lq) * mask_ld_bytes(P);
-  for (int r = tid; r < ROWS; r += NT)
-    sBits[r] = (row0 + r < P.Lq) ? *reinterpret_cast<const uint64_t*>(base + (int64_t)(row0 + r) * mask_ld_bytes(P) + (k0 >> 3)) : 0ull;
+template <int ROWS, int GROUPS, int NT>
+__device__ __forceinline__ void load_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int c0, int tid) {
+  uint8_t* sb = reinterpret_cast<uint8_t*>(sBits);
+  const int64_t ld = mask_ld_bytes(P);
+  const uint8_t* base = P.drop_mask + (((int64_t)b * P.H + h) * P.Lq) * ld;
+  for (int i = tid; i < ROWS * GROUPS; i += NT) {
+    const int r = i / GROUPS, grp = i % GROUPS;
+    sb[r * 8 + grp] = (row0 + r < P.Lq && (c0 >> 3) + grp < ld) ? base[(int64_t)(row0 + r) * ld + (c0 >> 3) + grp] : (uint8_t)0;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ forward
-template <int NWARPS>
+template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_attn_params_t P) {
-  constexpr int BM = NWARPS * 16, NT = NWARPS * 32;
+  constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sQ[BM][LDS];
   __shared__ __align__(16) bf16 sK[BN][LDS];
   __shared__ __align__(16) bf16 sV[BN][LDS];
@@ -133,17 +137,16 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
     load_tile<BN, NT>(sK, K, P.ldk, k0, P.Lk, tid);
     load_tile<BN, NT>(sV, V, P.ldv, k0, P.Lk, tid);
     for (int i = tid; i < BN; i += NT) sMask[i] = (k0 + i < P.Lk) ? (mask ? mask[k0 + i] : 0.f) : -INFINITY;
-    if (drop) gen_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
+    if (drop) gen_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid, P.drop_mask != nullptr);
     __syncthreads();
-    if (drop && P.drop_mask) store_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
 
-    float s[8][4];
+    float s[NJ][4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+    for (int j = 0; j < NJ; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
-      for (int jp = 0; jp < 4; ++jp) {
+      for (int jp = 0; jp < NJ / 2; ++jp) {
         uint32_t bb[4];
         load_b_nk(bb, sK, jp, kk, lane);
         mma16816(s[2 * jp], qa[kk], bb[0], bb[1]);
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
       }
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       const int c = j * 8 + 2 * t;
       const float ma = sMask[c], mb = sMask[c + 1];
       s[j][0] = s[j][0] * P.scale + ma; s[j][1] = s[j][1] * P.scale + mb;
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
     m0 = mn0; m1 = mn1;
     float ps0 = 0.f, ps1 = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       s[j][0] = __expf(s[j][0] - mu0); s[j][1] = __expf(s[j][1] - mu0);
       s[j][2] = __expf(s[j][2] - mu1); s[j][3] = __expf(s[j][3] - mu1);
       ps0 += s[j][0] + s[j][1];
@@ -185,14 +188,14 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
     if (drop) {
       const uint64_t bits0 = sBits[warp * 16 + g] >> (2 * t), bits1 = sBits[warp * 16 + g + 8] >> (2 * t);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < NJ; ++j) {
         const uint32_t ka = (uint32_t)(bits0 >> (8 * j)) & 3u, kb = (uint32_t)(bits1 >> (8 * j)) & 3u;
         s[j][0] = (ka & 1) ? s[j][0] * keep_scale : 0.f; s[j][1] = (ka & 2) ? s[j][1] * keep_scale : 0.f;
         s[j][2] = (kb & 1) ? s[j][2] * keep_scale : 0.f; s[j][3] = (kb & 2) ? s[j][3] * keep_scale : 0.f;
       }
     }
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
+    for (int kk = 0; kk < NK2; ++kk) {
       uint32_t pa[4];
       pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
       pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -233,9 +236,9 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
 }
 
 // ------------------------------------------------------------------------------------------------ backward: dQ
-template <int NWARPS>
+template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae_attn_params_t P) {
-  constexpr int BM = NWARPS * 16, NT = NWARPS * 32;
+  constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sQ[BM][LDS];   // Q, then dQ staging
   __shared__ __align__(16) bf16 sdO[BM][LDS];
   __shared__ __align__(16) bf16 sK[BN][LDS];
@@ -271,21 +274,21 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
     load_tile<BN, NT>(sV, V, P.ldv, k0, P.Lk, tid);
     for (int i = tid; i < BN; i += NT) sMask[i] = (k0 + i < P.Lk) ? (mask ? mask[k0 + i] : 0.f) : -INFINITY;
     if (drop) {
-      if (P.drop_mask) load_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
-      else gen_keep_tile<BM, NT>(sBits, P, b, h, q0, k0, tid);
+      if (P.drop_mask) load_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid);
+      else gen_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid, false);
     }
     __syncthreads();
     const uint64_t bits0 = drop ? sBits[warp * 16 + g] >> (2 * t) : 0ull, bits1 = drop ? sBits[warp * 16 + g + 8] >> (2 * t) : 0ull;
-    float s[8][4], dp[8][4];
+    float s[NJ][4], dp[NJ][4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
       dp[j][0] = dp[j][1] = dp[j][2] = dp[j][3] = 0.f;
     }
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
-      for (int jp = 0; jp < 4; ++jp) {
+      for (int jp = 0; jp < NJ / 2; ++jp) {
         uint32_t bb[4];
         load_b_nk(bb, sK, jp, kk, lane);
         mma16816(s[2 * jp], qa[kk], bb[0], bb[1]);
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
         mma16816(dp[2 * jp + 1], da[kk], bb[2], bb[3]);
       }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       const int c = j * 8 + 2 * t;
       const int key = k0 + c;
       const float ma = sMask[c], mb = sMask[c + 1];
@@ -317,7 +320,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
       s[j][2] = p2 * (d2 - dl1) * P.scale; s[j][3] = p3 * (d3 - dl1) * P.scale;
     }
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
+    for (int kk = 0; kk < NK2; ++kk) {
       uint32_t pa[4];
       pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
       pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -350,9 +353,9 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
 
 // ------------------------------------------------------------------------------------------------ backward: dK, dV
 // Works on the transposed problem: rows = keys (16 per warp), columns = queries (64 per smem tile).
-template <int NWARPS>
+template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3ae_attn_params_t P) {
-  constexpr int BM = NWARPS * 16, NT = NWARPS * 32;
+  constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sK[BM][LDS];   // K, then dK staging
   __shared__ __align__(16) bf16 sV[BM][LDS];   // V, then dV staging
   __shared__ __align__(16) bf16 sQ[BN][LDS];
@@ -377,8 +380,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
   const float ma0 = (mrow && key0 < P.Lk) ? mrow[key0] : 0.f, ma1 = (mrow && key1 < P.Lk) ? mrow[key1] : 0.f;
   const int64_t sbase = ((int64_t)b * P.H + h) * P.Lq;
   const float keep_scale = drop_keep_scale(P.drop_p);
-  const int kgrp0 = kb0 & ~63;                       // 64-key group start
-  const int kl0 = (kb0 - kgrp0) + warp * 16 + g, kl1 = kl0 + 8;  // bit positions of this thread's two keys
+  const int kl0 = warp * 16 + g, kl1 = kl0 + 8;  // bit positions of this thread's two keys inside the CTA's key bytes
   float dk[8][4], dv[8][4];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -395,20 +397,20 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
       sDl[i] = ok ? P.delta[sbase + i0 + i] : 0.f;
     }
     if (drop) {
-      if (P.drop_mask) load_keep_tile<BN, NT>(sBits, P, b, h, i0, kgrp0, tid);
-      else gen_keep_tile<BN, NT>(sBits, P, b, h, i0, kgrp0, tid);
+      if (P.drop_mask) load_keep_tile<BN, BM / 8, NT>(sBits, P, b, h, i0, kb0, tid);
+      else gen_keep_tile<BN, BM / 8, NT>(sBits, P, b, h, i0, kb0, tid, false);
     }
     __syncthreads();
-    float s[8][4], dp[8][4];  // S^T[key][query], dP^T[key][query]
+    float s[NJ][4], dp[NJ][4];  // S^T[key][query], dP^T[key][query]
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
       dp[j][0] = dp[j][1] = dp[j][2] = dp[j][3] = 0.f;
     }
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
-      for (int jp = 0; jp < 4; ++jp) {
+      for (int jp = 0; jp < NJ / 2; ++jp) {
         uint32_t bb[4];
         load_b_nk(bb, sQ, jp, kk, lane);
         mma16816(s[2 * jp], ka[kk], bb[0], bb[1]);
@@ -418,7 +420,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
         mma16816(dp[2 * jp + 1], va[kk], bb[2], bb[3]);
       }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < NJ; ++j) {
       const int c = j * 8 + 2 * t;
       const int qa_ = i0 + c, qb_ = qa_ + 1;
       const float la = sLse[c], lb = sLse[c + 1], da_ = sDl[c], db_ = sDl[c + 1];
@@ -445,7 +447,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3a
       s[j][0] = e0; s[j][1] = e1; s[j][2] = e2; s[j][3] = e3;
     }
 #pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
+    for (int kk = 0; kk < NK2; ++kk) {
       uint32_t pa[4], sa[4];
       pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
       pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
@@ -506,16 +508,28 @@ bool supported(const m3ae_attn_params_t* p, bool bwd) {
 
 }  // namespace
 
+// rows per CTA (16 x warps) and smem tile width for a sequence length: 325 -> 48 (7 x 48 = 336), <= 32 -> 32, else 64
+inline int pick_tile(int L) { return L <= 32 ? 32 : ((L + 47) / 48 * 48 <= (L + 63) / 64 * 64 ? 48 : 64); }
+
+#define ATTN_DISPATCH(KERNEL, ROWS_L, COLS_L, ROW_COUNT)                                              \
+  do {                                                                                                 \
+    const int bm = pick_tile(ROWS_L), bn = pick_tile(COLS_L);                                          \
+    dim3 grid((ROW_COUNT + bm - 1) / bm, p->H, p->B);                                                  \
+    if (bm == 32 && bn == 32) KERNEL<2, 32><<<grid, 64, 0, st>>>(*p);                                  \
+    else if (bm == 32 && bn == 48) KERNEL<2, 48><<<grid, 64, 0, st>>>(*p);                             \
+    else if (bm == 32) KERNEL<2, 64><<<grid, 64, 0, st>>>(*p);                                         \
+    else if (bm == 48 && bn == 32) KERNEL<3, 32><<<grid, 96, 0, st>>>(*p);                             \
+    else if (bm == 48 && bn == 48) KERNEL<3, 48><<<grid, 96, 0, st>>>(*p);                             \
+    else if (bm == 48) KERNEL<3, 64><<<grid, 96, 0, st>>>(*p);                                         \
+    else if (bn == 32) KERNEL<4, 32><<<grid, 128, 0, st>>>(*p);                                        \
+    else if (bn == 48) KERNEL<4, 48><<<grid, 128, 0, st>>>(*p);                                        \
+    else KERNEL<4, 64><<<grid, 128, 0, st>>>(*p);                                                      \
+    count_launch();                                                                                    \
+  } while (0)
+
 int attn_fwd_mma(const m3ae_attn_params_t* p, cudaStream_t st) {
   if (!supported(p, false)) return M3AE_ERR_UNSUPPORTED;
-  if (p->Lq <= 32) {
-    dim3 grid((p->Lq + 31) / 32, p->H, p->B);
-    attn_fwd_mma_kernel<2><<<grid, 64, 0, st>>>(*p);
-  } else {
-    dim3 grid((p->Lq + 63) / 64, p->H, p->B);
-    attn_fwd_mma_kernel<4><<<grid, 128, 0, st>>>(*p);
-  }
-  count_launch();
+  ATTN_DISPATCH(attn_fwd_mma_kernel, p->Lq, p->Lk, p->Lq);
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
 }
@@ -525,22 +539,8 @@ void launch_delta_bf16_64(const m3ae_attn_params_t* p, cudaStream_t st);  // att
 int attn_bwd_mma(const m3ae_attn_params_t* p, cudaStream_t st) {
   if (!supported(p, true)) return M3AE_ERR_UNSUPPORTED;
   launch_delta_bf16_64(p, st);
-  if (p->Lq <= 32) {
-    dim3 grid((p->Lq + 31) / 32, p->H, p->B);
-    attn_bwd_dq_mma_kernel<2><<<grid, 64, 0, st>>>(*p);
-  } else {
-    dim3 grid((p->Lq + 63) / 64, p->H, p->B);
-    attn_bwd_dq_mma_kernel<4><<<grid, 128, 0, st>>>(*p);
-  }
-  count_launch();
-  if (p->Lk <= 32) {
-    dim3 grid((p->Lk + 31) / 32, p->H, p->B);
-    attn_bwd_dkv_mma_kernel<2><<<grid, 64, 0, st>>>(*p);
-  } else {
-    dim3 grid((p->Lk + 63) / 64, p->H, p->B);
-    attn_bwd_dkv_mma_kernel<4><<<grid, 128, 0, st>>>(*p);
-  }
-  count_launch();
+  ATTN_DISPATCH(attn_bwd_dq_mma_kernel, p->Lq, p->Lk, p->Lq);    // CTA rows = queries, tiles over keys
+  ATTN_DISPATCH(attn_bwd_dkv_mma_kernel, p->Lk, p->Lq, p->Lk);   // CTA rows = keys, tiles over queries
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
 }
