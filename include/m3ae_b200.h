@@ -43,6 +43,7 @@ extern "C" {
 #define M3AE_GEMM_AUTO 0
 #define M3AE_GEMM_TCGEN05 1 /* TMA + tcgen05.mma + TMEM (bf16 inputs only) */
 #define M3AE_GEMM_SIMT 2    /* fp32 FFMA tiles (f32 or bf16 inputs): strict-parity + debugging path */
+#define M3AE_ATTN_MMA_SYNC 3 /* attention only: legacy mma.sync flash tiles instead of the tcgen05 kernels */
 
 #define M3AE_OK 0
 #define M3AE_ERR_INVALID (-1)
@@ -196,7 +197,9 @@ int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M
 int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M,
                        int32_t D, int32_t out_dtype, void* stream);
 
-/* Test hook: 0 = auto (tensor-core attention for bf16), 2 = force the generic fp32-math attention kernels. */
+/* Test hook: 0 = auto (tcgen05/TMEM attention for bf16 where the shape is covered, else mma.sync tiles),
+ * 1 = tcgen05 for every covered shape (auto skips the ones where mma.sync is faster), 2 = force the generic fp32-math
+ * attention kernels, 3 (M3AE_ATTN_MMA_SYNC) = skip tcgen05, use the mma.sync tiles. */
 int m3ae_set_attention_backend(int32_t backend);
 /* Test hook: 1 = force the generic per-element GEMM epilogue (cross-checks the TMA-staged one), 0 = auto. */
 int m3ae_set_gemm_epilogue(int32_t generic);

@@ -13,6 +13,7 @@ F32, BF16 = 0, 1
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
 MAJOR_K, MAJOR_MN = 0, 1
 GEMM_AUTO, GEMM_TCGEN05, GEMM_SIMT = 0, 1, 2
+ATTN_MMA_SYNC = 3
 
 
 class GemmEpilogue(C.Structure):

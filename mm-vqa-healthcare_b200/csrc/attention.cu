@@ -13,6 +13,8 @@ namespace m3ae {
 void count_launch();
 int attn_fwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);  // attention_mma.cu; returns M3AE_ERR_UNSUPPORTED if shape not covered
 int attn_bwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);
+int attn_fwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st);   // attention_tc.cu (tcgen05/TMEM); M3AE_ERR_UNSUPPORTED if not covered / not profitable
+int attn_bwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st);
 
 namespace {
 
@@ -476,7 +478,8 @@ int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, false);
   if (rc) return rc;
   if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
-    rc = attn_fwd_mma(p, st);
+    rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_fwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
+    if (rc == M3AE_ERR_UNSUPPORTED) rc = attn_fwd_mma(p, st);
     if (rc == M3AE_OK && p->probs) {
       launch_probs<bf16>(p, st);
       M3AE_CUDA(cudaGetLastError());
@@ -493,7 +496,8 @@ int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, true);
   if (rc) return rc;
   if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
-    rc = attn_bwd_mma(p, st);
+    rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_bwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
+    if (rc == M3AE_ERR_UNSUPPORTED) rc = attn_bwd_mma(p, st);
     if (rc != M3AE_ERR_UNSUPPORTED) return rc;
   }
   if (p->dtype == M3AE_BF16) launch_generic_bwd<bf16>(p, st);

@@ -215,12 +215,15 @@ ATT_CASES = [  # (B, H, Lq, Lk, dh, masked, causal)
     (2, 12, 325, 325, 64, False, False),
     (2, 12, 325, 32, 64, True, False),
     (2, 12, 577, 577, 64, False, False),
+    (2, 12, 384, 384, 64, True, False),
+    (2, 12, 130, 100, 64, True, False),
+    (1, 12, 5, 7, 64, False, False),
     (3, 8, 12, 12, 96, False, True),
     (3, 8, 12, 359, 96, False, False),
 ]
 
 
-@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO])
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO, ops.GEMM_TCGEN05, ops.ATTN_MMA_SYNC])
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2)])
 @pytest.mark.parametrize("case", ATT_CASES)
 def test_attention_fwd_bwd(backend, dtype, tol, case):
@@ -258,7 +261,7 @@ def test_attention_fwd_bwd(backend, dtype, tol, case):
 
 
 @pytest.mark.parametrize("cache", [False, True])
-@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO])
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO, ops.GEMM_TCGEN05, ops.ATTN_MMA_SYNC])
 def test_attention_dropout_consistency(backend, cache):
     """Dropout cannot be bit-matched to PyTorch's Philox stream; check keep-rate, scaling and fwd/bwd mask agreement
     (with and without the keep-bit cache the tensor-core forward writes for the backward kernels)."""
@@ -277,7 +280,7 @@ def test_attention_dropout_consistency(backend, cache):
         keep = probs != 0
         assert abs(keep.float().mean().item() - (1 - p)) < 5e-3
         assert rel_err(probs[keep], pref[keep] / (1 - p)) < 1e-2
-        if cache and backend == ops.GEMM_AUTO:
+        if cache and backend != ops.GEMM_SIMT:
             bits = kw["drop_mask"].view(B, H, Lq, -1)
             unpacked = ((bits[..., None] >> torch.arange(8, device=DEV, dtype=torch.uint8)) & 1).flatten(-2)[..., :Lk].bool()
             assert torch.equal(unpacked, keep), "cached keep bits must equal the mask the probabilities show"

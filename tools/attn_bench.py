@@ -6,6 +6,7 @@ from m3ae_b200 import ops
 dev = "cuda"
 B, H, dh = int(os.environ.get("B", "64")), 12, 64
 reps = int(os.environ.get("REPS", "10"))
+ops.set_attention_backend(int(os.environ.get("ATTN_BACKEND", "0")))  # 0 auto (tcgen05), 3 mma.sync
 def run(Lq, Lk, drop=0.0):
     q = torch.randn(B * Lq, 3 * H * dh, device=dev).to(torch.bfloat16)
     kv = torch.randn(B * Lk, 3 * H * dh, device=dev).to(torch.bfloat16)
