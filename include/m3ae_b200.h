@@ -62,7 +62,7 @@ int64_t m3ae_launch_count(void);
  * :426 (FFN up) and :439 (FFN down), m3ae_module.py:235,252 (modality projections),
  * m3ae_decoder.py:60-61,78-79 (in/out projections), :85 (FFN), :136 (vocab projection), and —
  * with MN-major operands — their autograd backward (dgrad: dX = dY·W, wgrad: dW = dY^T·X).
- * Epilogue order = the reference modules': (+bias) -> [aux_out := pre-activation] -> act ->
+ * Epilogue order = the reference modules': (+bias) -> [aux_out := pre-activation or act'(it)] -> act ->
  * (* act'(aux_in)) -> dropout -> (+residual)   (BertSelfOutput :361-363, BertIntermediate :426-427,
  * BertOutput :439-441).
  * --------------------------------------------------------------------------------------------- */
@@ -85,6 +85,8 @@ typedef struct m3ae_gemm_epilogue_t {
   uint64_t drop_stream; /* distinguishes dropout sites; element index = row*ldo+col */
   int32_t accumulate;   /* 1: out (fp32) += result (atomic; required when split_k > 1) */
   float alpha;
+  int32_t aux_is_grad;  /* 1: aux_out receives act'(pre-activation) instead of the pre-activation, and dact multiplies by
+                         * aux_in as stored (the FFN backward then needs one multiply per element instead of a GELU') */
 } m3ae_gemm_epilogue_t;
 
 typedef struct m3ae_gemm_problem_t {

@@ -24,7 +24,7 @@ class GemmEpilogue(C.Structure):
         ("dact", C.c_int32),
         ("residual", C.c_void_p), ("res_dtype", C.c_int32), ("ldr", C.c_int64),
         ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_stream", C.c_uint64),
-        ("accumulate", C.c_int32), ("alpha", C.c_float),
+        ("accumulate", C.c_int32), ("alpha", C.c_float), ("aux_is_grad", C.c_int32),
     ]
 
 

@@ -71,9 +71,11 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
   return cdf + x * pdf;
 }
 
-// Branch-free GELU for the bf16 tensor-core epilogue: erfc(|z|) ~ poly(t) exp(-z^2), t = 1/(1+p|z|)
-// (Abramowitz-Stegun 7.1.26, |abs err| < 1.5e-7 — far below bf16 resolution).  ~16 instructions, 2 MUFU.
-// The fp32 parity path keeps erff().  fast_gelu_terms returns (cdf, pdf) of the standard normal at x.
+// Branch-free GELU for the bf16 tensor-core epilogue.  h(x) = 0.5*erfc(|x|/sqrt(2)) ~ 0.5 * t(a1 + t(a2 + a3 t)) exp(-x^2/2),
+// t = 1/(1 + p|x|/sqrt(2))  (Abramowitz-Stegun 7.1.25, |abs err| <= 1.3e-5 on h — bf16 resolves 2e-3 relative).  Then
+//   gelu(x)  = relu(x) - |x| h          (x Phi(x) with Phi = 1-h for x >= 0, h for x < 0)
+//   gelu'(x) = Phi(x) + x pdf(x),  Phi(x) = 0.5 + copysign(0.5 - h, x)
+// 11 FMA-pipe instructions + 2 MUFU per element for gelu.  The fp32 parity path keeps erff().
 __device__ __forceinline__ float rcp_approx(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -84,27 +86,32 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
-__device__ __forceinline__ void fast_gelu_terms(float x, float& cdf, float& pdf) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = rcp_approx(fmaf(0.3275911f, z, 1.0f));
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float e = ex2_approx(z * z * -1.4426950408889634f);  // exp(-x^2/2)
-  const float half_erfc = 0.5f * poly * t * e;           // 0.5*erfc(|z|)
-  cdf = x >= 0.f ? 1.0f - half_erfc : half_erfc;
-  pdf = 0.39894228040143268f * e;
+// returns h = 0.5*erfc(|x|/sqrt(2)) and e = exp(-x^2/2)
+__device__ __forceinline__ float fast_half_erfc(float x, float& e) {
+  const float t = rcp_approx(fmaf(0.47047f * 0.70710678118654752f, fabsf(x), 1.0f));
+  float poly = fmaf(0.5f * 0.7478556f, t, 0.5f * -0.0958798f);
+  poly = fmaf(poly, t, 0.5f * 0.3480242f);
+  e = ex2_approx((x * -0.72134752044448170f) * x);  // 2^(-x^2 log2(e)/2)
+  return (poly * t) * e;
 }
 __device__ __forceinline__ float fast_gelu(float x) {
-  float c, p;
-  fast_gelu_terms(x, c, p);
-  return x * c;
+  float e;
+  const float h = fast_half_erfc(x, e);
+  return fmaf(-fabsf(x), h, fmaxf(x, 0.f));
 }
 __device__ __forceinline__ float fast_gelu_grad(float x) {
-  float c, p;
-  fast_gelu_terms(x, c, p);
-  return fmaf(x, p, c);
+  float e;
+  const float h = fast_half_erfc(x, e);
+  const float cdf = 0.5f + copysignf(0.5f - h, x);
+  return fmaf(x * 0.39894228040143268f, e, cdf);
+}
+// gelu and gelu' sharing one erfc evaluation
+__device__ __forceinline__ float fast_gelu_both(float x, float& grad) {
+  float e;
+  const float h = fast_half_erfc(x, e);
+  const float cdf = 0.5f + copysignf(0.5f - h, x);
+  grad = fmaf(x * 0.39894228040143268f, e, cdf);
+  return fmaf(-fabsf(x), h, fmaxf(x, 0.f));
 }
 
 // ---------------------------------------------------------------- Philox4x32-7 (counter-based RNG for dropout; 7 rounds pass BigCrush)
@@ -197,6 +204,7 @@ struct EpiDev {
   float drop_p; uint64_t drop_seed; uint64_t drop_stream;
   int accumulate;          // 1: atomicAdd into fp32 out (split-K partials / grad accumulation)
   float alpha;
+  int aux_is_grad;         // aux_out := act'(pre-activation); dact multiplies by aux_in as stored
 };
 
 // Applies the epilogue to `n` consecutive columns [col, col+n) of row `row` whose accumulators are acc[0..n).
@@ -213,7 +221,11 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
   }
   if (e.aux_out) {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) if (j < n_valid) store_from_f32(e.aux_out, e.out_dtype, (size_t)(row * e.ldo + col + j), acc[j]);
+    for (int j = 0; j < NV; ++j) if (j < n_valid) {
+      float a = acc[j];
+      if (e.aux_is_grad) a = e.act == M3AE_ACT_GELU ? gelu_erf_grad(a) : e.act == M3AE_ACT_RELU ? (a > 0.0f ? 1.0f : 0.0f) : 1.0f;
+      store_from_f32(e.aux_out, e.out_dtype, (size_t)(row * e.ldo + col + j), a);
+    }
   }
   if (e.act == M3AE_ACT_GELU) {
 #pragma unroll
@@ -226,7 +238,7 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
       const float u = load_as_f32(e.aux_in, e.aux_in_dtype, (size_t)(row * e.ld_aux_in + col + j));
-      acc[j] *= (e.dact == M3AE_ACT_GELU) ? gelu_erf_grad(u) : (u > 0.0f ? 1.0f : 0.0f);
+      acc[j] *= e.aux_is_grad ? u : (e.dact == M3AE_ACT_GELU) ? gelu_erf_grad(u) : (u > 0.0f ? 1.0f : 0.0f);
     }
   }
   if (e.drop_p > 0.0f) {
@@ -290,6 +302,12 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 // 2-D tiled TMA store shared -> global (bulk async-group completion); out-of-bounds rows/columns are clipped.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c_inner, int c_outer) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"((uint64_t)m),
+               "r"(smem_u32(smem_src)), "r"(c_inner), "r"(c_outer)
+               : "memory");
+}
+// 2-D tiled TMA reduction shared -> global: global[tile] += smem[tile] (element-wise add done at L2; clipped like a store).
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c_inner, int c_outer) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"((uint64_t)m),
                "r"(smem_u32(smem_src)), "r"(c_inner), "r"(c_outer)
                : "memory");
 }

@@ -12,7 +12,7 @@ void epi_to_dev(const m3ae_gemm_epilogue_t& e, EpiDev* d) {
   d->aux_in = e.aux_in; d->aux_in_dtype = e.aux_in_dtype; d->ld_aux_in = e.ld_aux_in; d->dact = e.dact;
   d->residual = e.residual; d->res_dtype = e.res_dtype; d->ldr = e.ldr;
   d->drop_p = e.drop_p; d->drop_seed = e.drop_seed; d->drop_stream = e.drop_stream;
-  d->accumulate = e.accumulate; d->alpha = e.alpha;
+  d->accumulate = e.accumulate; d->alpha = e.alpha; d->aux_is_grad = e.aux_is_grad;
 }
 void count_launch();
 

@@ -36,7 +36,8 @@ constexpr int EPI_BUF_BYTES = 32 * 64;
 constexpr int EPI_WARP_BYTES = 4 * EPI_BUF_BYTES;
 constexpr int EPI_BYTES = NUM_EPI_WARPS * EPI_WARP_BYTES;
 constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
+constexpr int BIAS_BYTES = NUM_EPI_WARPS * 128 * 4;  // every epilogue warp stages the 128 bias values of its column half
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
 constexpr int MAX_GROUP = 4;
 
 struct alignas(64) TcProblem {
@@ -45,7 +46,8 @@ struct alignas(64) TcProblem {
   CUtensorMap map_out;   // fast epilogue only: bf16 [M,N], box 32x32, SWIZZLE_64B
   CUtensorMap map_aux;   // aux_out (same geometry as out)
   CUtensorMap map_in;    // residual or aux_in
-  int epi_fast;          // 1: TMA-staged bf16 epilogue; 0: generic per-element epilogue
+  int epi_fast;          // 1: TMA-staged bf16 epilogue; 2: fp32 accumulate through TMA reduce-add tiles (split-K wgrad);
+                         // 0: generic per-element epilogue
   int in_is_residual;    // fast path: which operand map_in describes (0 = none/aux_in)
   int has_in;
   EpiDev epi;
@@ -94,7 +96,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
-  uint64_t* bars = (uint64_t*)(epi_smem + EPI_BYTES);
+  float* bias_smem = (float*)(epi_smem + EPI_BYTES);
+  uint64_t* bars = (uint64_t*)(epi_smem + EPI_BYTES + BIAS_BYTES);
   uint64_t* full_bar = bars;                  // [STAGES]
   uint64_t* empty_bar = bars + STAGES;        // [STAGES]
   uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
@@ -109,7 +112,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     for (int i = 0; i < P.n_problems; ++i) {
       tma_prefetch_desc(&P.p[i].map_a);
       tma_prefetch_desc(&P.p[i].map_b);
-      if (P.p[i].epi_fast) {
+      if (P.p[i].epi_fast == 2) tma_prefetch_desc(&P.p[i].map_out);
+      if (P.p[i].epi_fast == 1) {
         tma_prefetch_desc(&P.p[i].map_out);
         if (P.p[i].epi.aux_out) tma_prefetch_desc(&P.p[i].map_aux);
         if (P.p[i].has_in) tma_prefetch_desc(&P.p[i].map_in);
@@ -213,6 +217,47 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
       const EpiDev& epi = q.epi;
+      if (q.epi_fast == 2) {
+        // ---- fp32 accumulate (out += alpha * acc): 32x32 fp32 tiles staged in swizzled smem, added into global memory
+        //      by TMA reductions.  One bulk reduction replaces 1024 scattered RED.ADD.F32 (lane = row: 32 lines/instr).
+        uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
+        const int row0 = u.m_blk * BM + quad * 32;
+        const int col_base = u.n_blk * BN + half * 128;
+        const int nchunks = (row0 < q.M) ? min(4, (q.N - col_base + 31) / 32) : 0;
+        const float alpha = epi.alpha;
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tcgen05_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < nchunks; ++c) {
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 128 + c * 32);
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr, r);
+          tmem_ld_wait();
+          uint8_t* buf = wbuf + (c & 1) * (2 * EPI_BUF_BYTES);
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {  // SWIZZLE_128B: 16-byte chunk ^= row % 8
+            const float4 w = make_float4(__uint_as_float(r[4 * j]) * alpha, __uint_as_float(r[4 * j + 1]) * alpha,
+                                         __uint_as_float(r[4 * j + 2]) * alpha, __uint_as_float(r[4 * j + 3]) * alpha);
+            *reinterpret_cast<float4*>(buf + lane * 128 + (((uint32_t)j ^ (uint32_t)(lane & 7)) << 4)) = w;
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_reduce_add_2d(&q.map_out, buf, col_base + c * 32, row0);
+            tma_store_commit();
+          }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&tmem_empty[acc]);
+          tma_store_wait_read<0>();  // the next unit may be a bf16 problem whose TMA loads land in these bytes
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
       if (q.epi_fast) {
         // ---- TMA-staged bf16 epilogue: coalesced in/out through swizzled smem sub-tiles of 32 rows x 32 columns
         uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
@@ -226,6 +271,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         if (q.has_in && lane == 0 && nchunks > 0) {
           mbar_expect_tx(&ibar[0], EPI_BUF_BYTES);
           tma_load_2d(wbuf, &q.map_in, &ibar[0], col_base, row0);
+        }
+        float* sbias = bias_smem + e * 128;
+        if (epi.bias) {  // issued before the accumulator wait: the global-load latency hides behind the tile's MMAs
+          const int c4 = col_base + 4 * lane;
+          const float4 b4 = (c4 < q.N) ? __ldg(reinterpret_cast<const float4*>(epi.bias + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
+          __syncwarp();
         }
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
@@ -244,10 +296,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           if (epi.bias) {
-            const float4* b4 = reinterpret_cast<const float4*>(epi.bias + col);
+            const float4* b4 = reinterpret_cast<const float4*>(sbias + c * 32);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 t4 = __ldg(b4 + j);
+              const float4 t4 = b4[j];
               v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
             }
           }
@@ -256,7 +308,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           // previous TMA stores must have finished READING the staging buffers we are about to overwrite
           if (lane == 0) { if (aux) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
           __syncwarp();
-          if (aux) {
+          const bool aux_grad = aux && epi.aux_is_grad;
+          if (aux && !aux_grad) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 w;
@@ -265,7 +318,36 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
               *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
             }
           }
-          if (epi.act == M3AE_ACT_GELU) {
+          if (aux_grad && epi.act == M3AE_ACT_GELU) {
+            // aux := gelu'(v): the cdf/pdf terms are shared with the activation itself (one extra FMA per element)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float d[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                v[8 * j + k] = fast_gelu_both(v[8 * j + k], d[k]);
+              }
+              uint4 w;
+              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
+              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
+              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+            }
+          } else if (aux_grad) {
+            const bool relu = epi.act == M3AE_ACT_RELU;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float d[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                d[k] = (!relu || v[8 * j + k] > 0.f) ? 1.f : 0.f;
+                if (relu) v[8 * j + k] = fmaxf(v[8 * j + k], 0.f);
+              }
+              uint4 w;
+              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
+              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
+              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+            }
+          } else if (epi.act == M3AE_ACT_GELU) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fast_gelu(v[j]);
           } else if (epi.act == M3AE_ACT_RELU) {
@@ -288,8 +370,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             __syncwarp();  // all lanes done with in[c&1] before lane 0 re-arms it two chunks later
           }
           if (epi.dact != M3AE_ACT_NONE) {
+            if (epi.aux_is_grad) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= (epi.dact == M3AE_ACT_GELU) ? fast_gelu_grad(in[j]) : (in[j] > 0.f ? 1.f : 0.f);
+              for (int j = 0; j < 32; ++j) v[j] *= in[j];
+            } else if (epi.dact == M3AE_ACT_GELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] *= fast_gelu_grad(in[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = in[j] > 0.f ? v[j] : 0.f;
+            }
           }
           if (epi.drop_p > 0.f) {
             const float inv = 1.0f / (1.0f - epi.drop_p);
@@ -442,6 +532,29 @@ int encode_epi_map(CUtensorMap* map, const void* base, int64_t rows, int64_t col
   return M3AE_OK;
 }
 
+// fp32 [rows, cols] row-major (ld) viewed through 32x32 boxes (128-byte rows) with SWIZZLE_128B: reduce-add staging.
+int encode_f32_tile_map(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld) {
+  auto fn = get_encode_fn();
+  M3AE_CHECK(fn != nullptr, M3AE_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)(ld * 4)};
+  cuuint32_t box[2] = {32u, 32u};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  M3AE_CHECK(r == CUDA_SUCCESS, M3AE_ERR_CUDA, "cuTensorMapEncodeTiled (fp32 reduce) failed with CUresult %d", (int)r);
+  return M3AE_OK;
+}
+
+// Pure fp32 accumulation (the split-K weight gradients): out += alpha * acc with nothing else in the epilogue.
+bool epilogue_is_reduce(const m3ae_gemm_problem_t& g) {
+  const m3ae_gemm_epilogue_t& e = g.epi;
+  if (e.out_dtype != M3AE_F32 || !e.accumulate) return false;
+  if (e.bias || e.aux_out || e.aux_in || e.residual || e.act != M3AE_ACT_NONE || e.dact != M3AE_ACT_NONE || e.drop_p > 0.f) return false;
+  return e.out != nullptr && (((uintptr_t)e.out) & 15) == 0 && (e.ldo % 4) == 0;
+}
+
 bool tma_ok(const void* p, int64_t ld) { return p != nullptr && (((uintptr_t)p) & 15) == 0 && (ld % 8) == 0; }
 
 // The TMA-staged epilogue covers the layer's bf16 cases: bf16 out (no atomics), N % 32 == 0, alpha == 1, at most one
@@ -497,9 +610,13 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
     q.epi_fast = (!force_generic_epilogue && epilogue_is_fast(g)) ? 1 : 0;
+    if (!force_generic_epilogue && epilogue_is_reduce(g)) q.epi_fast = 2;
     q.has_in = 0;
     q.in_is_residual = 0;
-    if (q.epi_fast) {
+    if (q.epi_fast == 2) {
+      rc = encode_f32_tile_map(&q.map_out, g.epi.out, g.M, g.N, g.epi.ldo);
+      if (rc) return rc;
+    } else if (q.epi_fast) {
       rc = encode_epi_map(&q.map_out, g.epi.out, g.M, g.N, g.epi.ldo);
       if (rc) return rc;
       if (g.epi.aux_out) {

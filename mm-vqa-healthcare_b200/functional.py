@@ -257,7 +257,7 @@ def _forward_streams(cfg, training, streams, want_probs):
             specs.append(ops.GemmSpec(st.y, st.w.wkv2, st.kvc, bias=st.w.bkv2))
         L_["xproj"] = _Gemm(specs)
         L_["o2"] = _Gemm([ops.GemmSpec(st.ctx2, st.w.wo2, st.h2, bias=st.p[BO2], residual=st.a1, drop_p=ph, drop_stream=3) for st in S])
-        L_["ffn1"] = _Gemm([ops.GemmSpec(st.a2, st.w.w1, st.g, bias=st.p[BI], act=ops.ACT_GELU, aux_out=st.u) for st in S])
+        L_["ffn1"] = _Gemm([ops.GemmSpec(st.a2, st.w.w1, st.g, bias=st.p[BI], act=ops.ACT_GELU, aux_out=st.u, aux_is_grad=True) for st in S])
         L_["ffn2"] = _Gemm([ops.GemmSpec(st.g, st.w.w2, st.h3, bias=st.p[BO3], residual=st.a2, drop_p=ph, drop_stream=4) for st in S])
         for st in S:
             H = st.H
@@ -353,7 +353,7 @@ def _backward_streams(cfg, S, douts):
             st.delta = st.buf("delta", (st.B, nh, st.Lq), f32, dev)
         B_ = {}
         gbv = lambda st, n, r, c: st.gb[n].view(r, c)  # noqa: E731
-        B_["ffn2"] = _Gemm([ops.GemmSpec(st.dh3d, st.w.w2, st.du, b_major=MN, aux_in=st.u, dact=ops.ACT_GELU) for st in S] +
+        B_["ffn2"] = _Gemm([ops.GemmSpec(st.dh3d, st.w.w2, st.du, b_major=MN, aux_in=st.u, dact=ops.ACT_GELU, aux_is_grad=True) for st in S] +
                            [wgrad(st.dh3d, st.g, gbv(st, "w2", st.H, st.FF)) for st in S])
         B_["ffn1"] = _Gemm([ops.GemmSpec(st.du, st.w.w1, st.da2, b_major=MN, residual=st.dh3) for st in S] +
                            [wgrad(st.du, st.a2, gbv(st, "w1", st.FF, st.H)) for st in S])

@@ -53,7 +53,7 @@ class GemmSpec:
 
     def __init__(self, a, b, out, *, a_major=MAJOR_K, b_major=MAJOR_K, bias=None, act=ACT_NONE, aux_out=None,
                  aux_in=None, dact=ACT_NONE, residual=None, drop_p=0.0, drop_seed=0, drop_stream=0, accumulate=False,
-                 split_k=1, alpha=1.0):
+                 split_k=1, alpha=1.0, aux_is_grad=False):
         _need_cuda(a, b, out, bias, aux_out, aux_in, residual)
         assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
         assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
@@ -92,6 +92,7 @@ class GemmSpec:
         e.drop_p, e.drop_seed, e.drop_stream = float(drop_p), int(drop_seed), int(drop_stream)
         e.accumulate = 1 if accumulate else 0
         e.alpha = float(alpha)
+        e.aux_is_grad = 1 if aux_is_grad else 0
         self.problem = p
 
 

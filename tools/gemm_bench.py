@@ -50,9 +50,11 @@ for which in (["i"], ["t"], ["t", "i"]):
     bench(f"[{tag}] fwd O-proj N=768 bias+drop+res", lambda: [ops.GemmSpec(xs[s], wo, out(Ms[s], H), bias=bias[H], residual=xs[s], drop_p=0.1, drop_seed=1, drop_stream=1) for s in which])
     bench(f"[{tag}] fwd plain N=768 no epilogue", lambda: [ops.GemmSpec(xs[s], wo, out(Ms[s], H)) for s in which])
     bench(f"[{tag}] fwd FFN-up N=3072 bias+gelu+aux", lambda: [ops.GemmSpec(xs[s], w1, out(Ms[s], FF), bias=bias[FF], act=ops.ACT_GELU, aux_out=out(Ms[s], FF)) for s in which])
+    bench(f"[{tag}] fwd FFN-up N=3072 bias+gelu+aux=gelu'", lambda: [ops.GemmSpec(xs[s], w1, out(Ms[s], FF), bias=bias[FF], act=ops.ACT_GELU, aux_out=out(Ms[s], FF), aux_is_grad=True) for s in which])
     bench(f"[{tag}] fwd FFN-up N=3072 plain", lambda: [ops.GemmSpec(xs[s], w1, out(Ms[s], FF)) for s in which])
     bench(f"[{tag}] fwd FFN-down K=3072 bias+res", lambda: [ops.GemmSpec(ff[s], w2, out(Ms[s], H), bias=bias[H], residual=xs[s]) for s in which])
     bench(f"[{tag}] dgrad FFN-down (B MN) *gelu'", lambda: [ops.GemmSpec(xs[s], w2, out(Ms[s], FF), b_major=MN, aux_in=ff[s], dact=ops.ACT_GELU) for s in which])
+    bench(f"[{tag}] dgrad FFN-down (B MN) *aux", lambda: [ops.GemmSpec(xs[s], w2, out(Ms[s], FF), b_major=MN, aux_in=ff[s], dact=ops.ACT_GELU, aux_is_grad=True) for s in which])
     bench(f"[{tag}] dgrad FFN-up (B MN) +res", lambda: [ops.GemmSpec(ff[s], w1, out(Ms[s], H), b_major=MN, residual=xs[s]) for s in which])
     bench(f"[{tag}] dgrad QKV K=2304 (B MN) +res", lambda: [ops.GemmSpec(t(Ms[s], 3 * H), wqkv, out(Ms[s], H), b_major=MN, residual=xs[s]) for s in which])
     bench(f"[{tag}] wgrad W2 [768,3072] splitK", lambda: [ops.GemmSpec(xs[s], ff[s], torch.zeros(H, FF, device=dev), a_major=MN, b_major=MN, accumulate=True, split_k=_wgrad_split(Ms[s], H, FF)) for s in which])
