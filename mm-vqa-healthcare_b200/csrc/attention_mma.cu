@@ -81,7 +81,7 @@ __device__ __forceinline__ int64_t mask_ld_bytes(const m3ae_attn_params_t& P) { 
 // gen: evaluate Philox (8 keys per evaluation) and, if a global cache is given, store the bytes there as well.
 template <int ROWS, int GROUPS, int NT>
 __device__ __forceinline__ void gen_keep_tile(uint64_t* sBits, const m3ae_attn_params_t& P, int b, int h, int row0, int c0, int tid, bool store) {
-  const uint32_t thr = drop_thr16(P.drop_p);
+  const uint32_t thr = drop_thr15(P.drop_p);
   uint8_t* sb = reinterpret_cast<uint8_t*>(sBits);
   const int64_t ld = mask_ld_bytes(P);
   for (int i = tid; i < ROWS * GROUPS; i += NT) {

@@ -6,6 +6,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "../../include/m3ae_b200.h"
 
@@ -155,27 +156,42 @@ __device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream
   return m;
 }
 
-// Attention-probability dropout.  Element (row_lin = (b*H+h)*Lq+i, key) takes the 16-bit lane key%8 of the Philox
-// evaluation with counter (row_lin, site<<32 | key/8): one evaluation covers 8 consecutive keys of a row.  The drop
-// threshold is p quantised to 1/65536 and the keep scale uses the quantised rate, so every kernel (tensor-core tiles
-// that generate 64x64 bit tiles cooperatively, generic per-element kernels) sees exactly the same mask and scale.
-__device__ __forceinline__ uint32_t drop_thr16(float p) { return (uint32_t)(p * 65536.0f + 0.5f); }
+// Attention-probability dropout.  One Philox evaluation with counter (row_lin = (b*H+h)*Lq+i, site<<32 | key/8) covers the
+// 8 consecutive keys 8g..8g+7 of a row: key 8g+2i takes the low 16-bit lane of word i, key 8g+2i+1 the high lane (the
+// order bf16x2 packing uses).  Only 15 bits of a lane are used: adding (0x8000 - thr15) to a 15-bit value carries into the
+// lane's top bit exactly when value >= thr15, so two keep decisions cost one AND and one ADD and never cross lanes.
+// The drop threshold is p quantised to 1/32768 and the keep scale uses the quantised rate, so every kernel (tcgen05
+// tiles, mma.sync tiles that cache 64x64 bit tiles, generic per-element kernels) sees exactly the same mask and scale.
+__device__ __forceinline__ uint32_t drop_thr15(float p) { return (uint32_t)(p * 32768.0f + 0.5f); }
 __device__ __forceinline__ float drop_keep_scale(float p) {
-  return p > 0.f ? 65536.0f / (65536.0f - (float)drop_thr16(p)) : 1.0f;
+  return p > 0.f ? 32768.0f / (32768.0f - (float)drop_thr15(p)) : 1.0f;
 }
-// keep bits for keys 8*key_group .. 8*key_group+7 of one attention row
-__device__ __forceinline__ uint32_t attn_keep_bits8(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key_group, uint32_t thr16) {
+// per-lane addend for attn_keep_flags
+__device__ __forceinline__ uint32_t drop_lane_add(uint32_t thr15) { return (0x8000u - thr15) * 0x00010001u; }
+// f[i] bit 15 = key 8g+2i kept, bit 31 = key 8g+2i+1 kept (all other bits zero)
+__device__ __forceinline__ void attn_keep_flags(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key_group, uint32_t lane_add,
+                                                uint32_t (&f)[4]) {
   Philox ph(seed);
   const uint4 r = ph(row_lin, (stream_id << 32) | (uint64_t)(uint32_t)key_group);
-  uint32_t m = 0;
-  m |= ((r.x & 0xFFFFu) >= thr16) ? 1u : 0u;   m |= ((r.x >> 16) >= thr16) ? 2u : 0u;
-  m |= ((r.y & 0xFFFFu) >= thr16) ? 4u : 0u;   m |= ((r.y >> 16) >= thr16) ? 8u : 0u;
-  m |= ((r.z & 0xFFFFu) >= thr16) ? 16u : 0u;  m |= ((r.z >> 16) >= thr16) ? 32u : 0u;
-  m |= ((r.w & 0xFFFFu) >= thr16) ? 64u : 0u;  m |= ((r.w >> 16) >= thr16) ? 128u : 0u;
-  return m;
+  f[0] = ((r.x & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[1] = ((r.y & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[2] = ((r.z & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[3] = ((r.w & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+}
+// flags -> byte with bit j = key 8g+j kept.  umulhi(f, 0x20004) = (f >> 15) + (f >> 30): bit 0 = low lane, bit 1 = high lane
+// (bit 16 repeats the high lane and ends up above bit 7).
+__device__ __forceinline__ uint32_t attn_flags_to_byte(const uint32_t (&f)[4]) {
+  const uint32_t t0 = __umulhi(f[0], 0x20004u), t1 = __umulhi(f[1], 0x20004u), t2 = __umulhi(f[2], 0x20004u), t3 = __umulhi(f[3], 0x20004u);
+  return ((t3 * 4u + t2) * 16u + (t1 * 4u + t0)) & 0xFFu;
+}
+// keep bits for keys 8*key_group .. 8*key_group+7 of one attention row
+__device__ __forceinline__ uint32_t attn_keep_bits8(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key_group, uint32_t thr15) {
+  uint32_t f[4];
+  attn_keep_flags(seed, stream_id, row_lin, key_group, drop_lane_add(thr15), f);
+  return attn_flags_to_byte(f);
 }
 __device__ __forceinline__ bool attn_dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t row_lin, int key, float p) {
-  return (attn_keep_bits8(seed, stream_id, row_lin, key >> 3, drop_thr16(p)) >> (key & 7)) & 1u;
+  return (attn_keep_bits8(seed, stream_id, row_lin, key >> 3, drop_thr15(p)) >> (key & 7)) & 1u;
 }
 
 // ---------------------------------------------------------------- warp helpers
@@ -282,8 +298,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// A barrier that never completes is a protocol bug: report it and trap instead of hanging the GPU (fail loudly).
+#ifndef M3AE_WATCHDOG_CYCLES
+#define M3AE_WATCHDOG_CYCLES 20000000000ll  // ~10 s at 2 GHz
+#endif
+static __device__ __noinline__ void mbar_timeout(uint32_t bar_addr, uint32_t parity) {
+  printf("m3ae: mbarrier wait timed out: block (%d,%d) thread %d barrier@smem+0x%x parity %u\n", (int)blockIdx.x, (int)blockIdx.y,
+         (int)threadIdx.x, bar_addr, parity);
+  __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > M3AE_WATCHDOG_CYCLES) mbar_timeout(smem_u32(bar), parity);
   }
 }
 

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   uint64_t* in_bar = bars + 2 * STAGES + 4;   // [NUM_EPI_WARPS][2]
   uint32_t* tmem_ptr_smem = (uint32_t*)(bars + NUM_BARS);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform by construction: say so
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -138,7 +138,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  if (warp == 0 && lane == 0) {
+  // Producer and MMA warps run their control flow with ALL lanes (convergent) and elect one lane per batch of
+  // asynchronous operations.  Issuing from inside an `if (lane == 0)` region makes the compiler feed every TMA / MMA
+  // operand into uniform registers through an ELECT + R2UR.BROADCAST waterfall loop in front of EACH instruction
+  // (~130 cycles per tcgen05.mma: as long as the 128-cycle MMA itself, so the issue thread paced the tensor pipe).
+  if (warp == 0) {
     // ===================== TMA producer =====================
     int stage = 0;
     uint32_t phase = 0;
@@ -147,28 +151,31 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       const TcProblem& q = P.p[u.p];
       for (int kb = u.kb0; kb < u.kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * STAGE_BYTES;
-        uint8_t* sb = sa + A_STAGE_BYTES;
-        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
-        if (q.a_major == M3AE_MAJOR_K) {
-          tma_load_2d(sa, &q.map_a, &full_bar[stage], kb * BK, u.m_blk * BM);
-        } else {
+        if (elect_one()) {
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_STAGE_BYTES;
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          if (q.a_major == M3AE_MAJOR_K) {
+            tma_load_2d(sa, &q.map_a, &full_bar[stage], kb * BK, u.m_blk * BM);
+          } else {
 #pragma unroll
-          for (int j = 0; j < BM / 64; ++j)
-            tma_load_2d(sa + j * (BK * 128), &q.map_a, &full_bar[stage], u.m_blk * BM + j * 64, kb * BK);
-        }
-        if (q.b_major == M3AE_MAJOR_K) {
-          tma_load_2d(sb, &q.map_b, &full_bar[stage], kb * BK, u.n_blk * BN);
-        } else {
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * (BK * 128), &q.map_a, &full_bar[stage], u.m_blk * BM + j * 64, kb * BK);
+          }
+          if (q.b_major == M3AE_MAJOR_K) {
+            tma_load_2d(sb, &q.map_b, &full_bar[stage], kb * BK, u.n_blk * BN);
+          } else {
 #pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_2d(sb + j * (BK * 128), &q.map_b, &full_bar[stage], u.n_blk * BN + j * 64, kb * BK);
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * (BK * 128), &q.map_b, &full_bar[stage], u.n_blk * BN + j * 64, kb * BK);
+          }
         }
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ===================== MMA issuer (single thread) =====================
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one elected lane per k-block) =====================
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -193,16 +200,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         tcgen05_fence_after();
         const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
         const uint32_t sb = sa + A_STAGE_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t da = make_smem_desc(sa + k * a_kstep, a_lbo, 1024);
-          const uint64_t db = make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
-          umma_f16(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = make_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+            umma_f16(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          if (kb + 1 == u.kb1) umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
         }
-        umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {

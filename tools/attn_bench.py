@@ -29,6 +29,8 @@ def run(Lq, Lk, drop=0.0):
         us = e0.elapsed_time(e1) * 1e3 / reps
         flops = mult * B * H * Lq * Lk * dh
         print(f"attn {name} Lq={Lq:4d} Lk={Lk:4d} drop={drop}: {us:8.1f} us  {flops / us / 1e6:7.1f} TFLOP/s (algorithmic {mult}*B*H*Lq*Lk*dh)")
-for (Lq, Lk) in [(325, 325), (325, 32), (32, 325), (32, 32)]:
-    for drop in (0.0, 0.1):
+shapes = [tuple(int(v) for v in t.split("x")) for t in os.environ.get("SHAPES", "325x325,325x32,32x325,32x32").split(",")]
+drops = [float(v) for v in os.environ.get("DROPS", "0.0,0.1").split(",")]
+for (Lq, Lk) in shapes:
+    for drop in drops:
         run(Lq, Lk, drop)
