@@ -36,7 +36,32 @@ template <> struct Vec<bf16> {
 
 constexpr int LN_WARPS = 4;
 
-// H == HV * 32 * Vec<T>::N exactly (768 or 1536 columns on this path).
+// 16-byte vector of T straight from memory (kept packed so that a prefetched row costs few registers)
+template <typename T>
+__device__ __forceinline__ uint4 ld_raw(const T* p) { return *reinterpret_cast<const uint4*>(p); }
+template <typename T> __device__ __forceinline__ void unpack_raw(const uint4& t, float (&v)[Vec<T>::N]);
+template <> __device__ __forceinline__ void unpack_raw<float>(const uint4& t, float (&v)[4]) {
+  v[0] = __uint_as_float(t.x); v[1] = __uint_as_float(t.y); v[2] = __uint_as_float(t.z); v[3] = __uint_as_float(t.w);
+}
+template <> __device__ __forceinline__ void unpack_raw<bf16>(const uint4& t, float (&v)[8]) {
+  float2 f;
+  f = unpack_bf16x2(t.x); v[0] = f.x; v[1] = f.y;
+  f = unpack_bf16x2(t.y); v[2] = f.x; v[3] = f.y;
+  f = unpack_bf16x2(t.z); v[4] = f.x; v[5] = f.y;
+  f = unpack_bf16x2(t.w); v[6] = f.x; v[7] = f.y;
+}
+// VN consecutive fp32 parameters (gamma / beta) as 16-byte loads
+template <int VN>
+__device__ __forceinline__ void ld_param(const float* p, float (&v)[VN]) {
+#pragma unroll
+  for (int q = 0; q < VN / 4; ++q) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p) + q);
+    v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+  }
+}
+
+// H == HV * 32 * Vec<T>::N exactly (768 or 1536 columns on this path).  One warp per row; gamma / beta come in as
+// 16-byte loads (the first version read them as scalars: 48 extra load instructions per row, 4x slower than the HBM bound).
 template <typename T, int HV>
 __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma,
                                                               const float* __restrict__ beta, T* __restrict__ y,
@@ -68,17 +93,21 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const T* __restri
 #pragma unroll
   for (int i = 0; i < HV; ++i) {
     const int c = (i * 32 + lane) * VN;
-    float o[VN];
+    float g[VN], b[VN], o[VN];
+    ld_param<VN>(gamma + c, g);
+    ld_param<VN>(beta + c, b);
 #pragma unroll
-    for (int j = 0; j < VN; ++j) o[j] = (v[i][j] - mean) * rstd * __ldg(gamma + c + j) + __ldg(beta + c + j);
+    for (int j = 0; j < VN; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
     Vec<T>::store(yr + c, o);
   }
 }
 
 // Backward: each warp walks rows row0, row0+stride, ... and keeps per-lane column partials of
 // dgamma / dbeta / colsum(dx) in registers; one smem reduction + one atomicAdd per column per CTA.
+// The next row's x and dy are already in flight (packed, 2*HV registers) while the current row is reduced.
+constexpr int LN_BWD_CTAS_PER_SM = 3;
 template <typename T, int HV>
-__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+__global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
                                                               const float* __restrict__ gamma, T* __restrict__ dx,
                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -90,32 +119,51 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restri
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[HV][VN], pg[HV][VN], pb[HV][VN], pc[HV][VN];
 #pragma unroll
-  for (int i = 0; i < HV; ++i)
+  for (int i = 0; i < HV; ++i) {
+    ld_param<VN>(gamma + (i * 32 + lane) * VN, g[i]);
 #pragma unroll
-    for (int j = 0; j < VN; ++j) {
-      g[i][j] = __ldg(gamma + (i * 32 + lane) * VN + j);
-      pg[i][j] = 0.f; pb[i][j] = 0.f; pc[i][j] = 0.f;
-    }
+    for (int j = 0; j < VN; ++j) { pg[i][j] = 0.f; pb[i][j] = 0.f; pc[i][j] = 0.f; }
+  }
   const float invH = 1.0f / (float)H;
-  for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < M; row += (int64_t)gridDim.x * LN_WARPS) {
-    const float mu = mean[row], rs = rstd[row];
-    float xh[HV][VN], gd[HV][VN];
-    float c1 = 0.f, c2 = 0.f;
+  const int64_t stride = (int64_t)gridDim.x * LN_WARPS;
+  int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp;
+  uint4 rx[HV], rdy[HV];
+  float mu = 0.f, rs = 0.f;
+  if (row < M) {
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
-      const int c = (i * 32 + lane) * VN;
+      rx[i] = ld_raw(x + row * H + (i * 32 + lane) * VN);
+      rdy[i] = ld_raw(dy + row * H + (i * 32 + lane) * VN);
+    }
+    mu = mean[row]; rs = rstd[row];
+  }
+  for (; row < M; row += stride) {
+    float xh[HV][VN], gd[HV][VN];
+    float c1 = 0.f, c2 = 0.f;
+    const float mu_c = mu, rs_c = rs;
+#pragma unroll
+    for (int i = 0; i < HV; ++i) {
       float dv[VN];
-      Vec<T>::load(x + row * H + c, xh[i]);
-      Vec<T>::load(dy + row * H + c, dv);
+      unpack_raw<T>(rx[i], xh[i]);
+      unpack_raw<T>(rdy[i], dv);
 #pragma unroll
       for (int j = 0; j < VN; ++j) {
-        xh[i][j] = (xh[i][j] - mu) * rs;
+        xh[i][j] = (xh[i][j] - mu_c) * rs_c;
         pg[i][j] += dv[j] * xh[i][j];
         pb[i][j] += dv[j];
         gd[i][j] = dv[j] * g[i][j];
         c1 += gd[i][j];
         c2 += gd[i][j] * xh[i][j];
       }
+    }
+    const int64_t nrow = row + stride;
+    if (nrow < M) {  // prefetch: the loads fly during the reductions and the dropout regeneration below
+#pragma unroll
+      for (int i = 0; i < HV; ++i) {
+        rx[i] = ld_raw(x + nrow * H + (i * 32 + lane) * VN);
+        rdy[i] = ld_raw(dy + nrow * H + (i * 32 + lane) * VN);
+      }
+      mu = mean[nrow]; rs = rstd[nrow];
     }
     c1 = warp_sum(c1) * invH;
     c2 = warp_sum(c2) * invH;
@@ -124,7 +172,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(const T* __restri
       const int c = (i * 32 + lane) * VN;
       float o[VN];
 #pragma unroll
-      for (int j = 0; j < VN; ++j) o[j] = rs * (gd[i][j] - c1 - xh[i][j] * c2);
+      for (int j = 0; j < VN; ++j) o[j] = rs_c * (gd[i][j] - c1 - xh[i][j] * c2);
       Vec<T>::store(dx + row * H + c, o);
       if (dx_drop != nullptr) {
         // gradient through the hidden dropout of the producing GEMM epilogue: same Philox stream, element = row*H+col
@@ -244,7 +292,7 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   if (drop_p == 0.f) dx_drop = nullptr;
   M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
   int64_t want = (M + LN_WARPS - 1) / LN_WARPS;
-  const int64_t cap = (int64_t)sm_count() * 4;
+  const int64_t cap = (int64_t)sm_count() * LN_BWD_CTAS_PER_SM;  // persistent: exactly the resident CTAs
   const unsigned grid = (unsigned)(want < cap ? want : cap);
   const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
 #define LN_BWD(T, HV)                                                                                                     \
