@@ -169,6 +169,17 @@ int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int
 /* dst[i] = (dst_dtype) src[i]  — fp32 master parameters -> bf16 operand cache, activations casts. */
 int m3ae_cast(const void* src, int32_t src_dtype, void* dst, int32_t dst_dtype, int64_t n, void* stream);
 
+/* Up to M3AE_MAX_CAST_GROUP casts in ONE launch: a layer's fp32 master parameters (reference state-dict tensors,
+ * bert_model.py:214-452) -> its compute-dtype operand cache, refreshed before every training forward. */
+#define M3AE_MAX_CAST_GROUP 16
+typedef struct m3ae_cast_item {
+  const void* src;
+  void* dst;
+  int64_t n;
+  int32_t src_dtype, dst_dtype;
+} m3ae_cast_item_t;
+int m3ae_cast_group(const m3ae_cast_item_t* items, int32_t n, void* stream);
+
 /* out[r, :] = a[r, :] + b[:]  (row-broadcast add; modality type embedding, m3ae_module.py:260-263). */
 int m3ae_add_rowvec(const void* a, const float* b, void* out, int64_t M, int32_t N, int32_t in_dtype, int32_t out_dtype,
                     void* stream);

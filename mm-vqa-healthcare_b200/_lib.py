@@ -37,6 +37,13 @@ class GemmProblem(C.Structure):
     ]
 
 
+class CastItem(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("n", C.c_int64), ("src_dtype", C.c_int32), ("dst_dtype", C.c_int32)]
+
+
+MAX_CAST_GROUP = 16
+
+
 class AttnParams(C.Structure):
     _fields_ = [
         ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p),
@@ -68,6 +75,7 @@ SIGNATURES = {
                                      C.c_float, C.c_uint64, C.c_uint64, C.c_void_p]),
     "m3ae_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.c_void_p]),
     "m3ae_cast": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]),
+    "m3ae_cast_group": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),
     "m3ae_add_rowvec": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                   C.c_void_p]),
     "m3ae_dropout_apply": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_float, C.c_uint64,

@@ -68,6 +68,7 @@ int layernorm_fwd(const void*, const float*, const float*, void*, float*, float*
 int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, void*, float, uint64_t, uint64_t, cudaStream_t);
 int colsum(const void*, float*, int64_t, int, int64_t, int, cudaStream_t);
 int cast(const void*, int, void*, int, int64_t, cudaStream_t);
+int cast_group(const m3ae_cast_item_t*, int, cudaStream_t);
 int add_rowvec(const void*, const float*, void*, int64_t, int, int, int, cudaStream_t);
 int dropout_apply(const void*, void*, int64_t, int, int64_t, float, uint64_t, uint64_t, int, cudaStream_t);
 int decode_attn(const void*, int64_t, const void*, const void*, int64_t, int64_t, int64_t, int64_t, void*, int64_t, int, int, int, int, float, int, cudaStream_t);
@@ -141,6 +142,16 @@ int m3ae_cast(const void* src, int32_t sd, void* dst, int32_t dd, int64_t n, voi
   ARCH_GATE();
   M3AE_CHECK((src && dst) || n == 0, M3AE_ERR_INVALID, "cast: null pointer");
   return cast(src, sd, dst, dd, n, (cudaStream_t)stream);
+}
+int m3ae_cast_group(const m3ae_cast_item_t* items, int32_t n, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(items != nullptr && n >= 1 && n <= M3AE_MAX_CAST_GROUP, M3AE_ERR_INVALID, "cast_group: need 1..%d items, got %d", M3AE_MAX_CAST_GROUP, n);
+  for (int i = 0; i < n; ++i) {
+    M3AE_CHECK((items[i].src && items[i].dst) || items[i].n == 0, M3AE_ERR_INVALID, "cast_group: null pointer in item %d", i);
+    M3AE_CHECK((items[i].src_dtype == M3AE_F32 || items[i].src_dtype == M3AE_BF16) && (items[i].dst_dtype == M3AE_F32 || items[i].dst_dtype == M3AE_BF16),
+               M3AE_ERR_INVALID, "cast_group: bad dtype in item %d", i);
+  }
+  return cast_group(items, n, (cudaStream_t)stream);
 }
 int m3ae_add_rowvec(const void* a, const float* b, void* out, int64_t M, int32_t N, int32_t in_dtype, int32_t out_dtype, void* stream) {
   ARCH_GATE();

@@ -246,6 +246,50 @@ __global__ void cast_f32_bf16_vec_kernel(const float4* __restrict__ src, uint4* 
   }
 }
 
+// One launch for a whole list of casts (a layer's 9 weights + 5 biases -> its operand cache): blockIdx.y = item.
+struct CastGroup {
+  const void* src[M3AE_MAX_CAST_GROUP];
+  void* dst[M3AE_MAX_CAST_GROUP];
+  int64_t n[M3AE_MAX_CAST_GROUP];
+  int8_t sd[M3AE_MAX_CAST_GROUP], dd[M3AE_MAX_CAST_GROUP];
+};
+__global__ void cast_group_kernel(const __grid_constant__ CastGroup G) {
+  const int it = blockIdx.y;
+  const int64_t n = G.n[it];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int sd = G.sd[it], dd = G.dd[it];
+  if (sd == M3AE_F32 && dd == M3AE_BF16) {
+    const float* src = (const float*)G.src[it];
+    bf16* dst = (bf16*)G.dst[it];
+    if (n % 8 == 0 && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
+      const float4* s4 = (const float4*)src;
+      uint4* d4 = (uint4*)dst;
+      for (int64_t i = t0; i < n / 8; i += stride) {
+        const float4 a = __ldg(s4 + 2 * i), b = __ldg(s4 + 2 * i + 1);
+        uint4 o;
+        o.x = pack_bf16x2(a.x, a.y); o.y = pack_bf16x2(a.z, a.w);
+        o.z = pack_bf16x2(b.x, b.y); o.w = pack_bf16x2(b.z, b.w);
+        d4[i] = o;
+      }
+    } else {
+      for (int64_t i = t0; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i]);
+    }
+  } else if (sd == M3AE_F32 && dd == M3AE_F32) {
+    const float* src = (const float*)G.src[it];
+    float* dst = (float*)G.dst[it];
+    for (int64_t i = t0; i < n; i += stride) dst[i] = src[i];
+  } else if (sd == M3AE_BF16 && dd == M3AE_F32) {
+    const bf16* src = (const bf16*)G.src[it];
+    float* dst = (float*)G.dst[it];
+    for (int64_t i = t0; i < n; i += stride) dst[i] = __bfloat162float(src[i]);
+  } else {
+    const bf16* src = (const bf16*)G.src[it];
+    bf16* dst = (bf16*)G.dst[it];
+    for (int64_t i = t0; i < n; i += stride) dst[i] = src[i];
+  }
+}
+
 template <typename TI, typename TO>
 __global__ void add_rowvec_kernel(const TI* __restrict__ a, const float* __restrict__ b, TO* __restrict__ out, int64_t M, int N) {
   const int64_t total = M * N;
@@ -340,6 +384,27 @@ int cast(const void* src, int sd, void* dst, int dd, int64_t n, cudaStream_t st)
     else if (sd == M3AE_F32 && dd == M3AE_F32) cast_kernel<float, float><<<grid, threads, 0, st>>>((const float*)src, (float*)dst, n);
     else cast_kernel<bf16, bf16><<<grid, threads, 0, st>>>((const bf16*)src, (bf16*)dst, n);
   }
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int cast_group(const m3ae_cast_item_t* items, int n, cudaStream_t st) {
+  CastGroup G;
+  memset(&G, 0, sizeof(G));
+  int64_t nmax = 0;
+  for (int i = 0; i < n; ++i) {
+    G.src[i] = items[i].src; G.dst[i] = items[i].dst; G.n[i] = items[i].n;
+    G.sd[i] = (int8_t)items[i].src_dtype; G.dd[i] = (int8_t)items[i].dst_dtype;
+    if (items[i].n > nmax) nmax = items[i].n;
+  }
+  if (nmax == 0) return M3AE_OK;
+  const int threads = 256;
+  int64_t b = (nmax / 8 + threads - 1) / threads;
+  const int64_t cap = (int64_t)sm_count() * 2;
+  if (b < 1) b = 1;
+  dim3 grid((unsigned)(b < cap ? b : cap), (unsigned)n);
+  cast_group_kernel<<<grid, threads, 0, st>>>(G);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

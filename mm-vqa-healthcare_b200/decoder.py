@@ -121,6 +121,10 @@ class Decoder(nn.Module):
         if not cross_attn_feats.is_cuda:
             raise RuntimeError("Decoder (B200) needs CUDA tensors: there is no CPU fallback")
         dt = self.compute_dtype
+        if torch.is_grad_enabled():
+            # a differentiated forward is followed by an optimizer step; fused optimizers do not bump the parameters'
+            # version counters, so the greedy path's operand cache cannot be trusted afterwards
+            self._cache = {}
         B, T = padded_targets.shape
         Lm, D = cross_attn_feats.shape[1], self.d_model
         dev = cross_attn_feats.device

@@ -49,17 +49,23 @@ NP = len(PARAM_NAMES)  # 26
 class LayerOperands:
     """Compute-dtype operand cache of one layer's fp32 master parameters: fused [Wq;Wk;Wv] and [Wk2;Wv2] weights
     (one N=2304 / N=1536 GEMM instead of three / two) cast to bf16 (product path) or copied as fp32 (parity path).
-    Buffers are allocated once and refreshed IN PLACE whenever a parameter's version counter moves (i.e. after every
-    optimizer step), so launch descriptors that point at them stay valid.  Also owns the layer's workspace pool."""
+    Buffers are allocated once and refreshed IN PLACE by one grouped cast launch, so launch descriptors that point at
+    them stay valid.  Refresh policy: always before a forward that will be differentiated (the optimizer moves the
+    masters between two such forwards, and fused optimizers — torch.optim.AdamW(fused=True) — do NOT bump the
+    parameters' version counters, so staleness cannot be detected), and once more on the first forward after one;
+    consecutive no-grad forwards re-use the cache while (address, version) of every parameter is unchanged.
+    Also owns the layer's workspace pool."""
 
     def __init__(self):
         self.key = None
         self.alloc_key = None
+        self.cast_key = None
+        self.volatile = True
         self.workspaces = []
 
-    def get(self, params, dtype):
+    def get(self, params, dtype, will_train=True):
         key = (dtype,) + tuple((p.data_ptr(), p._version) for p in params)
-        if key == self.key:
+        if key == self.key and not self.volatile and not will_train:
             return self
         dev = params[0].device
         H = params[WQ].shape[1]
@@ -74,19 +80,27 @@ class LayerOperands:
                 self.bkv2 = torch.empty(2 * H, dtype=torch.float32, device=dev)
                 self.wo, self.wq2, self.wo2, self.w1, self.w2 = buf(H, H), buf(H, H), buf(H, H), buf(FF, H), buf(H, FF)
                 self.alloc_key = alloc_key
+                self.cast_key = None
                 self.workspaces = []  # descriptors built on the old buffers are stale
-            for i, idx in enumerate((WQ, WK, WV)):
-                ops.cast(params[idx].detach(), self.wqkv[i * H:(i + 1) * H])
-                ops.cast(params[(BQ, BK, BV)[i]].detach(), self.bqkv[i * H:(i + 1) * H])
-            for i, idx in enumerate((WK2, WV2)):
-                ops.cast(params[idx].detach(), self.wkv2[i * H:(i + 1) * H])
-                ops.cast(params[(BK2, BV2)[i]].detach(), self.bkv2[i * H:(i + 1) * H])
-            ops.cast(params[WO].detach(), self.wo)
-            ops.cast(params[WQ2].detach(), self.wq2)
-            ops.cast(params[WO2].detach(), self.wo2)
-            ops.cast(params[W1].detach(), self.w1)
-            ops.cast(params[W2].detach(), self.w2)
+            cast_key = tuple(p.data_ptr() for p in params)
+            if cast_key != self.cast_key:
+                pairs = []
+                for i, idx in enumerate((WQ, WK, WV)):
+                    pairs.append((params[idx].detach(), self.wqkv[i * H:(i + 1) * H]))
+                    pairs.append((params[(BQ, BK, BV)[i]].detach(), self.bqkv[i * H:(i + 1) * H]))
+                for i, idx in enumerate((WK2, WV2)):
+                    pairs.append((params[idx].detach(), self.wkv2[i * H:(i + 1) * H]))
+                    pairs.append((params[(BK2, BV2)[i]].detach(), self.bkv2[i * H:(i + 1) * H]))
+                pairs += [(params[WO].detach(), self.wo), (params[WQ2].detach(), self.wq2), (params[WO2].detach(), self.wo2),
+                          (params[W1].detach(), self.w1), (params[W2].detach(), self.w2)]
+                for src, _ in pairs:
+                    if not src.is_contiguous() or src.dtype != torch.float32:
+                        raise ValueError("BertCrossLayer (B200) expects contiguous fp32 master parameters")
+                self.casts = ops.CastGroup(pairs)
+                self.cast_key = cast_key
+            self.casts.run()
         self.key = key
+        self.volatile = will_train
         return self
 
     def acquire(self, key):
@@ -185,7 +199,7 @@ class _Attn:
         ops.L.check(self.fn(self.ref, stream), "m3ae_attn")
 
 
-def _forward_streams(cfg, training, streams, want_probs):
+def _forward_streams(cfg, training, streams, want_probs, will_train=True):
     """streams: list of dicts(hidden, encoder, mask, enc_mask, params(list of 26), operands(LayerOperands))."""
     dt = cfg.compute_dtype
     be = cfg.gemm_backend
@@ -202,7 +216,7 @@ def _forward_streams(cfg, training, streams, want_probs):
         dev = h.device
         key = (B, Lq, Lk, H, dt, dev, pa, ph, bool(want_probs), s["mask"] is None, s["enc_mask"] is None,
                tuple(p.data_ptr() for p in params))
-        w = s["operands"].get(params, dt)
+        w = s["operands"].get(params, dt, will_train)
         st = s["operands"].acquire(key)
         st.B, st.Lq, st.H, st.Lk = B, Lq, H, Lk
         st.dh = H // nh
@@ -465,11 +479,11 @@ class _CrossLayersFn(torch.autograd.Function):
         for i in range(n_streams):
             c = flat[i * per:(i + 1) * per]
             streams.append(dict(hidden=c[0], encoder=c[1], mask=c[2], enc_mask=c[3], params=list(c[4:]), operands=operands[i]))
-        S = _forward_streams(cfg, training, streams, want_probs)
+        needs_bwd = any(ctx.needs_input_grad)  # grad mode is off inside forward(); this reflects the caller's mode
+        S = _forward_streams(cfg, training, streams, want_probs, will_train=needs_bwd)
         ctx.cfg = cfg
         ctx.S = S
         ctx.in_dtypes = [(s["hidden"].dtype, s["encoder"].dtype) for s in streams]
-        needs_bwd = any(ctx.needs_input_grad)  # grad mode is off inside forward(); this reflects the caller's mode
         outs = []
         nondiff = []
         for st, s in zip(S, streams):

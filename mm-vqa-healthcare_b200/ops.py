@@ -210,6 +210,23 @@ def cast(src, dst):
     return dst
 
 
+class CastGroup:
+    """A cached list of (src, dst) casts issued as ONE launch (m3ae_cast_group)."""
+
+    def __init__(self, pairs):
+        assert 1 <= len(pairs) <= L.MAX_CAST_GROUP
+        for src, dst in pairs:
+            _need_cuda(src, dst)
+            assert src.is_contiguous() and dst.is_contiguous() and src.numel() == dst.numel()
+        self.keep = pairs
+        self.n = len(pairs)
+        self.arr = (L.CastItem * self.n)(*[L.CastItem(s.data_ptr(), d.data_ptr(), s.numel(), _code(s.dtype), _code(d.dtype)) for s, d in pairs])
+        self.fn = L.load().m3ae_cast_group
+
+    def run(self):
+        L.check(self.fn(self.arr, self.n, _stream()), "m3ae_cast_group")
+
+
 def add_rowvec(a, b, out):
     _need_cuda(a, b, out)
     assert a.is_contiguous() and out.is_contiguous() and b.dtype == torch.float32 and b.is_contiguous()

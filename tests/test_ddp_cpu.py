@@ -31,7 +31,7 @@ def _worker(rank, world, port, q):
         xs = x[rank * 4:(rank + 1) * 4]
         m(xs).square().sum().backward()
         red.wait()
-    q.put((rank, [p.grad.clone() for p in m.parameters()]))
+    q.put((rank, [p.grad.numpy().copy() for p in m.parameters()]))  # by value: fd-shared tensors die with the worker
     dist.barrier()
     dist.destroy_process_group()
 
@@ -53,4 +53,4 @@ def test_two_rank_gradient_average_matches_single_process():
     (m(x).square().sum() / 2).backward()  # mean over 2 ranks of per-rank sums
     for r in range(2):
         for a, p in zip(got[r], m.parameters()):
-            assert torch.allclose(a, p.grad, rtol=1e-5, atol=1e-6)
+            assert torch.allclose(torch.from_numpy(a), p.grad, rtol=1e-5, atol=1e-6)

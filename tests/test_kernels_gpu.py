@@ -207,6 +207,12 @@ def test_elementwise_helpers():
     xo = torch.empty(1003, dtype=torch.bfloat16, device=DEV)
     ops.cast(rnd(1003), xo)  # odd length -> scalar path
     assert torch.equal(xo, rnd(1003).to(torch.bfloat16))
+    srcs = [rnd(768, 768, seed=1), rnd(768, seed=2), rnd(1003, seed=3), rnd(3072, 768, seed=4), rnd(77, seed=6).to(torch.bfloat16)]
+    dsts = [torch.empty_like(srcs[0], dtype=torch.bfloat16), torch.empty_like(srcs[1]), torch.empty_like(srcs[2], dtype=torch.bfloat16),
+            torch.empty_like(srcs[3], dtype=torch.bfloat16), torch.empty_like(srcs[4], dtype=torch.float32)]
+    ops.CastGroup(list(zip(srcs, dsts))).run()  # one launch: vector, copy, scalar-tail, large and widening items
+    for s_, d_ in zip(srcs, dsts):
+        assert torch.equal(d_, s_.to(d_.dtype))
     v = rnd(768, seed=5)
     o = torch.empty_like(xb)
     ops.add_rowvec(x, v, o)

@@ -131,3 +131,30 @@ def test_cpu_tensors_fail_loudly():
     layer = BertCrossLayer(fusion_cfg())
     with pytest.raises(RuntimeError, match="no CPU"):
         layer(torch.zeros(1, 32, 768), torch.zeros(1, 325, 768))
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_operand_cache_follows_optimizer_steps(fused):
+    """The bf16 operand cache must track the fp32 masters through optimizer steps.  torch's fused AdamW updates
+    parameters WITHOUT bumping their version counters, so version-keyed caching would silently keep training (and then
+    evaluating) on the initial weights."""
+    layer = make_layer(5, torch.bfloat16).train()
+    opt = torch.optim.AdamW(layer.parameters(), lr=1e-2, fused=fused)
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(2, 32, 768, generator=g).to(DEV)
+    y = torch.randn(2, 325, 768, generator=g).to(DEV)
+    for _ in range(2):
+        opt.zero_grad(set_to_none=True)
+        layer(x, y)[0].float().square().mean().backward()
+        opt.step()
+    fresh = BertCrossLayer(fusion_cfg(), compute_dtype=torch.bfloat16).to(DEV)
+    fresh.load_state_dict(layer.state_dict())
+    with torch.no_grad():
+        o_eval = layer.eval()(x, y)[0]          # first no-grad forward after training: must re-cast
+        o_eval2 = layer(x, y)[0]                # second: may use the cache
+        o_fresh = fresh.eval()(x, y)[0]
+    assert torch.equal(o_eval, o_fresh) and torch.equal(o_eval2, o_fresh)
+    o_train = layer.train()(x.requires_grad_(True), y)[0]
+    assert torch.equal(o_train.detach(), o_fresh)
+    sd0 = O.make_cross_layer_state(5)
+    assert rel(layer.intermediate.dense.weight, sd0["intermediate.dense.weight"]) > 1e-3  # the masters did move
