@@ -88,6 +88,7 @@ SIGNATURES = {
                                      C.c_int32, C.c_void_p]),
     "m3ae_set_attention_backend": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
+    "m3ae_set_gemm_cta_pair": (C.c_int, [C.c_int32]),
 }
 
 _lib = None

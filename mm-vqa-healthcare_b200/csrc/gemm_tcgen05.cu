@@ -23,10 +23,7 @@ constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 3;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
-constexpr int B_STAGE_BYTES = BN * BK * 2;
-constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4..11 epilogue
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
@@ -35,9 +32,21 @@ constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 constexpr int EPI_BUF_BYTES = 32 * 64;
 constexpr int EPI_WARP_BYTES = 4 * EPI_BUF_BYTES;
 constexpr int EPI_BYTES = NUM_EPI_WARPS * EPI_WARP_BYTES;
-constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
 constexpr int BIAS_BYTES = NUM_EPI_WARPS * 128 * 4;  // every epilogue warp stages the 128 bias values of its column half
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
+// CTAS = 1: one CTA computes a 128x256 tile (tcgen05.mma.cta_group::1).  CTAS = 2: a CTA PAIR (cluster of 2 on one TPC)
+// computes a 256x256 tile with tcgen05.mma.cta_group::2 — each CTA stages its own 128 rows of A and HALF of B
+// (128 of the 256 columns), so the operand bytes an SM reads from shared memory per MMA drop from 12 KB to 8 KB
+// (96 -> 64 B/clk against the 128 B/clk an SM can deliver) and a stage shrinks from 48 KB to 32 KB (4 stages instead of 3).
+template <int CTAS>
+struct Cfg {
+  static constexpr int TILE_M = BM * CTAS;
+  static constexpr int B_ROWS = BN / CTAS;  // B rows (output columns) staged per CTA
+  static constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = CTAS == 1 ? 3 : 4;
+  static constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
+};
 constexpr int MAX_GROUP = 4;
 
 struct alignas(64) TcProblem {
@@ -92,9 +101,20 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& P, int unit) {
   return u;
 }
 
+template <int CTAS>
 __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ TcParams P) {
+  using C = Cfg<CTAS>;
+  constexpr int STAGES = C::STAGES;
+  constexpr int STAGE_BYTES = C::STAGE_BYTES;
+  constexpr int NUM_BARS = C::NUM_BARS;
+  constexpr int TILE_M = C::TILE_M;
   extern __shared__ uint8_t smem_raw[];
+  // the dynamic shared window starts at the same offset in both CTAs of a pair, so this rounding is identical in both
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  // CTA pair: rank 0 (leader) issues the MMAs for both; work is distributed per pair
+  const int rank = CTAS == 2 ? (int)cluster_ctarank() : 0;
+  const int worker = CTAS == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int n_workers = CTAS == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
   float* bias_smem = (float*)(epi_smem + EPI_BYTES);
   uint64_t* bars = (uint64_t*)(epi_smem + EPI_BYTES + BIAS_BYTES);
@@ -127,14 +147,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], NUM_EPI_WARPS);
+      mbar_init(&tmem_empty[s], NUM_EPI_WARPS * CTAS);  // the leader's barrier collects the epilogue warps of both CTAs
     }
     for (int s = 0; s < 2 * NUM_EPI_WARPS; ++s) mbar_init(&in_bar[s], 1);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_ptr_smem);
+  if (warp == 2) {
+    if (CTAS == 2) tmem_alloc_pair<TMEM_COLS>(tmem_ptr_smem);
+    else tmem_alloc<TMEM_COLS>(tmem_ptr_smem);
+  }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer's barriers must be initialised before anything remote arrives on them
+  else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
@@ -146,46 +170,50 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     // ===================== TMA producer =====================
     int stage = 0;
     uint32_t phase = 0;
-    for (int unit = blockIdx.x; unit < P.total_units; unit += gridDim.x) {
+    for (int unit = worker; unit < P.total_units; unit += n_workers) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
+      const int a_row0 = u.m_blk * TILE_M + rank * BM;         // this CTA's 128 rows of A
+      const int b_row0 = u.n_blk * BN + rank * C::B_ROWS;      // this CTA's share of B (all 256 columns when alone)
       for (int kb = u.kb0; kb < u.kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
-          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+            if (CTAS == 2) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1);
+            else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+          };
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], STAGE_BYTES * CTAS);  // bytes of both CTAs land on the leader's barrier
           if (q.a_major == M3AE_MAJOR_K) {
-            tma_load_2d(sa, &q.map_a, &full_bar[stage], kb * BK, u.m_blk * BM);
+            load(sa, &q.map_a, kb * BK, a_row0);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(sa + j * (BK * 128), &q.map_a, &full_bar[stage], u.m_blk * BM + j * 64, kb * BK);
+            for (int j = 0; j < BM / 64; ++j) load(sa + j * (BK * 128), &q.map_a, a_row0 + j * 64, kb * BK);
           }
           if (q.b_major == M3AE_MAJOR_K) {
-            tma_load_2d(sb, &q.map_b, &full_bar[stage], kb * BK, u.n_blk * BN);
+            load(sb, &q.map_b, kb * BK, b_row0);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sb + j * (BK * 128), &q.map_b, &full_bar[stage], u.n_blk * BN + j * 64, kb * BK);
+            for (int j = 0; j < C::B_ROWS / 64; ++j) load(sb + j * (BK * 128), &q.map_b, b_row0 + j * 64, kb * BK);
           }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (one elected lane per k-block) =====================
+  } else if (warp == 1 && rank == 0) {
+    // ===================== MMA issuer (one elected lane per k-block; the leader CTA of a pair) =====================
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int unit = blockIdx.x; unit < P.total_units; unit += gridDim.x) {
+    for (int unit = worker; unit < P.total_units; unit += n_workers) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
       const uint32_t idesc = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
                              ((uint32_t)q.a_major << 15) | ((uint32_t)q.b_major << 16) | ((uint32_t)(BN >> 3) << 17) |
-                             ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)(TILE_M >> 4) << 24);
       // K-major: 8-row groups 1024 B apart, K advance = 32 B inside the swizzle row.
       // MN-major: 64-element column groups BK*128 B apart (LBO), 8-k groups 1024 B apart (SBO), K advance = 16 rows.
       const uint32_t a_lbo = q.a_major == M3AE_MAJOR_K ? 16u : (uint32_t)(BK * 128);
@@ -205,10 +233,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = make_smem_desc(sa + k * a_kstep, a_lbo, 1024);
             const uint64_t db = make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
-            umma_f16(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
+            if (CTAS == 2) umma_f16_pair(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
+            else umma_f16(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
-          if (kb + 1 == u.kb1) umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+          if (CTAS == 2) {
+            umma_commit_pair(&empty_bar[stage]);  // frees the smem slot in BOTH CTAs once these MMAs have read it
+            if (kb + 1 == u.kb1) umma_commit_pair(&tmem_full[acc]);
+          } else {
+            umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+            if (kb + 1 == u.kb1) umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -223,15 +257,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t iph0 = 0, iph1 = 0;  // phases of this warp's two in-buffer barriers
-    for (int unit = blockIdx.x; unit < P.total_units; unit += gridDim.x) {
+    auto release_acc = [&](int a) {  // this warp is done reading accumulator `a`
+      if (CTAS == 2 && rank != 0) mbar_arrive_cluster(&tmem_empty[a], 0);
+      else mbar_arrive(&tmem_empty[a]);
+    };
+    for (int unit = worker; unit < P.total_units; unit += n_workers) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
       const EpiDev& epi = q.epi;
+      const int tile_row0 = u.m_blk * TILE_M + rank * BM;  // first output row of this CTA's 128-lane accumulator
       if (q.epi_fast == 2) {
         // ---- fp32 accumulate (out += alpha * acc): 32x32 fp32 tiles staged in swizzled smem, added into global memory
         //      by TMA reductions.  One bulk reduction replaces 1024 scattered RED.ADD.F32 (lane = row: 32 lines/instr).
         uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
-        const int row0 = u.m_blk * BM + quad * 32;
+        const int row0 = tile_row0 + quad * 32;
         const int col_base = u.n_blk * BN + half * 128;
         const int nchunks = (row0 < q.M) ? min(4, (q.N - col_base + 31) / 32) : 0;
         const float alpha = epi.alpha;
@@ -262,7 +301,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(&tmem_empty[acc]);
+          release_acc(acc);
           tma_store_wait_read<0>();  // the next unit may be a bf16 problem whose TMA loads land in these bytes
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -272,7 +311,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         // ---- TMA-staged bf16 epilogue: coalesced in/out through swizzled smem sub-tiles of 32 rows x 32 columns
         uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
         uint64_t* ibar = in_bar + 2 * e;
-        const int row0 = u.m_blk * BM + quad * 32;
+        const int row0 = tile_row0 + quad * 32;
         const int col_base = u.n_blk * BN + half * 128;
         const int nchunks = min(4, (q.N - col_base + 31) / 32);  // <= 0: this warp's half lies outside N
         const int64_t row = (int64_t)row0 + lane;
@@ -422,13 +461,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) release_acc(acc);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         continue;
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
-      const int64_t row = (int64_t)u.m_blk * BM + quad * 32 + lane;
+      const int64_t row = (int64_t)tile_row0 + quad * 32 + lane;
       const bool row_ok = row < q.M;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
@@ -482,17 +521,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       }
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) release_acc(acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait_all();  // staged output tiles must be drained before the CTA's smem goes away
   }
 
   tcgen05_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // neither CTA may leave while its partner still multicasts onto its barriers / reads its smem
+  else __syncthreads();
   if (warp == 2) {
     tcgen05_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (CTAS == 2) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+    else tmem_dealloc<TMEM_COLS>(tmem_base);
   }
 }
 
@@ -589,16 +630,49 @@ void epi_to_dev(const m3ae_gemm_epilogue_t& e, EpiDev* d);
 void count_launch();
 
 bool force_generic_epilogue = false;  // test hook (m3ae_set_gemm_epilogue): run the per-element epilogue everywhere
+int gemm_cta_pair_mode = 0;           // m3ae_set_gemm_cta_pair: 0 auto, 1 always single CTA, 2 always CTA pair
 
-int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t stream) {
-  M3AE_CHECK(n >= 1 && n <= MAX_GROUP, M3AE_ERR_INVALID, "gemm group size %d not in [1,%d]", n, MAX_GROUP);
+namespace {
+template <int CTAS>
+int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CTAS>::SMEM_BYTES);
   });
-  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", SMEM_BYTES,
+  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CTAS>::SMEM_BYTES,
              cudaGetErrorString(attr_err));
+  const int workers_max = sm_count() / CTAS;
+  const int workers = units < workers_max ? units : workers_max;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(workers * CTAS));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = Cfg<CTAS>::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CTAS>, P));
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+}  // namespace
+
+int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t stream) {
+  M3AE_CHECK(n >= 1 && n <= MAX_GROUP, M3AE_ERR_INVALID, "gemm group size %d not in [1,%d]", n, MAX_GROUP);
+  // CTA pairs (256-row tiles) unless every problem fits one 128-row tile (the decoder's per-token GEMMs, M = batch:
+  // there the second CTA would only multiply zero rows and halve the number of SMs streaming the weights).
+  int max_m = 0;
+  for (int i = 0; i < n; ++i) max_m = probs[i].M > max_m ? probs[i].M : max_m;
+  const int ctas = gemm_cta_pair_mode == 1 ? 1 : gemm_cta_pair_mode == 2 ? 2 : (max_m > BM ? 2 : 1);
+  const int tile_m = BM * ctas;
+  const int b_rows = BN / ctas;
   TcParams P;
   memset(&P, 0, sizeof(P));
   P.n_problems = n;
@@ -615,7 +689,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     if (g.a_major == M3AE_MAJOR_K) rc = encode_map(&q.map_a, g.a, g.M, g.K, g.lda, BM);
     else rc = encode_map(&q.map_a, g.a, g.K, g.M, g.lda, BK);
     if (rc) return rc;
-    if (g.b_major == M3AE_MAJOR_K) rc = encode_map(&q.map_b, g.b, g.N, g.K, g.ldb, BN);
+    if (g.b_major == M3AE_MAJOR_K) rc = encode_map(&q.map_b, g.b, g.N, g.K, g.ldb, b_rows);
     else rc = encode_map(&q.map_b, g.b, g.K, g.N, g.ldb, BK);
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
@@ -644,7 +718,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     }
     q.M = g.M; q.N = g.N; q.K = g.K;
     q.a_major = g.a_major; q.b_major = g.b_major;
-    q.tiles_m = (g.M + BM - 1) / BM;
+    q.tiles_m = (g.M + tile_m - 1) / tile_m;
     q.tiles_n = (g.N + BN - 1) / BN;
     q.kblocks = (g.K + BK - 1) / BK;
     int split = g.split_k < q.kblocks ? g.split_k : q.kblocks;
@@ -655,12 +729,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     q.unit_end = units;
   }
   P.total_units = units;
-  const int sms = sm_count();
-  const int grid = units < sms ? units : sms;
-  gemm_tcgen05_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(P);
-  count_launch();
-  M3AE_CUDA(cudaGetLastError());
-  return M3AE_OK;
+  return ctas == 2 ? launch_tc<2>(P, units, stream) : launch_tc<1>(P, units, stream);
 }
 
 }  // namespace m3ae

@@ -45,6 +45,11 @@ def set_gemm_epilogue(generic):
     L.check(L.load().m3ae_set_gemm_epilogue(1 if generic else 0), "m3ae_set_gemm_epilogue")
 
 
+def set_gemm_cta_pair(mode):
+    """0 auto, 1 one CTA per 128x256 tile, 2 CTA pairs (tcgen05.mma.cta_group::2, 256x256 tiles)."""
+    L.check(L.load().m3ae_set_gemm_cta_pair(int(mode)), "m3ae_set_gemm_cta_pair")
+
+
 class GemmSpec:
     """One problem of a grouped launch: out (+)= epi(alpha * A[M,K] · B[N,K]^T).
 

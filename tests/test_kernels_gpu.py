@@ -378,3 +378,49 @@ def test_gemm_tma_staged_epilogue_matches_generic_epilogue():
                     assert rel_err(a_fast, a_gen) < 3e-3
                 else:
                     assert torch.equal(a_fast, a_gen)
+
+
+def test_gemm_cta_pair_matches_single_cta_tiles():
+    """cta_group::2 (256x256 tiles on a CTA pair) and cta_group::1 (128x256 tiles) accumulate every output over K in
+    the same order, so plain and fused-epilogue results must be bit-identical; split-K reductions (fp32 adds in
+    arrival order) agree to rounding.  Auto mode picks pairs for M > 128, so the rest of this file exercises pairs."""
+    MN = ops.MAJOR_MN
+    bf = torch.bfloat16
+    cases = []
+    for (M, N, K) in [(300, 498, 768), (2600, 2304, 768), (257, 768, 3072), (20800 // 8, 3072, 768)]:
+        a, b = rnd(M, K, dtype=bf, scale=0.5), rnd(N, K, dtype=bf, scale=0.5, seed=1)
+        res, pre = rnd(M, N, dtype=bf, seed=2), rnd(M, N, dtype=bf, seed=3)
+        bias = rnd(N, seed=4)
+        cases.append(("plain f32", lambda a=a, b=b, M=M, N=N: [ops.GemmSpec(a, b, torch.empty(M, N, device=DEV))]))
+        if N % 32 == 0:
+            cases.append(("bias+gelu+aux", lambda a=a, b=b, M=M, N=N, bias=bias: [ops.GemmSpec(
+                a, b, torch.empty(M, N, dtype=bf, device=DEV), bias=bias, act=ops.ACT_GELU, aux_out=torch.empty(M, N, dtype=bf, device=DEV), aux_is_grad=True)]))
+            cases.append(("bias+drop+res", lambda a=a, b=b, M=M, N=N, bias=bias, res=res: [ops.GemmSpec(
+                a, b, torch.empty(M, N, dtype=bf, device=DEV), bias=bias, residual=res, drop_p=0.1, drop_seed=7, drop_stream=2)]))
+            cases.append(("dact", lambda a=a, b=b, M=M, N=N, pre=pre: [ops.GemmSpec(
+                a, b, torch.empty(M, N, dtype=bf, device=DEV), aux_in=pre, dact=ops.ACT_GELU)]))
+        if N % 8 == 0:  # TMA needs 16-byte row pitches
+            bt = b.t().contiguous()  # [K, N]: B MN-major (dgrad form)
+            cases.append(("B MN-major", lambda a=a, bt=bt, M=M, N=N: [ops.GemmSpec(a, bt, torch.empty(M, N, dtype=bf, device=DEV), b_major=MN)]))
+    # wgrad form: both operands MN-major, split-K accumulate, grouped with a second (text-sized) problem
+    dy, x = rnd(2600, 768, dtype=bf, scale=0.5), rnd(2600, 3072, dtype=bf, scale=0.5, seed=1)
+    dy2, x2 = rnd(256, 768, dtype=bf, scale=0.5, seed=5), rnd(256, 3072, dtype=bf, scale=0.5, seed=6)
+    cases.append(("wgrad splitK group", lambda: [
+        ops.GemmSpec(dy, x, torch.zeros(768, 3072, device=DEV), a_major=MN, b_major=MN, accumulate=True, split_k=4),
+        ops.GemmSpec(dy2, x2, torch.zeros(768, 3072, device=DEV), a_major=MN, b_major=MN, accumulate=True, split_k=2)]))
+    try:
+        for name, mk in cases:
+            outs = {}
+            for mode in (1, 2):
+                ops.set_gemm_cta_pair(mode)
+                specs = mk()
+                ops.gemm_group(specs, backend=ops.GEMM_TCGEN05)
+                torch.cuda.synchronize()
+                outs[mode] = [t for s in specs for t in (s.keep[2], s.keep[4]) if t is not None]
+            for o1, o2 in zip(outs[1], outs[2]):
+                if "splitK" in name:
+                    assert rel_err(o2, o1) < 1e-5, name
+                else:
+                    assert torch.equal(o1, o2), f"{name}: CTA-pair result differs from single-CTA result"
+    finally:
+        ops.set_gemm_cta_pair(0)
