@@ -87,6 +87,9 @@ typedef struct m3ae_gemm_epilogue_t {
   float alpha;
   int32_t aux_is_grad;  /* 1: aux_out receives act'(pre-activation) instead of the pre-activation, and dact multiplies by
                          * aux_in as stored (the FFN backward then needs one multiply per element instead of a GELU') */
+  uint32_t* drop_bits;  /* optional (drop_p > 0, N % 32 == 0, tcgen05 backend): keep bits of the dropout, one uint32 per
+                         * (row, 32 columns) at drop_bits[row * (N/32) + col/32], bit j = column col+j kept.  Handed to
+                         * m3ae_layernorm_bwd so that backward does not regenerate the Philox stream. */
 } m3ae_gemm_epilogue_t;
 
 typedef struct m3ae_gemm_problem_t {
@@ -158,10 +161,12 @@ int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, voi
  * grad-accumulating fp32 buffers).  When the Linear that produced x applied hidden dropout in its epilogue
  * (drop_p > 0), dx_drop receives dx pushed back through that dropout (same Philox stream, element = row*H+col) —
  * the operand of that Linear's dgrad/wgrad GEMMs — while dx stays the residual-branch gradient.
- * dcolsum (optional, fp32 [H]) += column sums of dx_drop (or dx when drop_p == 0): the Linear's bias gradient. */
+ * dcolsum (optional, fp32 [H]) += column sums of dx_drop (or dx when drop_p == 0): the Linear's bias gradient.
+ * drop_bits (optional): the keep bits the forward GEMM epilogue cached ([M, H/32] uint32); NULL = regenerate. */
 int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma,
                        void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype,
-                       void* dx_drop, float drop_p, uint64_t drop_seed, uint64_t drop_stream, void* stream);
+                       void* dx_drop, float drop_p, uint64_t drop_seed, uint64_t drop_stream, const uint32_t* drop_bits,
+                       void* stream);
 
 /* out[N] (fp32) += column sums of x[M,N] (ld elements).  Bias gradients of the projections. */
 int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int32_t dtype, void* stream);

@@ -25,6 +25,7 @@ class GemmEpilogue(C.Structure):
         ("residual", C.c_void_p), ("res_dtype", C.c_int32), ("ldr", C.c_int64),
         ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_stream", C.c_uint64),
         ("accumulate", C.c_int32), ("alpha", C.c_float), ("aux_is_grad", C.c_int32),
+        ("drop_bits", C.c_void_p),
     ]
 
 
@@ -72,7 +73,7 @@ SIGNATURES = {
                                      C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p]),
     "m3ae_layernorm_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
-                                     C.c_float, C.c_uint64, C.c_uint64, C.c_void_p]),
+                                     C.c_float, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]),
     "m3ae_colsum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.c_void_p]),
     "m3ae_cast": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]),
     "m3ae_cast_group": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),

@@ -144,6 +144,35 @@ __global__ void __launch_bounds__(128) attn_delta_kernel(const m3ae_attn_params_
   if (lane == 0) P.delta[((size_t)b * P.H + h) * P.Lq + qi] = s;
 }
 
+// bf16, dh = 64, heads packed side by side in a row (the fusion stack's ctx layout): one warp per token row, 16-byte loads,
+// 8 lanes share a head.  Streams O and dO once at full sector efficiency (the generic kernel above issues 2-byte loads).
+__global__ void __launch_bounds__(256) attn_delta_rows_bf16_64_kernel(const m3ae_attn_params_t P) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);  // token row b*Lq + qi
+  if (r >= (int64_t)P.B * P.Lq) return;
+  const int b = (int)(r / P.Lq), qi = (int)(r % P.Lq);
+  const bf16* __restrict__ O = (const bf16*)P.out + r * P.ldo;
+  const bf16* __restrict__ dO = (const bf16*)P.dout + r * P.ldo;
+  const int nvec = P.H * 8;  // 16-byte vectors per row
+  for (int v = lane; v < ((nvec + 31) & ~31); v += 32) {
+    float s = 0.f;
+    if (v < nvec) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(O) + v), g = __ldg(reinterpret_cast<const uint4*>(dO) + v);
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 x = unpack_bf16x2(aw[j]), y = unpack_bf16x2(gw[j]);
+        s = fmaf(x.x, y.x, s);
+        s = fmaf(x.y, y.y, s);
+      }
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if ((lane & 7) == 0 && v < nvec) P.delta[((size_t)b * P.H + (v >> 3)) * P.Lq + qi] = s;
+  }
+}
+
 // dQ_i = scale * sum_j dS_ij K_j,  dS_ij = P_ij (dP_ij - delta_i),  dP_ij = keep_ij/(1-p) * dO_i.V_j
 template <typename T, int DH>
 __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params_t P) {
@@ -469,8 +498,13 @@ int validate(const m3ae_attn_params_t* p, bool bwd) {
 }  // namespace
 
 void launch_delta_bf16_64(const m3ae_attn_params_t* p, cudaStream_t st) {
-  dim3 g0((p->Lq + 3) / 4, p->H, p->B);
-  attn_delta_kernel<bf16, 64><<<g0, 128, 0, st>>>(*p);
+  if ((p->ldo % 8) == 0 && (((uintptr_t)p->out | (uintptr_t)p->dout) & 15) == 0) {
+    const int64_t rows = (int64_t)p->B * p->Lq;
+    attn_delta_rows_bf16_64_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(*p);
+  } else {
+    dim3 g0((p->Lq + 3) / 4, p->H, p->B);
+    attn_delta_kernel<bf16, 64><<<g0, 128, 0, st>>>(*p);
+  }
   count_launch();
 }
 

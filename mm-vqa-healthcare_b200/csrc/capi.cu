@@ -65,7 +65,7 @@ int gemm_simt_launch(const m3ae_gemm_problem_t* probs, int n, int in_dtype, cuda
 int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
 int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
 int layernorm_fwd(const void*, const float*, const float*, void*, float*, float*, int64_t, int, float, int, cudaStream_t);
-int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, void*, float, uint64_t, uint64_t, cudaStream_t);
+int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, void*, float, uint64_t, uint64_t, const uint32_t*, cudaStream_t);
 int colsum(const void*, float*, int64_t, int, int64_t, int, cudaStream_t);
 int cast(const void*, int, void*, int, int64_t, cudaStream_t);
 int cast_group(const m3ae_cast_item_t*, int, cudaStream_t);
@@ -104,6 +104,8 @@ int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n, int32_t in_dtype, 
     M3AE_CHECK(g.a && g.b && g.epi.out, M3AE_ERR_INVALID, "m3ae_gemm: null operand in problem %d", i);
     M3AE_CHECK(g.epi.drop_p >= 0.f && g.epi.drop_p < 1.f, M3AE_ERR_INVALID, "m3ae_gemm: dropout %f not in [0,1)", g.epi.drop_p);
     M3AE_CHECK(g.epi.dact == M3AE_ACT_NONE || g.epi.aux_in != nullptr, M3AE_ERR_INVALID, "m3ae_gemm: dact needs aux_in");
+    M3AE_CHECK(g.epi.drop_bits == nullptr || (g.epi.drop_p > 0.f && g.N % 32 == 0 && in_dtype == M3AE_BF16 && backend != M3AE_GEMM_SIMT),
+               M3AE_ERR_UNSUPPORTED, "m3ae_gemm: drop_bits needs drop_p > 0, N %% 32 == 0 and the tcgen05 backend");
     M3AE_CHECK(g.split_k <= 1 || (!g.epi.bias && g.epi.act == M3AE_ACT_NONE && !g.epi.residual && g.epi.dact == M3AE_ACT_NONE && g.epi.drop_p == 0.f && !g.epi.aux_out),
                M3AE_ERR_INVALID, "m3ae_gemm: split_k > 1 supports only the plain accumulate epilogue");
   }
@@ -133,11 +135,11 @@ int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, voi
   M3AE_CHECK(x && gamma && beta && y && mean && rstd, M3AE_ERR_INVALID, "layernorm_fwd: null pointer");
   return layernorm_fwd(x, gamma, beta, y, mean, rstd, M, H, eps, dtype, (cudaStream_t)stream);
 }
-int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype, void* dx_drop, float drop_p, uint64_t drop_seed, uint64_t drop_stream, void* stream) {
+int m3ae_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx, float* dgamma, float* dbeta, float* dcolsum, int64_t M, int32_t H, int32_t dtype, void* dx_drop, float drop_p, uint64_t drop_seed, uint64_t drop_stream, const uint32_t* drop_bits, void* stream) {
   ARCH_GATE();
   M3AE_CHECK(dy && x && mean && rstd && gamma && dx, M3AE_ERR_INVALID, "layernorm_bwd: null pointer");
   M3AE_CHECK(drop_p == 0.f || dx_drop != nullptr, M3AE_ERR_INVALID, "layernorm_bwd: drop_p > 0 needs dx_drop");
-  return layernorm_bwd(dy, x, mean, rstd, gamma, dx, dgamma, dbeta, dcolsum, M, H, dtype, dx_drop, drop_p, drop_seed, drop_stream, (cudaStream_t)stream);
+  return layernorm_bwd(dy, x, mean, rstd, gamma, dx, dgamma, dbeta, dcolsum, M, H, dtype, dx_drop, drop_p, drop_seed, drop_stream, drop_bits, (cudaStream_t)stream);
 }
 int m3ae_colsum(const void* x, float* out, int64_t M, int32_t N, int64_t ld, int32_t dtype, void* stream) {
   ARCH_GATE();

@@ -133,29 +133,6 @@ struct Philox {
     return make_uint4(c0, c1, c2, c3);
   }
 };
-// Keep-decision for element `idx` of dropout stream `stream_id`: one Philox call yields 4 lanes,
-// element idx uses lane idx&3 of counter idx>>2, so forward and backward regenerate identical masks.
-__device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
-  Philox ph(seed);
-  const uint4 r = ph(idx >> 2, stream_id);
-  const uint32_t lane = (uint32_t)(idx & 3);
-  const uint32_t v = lane == 0 ? r.x : lane == 1 ? r.y : lane == 2 ? r.z : r.w;
-  // uniform in [0,1): keep when u >= p
-  return (float)(v >> 8) * (1.0f / 16777216.0f) >= p;
-}
-// 4 consecutive elements starting at idx (idx % 4 == 0): returns a 4-bit keep mask.
-__device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
-  Philox ph(seed);
-  const uint4 r = ph(idx >> 2, stream_id);
-  const float s = 1.0f / 16777216.0f;
-  uint32_t m = 0;
-  m |= ((float)(r.x >> 8) * s >= p) ? 1u : 0u;
-  m |= ((float)(r.y >> 8) * s >= p) ? 2u : 0u;
-  m |= ((float)(r.z >> 8) * s >= p) ? 4u : 0u;
-  m |= ((float)(r.w >> 8) * s >= p) ? 8u : 0u;
-  return m;
-}
-
 // Attention-probability dropout.  One Philox evaluation with counter (row_lin = (b*H+h)*Lq+i, site<<32 | key/8) covers the
 // 8 consecutive keys 8g..8g+7 of a row: key 8g+2i takes the low 16-bit lane of word i, key 8g+2i+1 the high lane (the
 // order bf16x2 packing uses).  Only 15 bits of a lane are used: adding (0x8000 - thr15) to a 15-bit value carries into the
@@ -194,6 +171,29 @@ __device__ __forceinline__ bool attn_dropout_keep(uint64_t seed, uint64_t stream
   return (attn_keep_bits8(seed, stream_id, row_lin, key >> 3, drop_thr15(p)) >> (key & 7)) & 1u;
 }
 
+// Hidden (activation) dropout of the GEMM epilogues.  Same 15-bit-lane scheme: one Philox evaluation with counter
+// (element index / 8, stream) decides the 8 consecutive elements 8g..8g+7 (element index = row*ld + col), so the forward
+// epilogue, the generic per-element paths and the LayerNorm backward all see the same mask.  The drop rate is p quantised
+// to 1/32768 and the keep scale is drop_keep_scale(p) (the exact inverse of the quantised keep rate).
+__device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint64_t stream_id, uint64_t idx8, uint32_t thr15) {
+  Philox ph(seed);
+  const uint4 r = ph(idx8 >> 3, stream_id);
+  const uint32_t lane_add = drop_lane_add(thr15);
+  uint32_t f[4];
+  f[0] = ((r.x & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[1] = ((r.y & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[2] = ((r.z & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  f[3] = ((r.w & 0x7FFF7FFFu) + lane_add) & 0x80008000u;
+  return attn_flags_to_byte(f);
+}
+__device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
+  return (dropout_keep8(seed, stream_id, idx & ~(uint64_t)7, drop_thr15(p)) >> (uint32_t)(idx & 7)) & 1u;
+}
+// 4 consecutive elements starting at idx (idx % 4 == 0): returns a 4-bit keep mask.
+__device__ __forceinline__ uint32_t dropout_keep4(uint64_t seed, uint64_t stream_id, uint64_t idx, float p) {
+  return (dropout_keep8(seed, stream_id, idx & ~(uint64_t)7, drop_thr15(p)) >> (uint32_t)(idx & 4)) & 0xFu;
+}
+
 // ---------------------------------------------------------------- warp helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -221,6 +221,8 @@ struct EpiDev {
   int accumulate;          // 1: atomicAdd into fp32 out (split-K partials / grad accumulation)
   float alpha;
   int aux_is_grad;         // aux_out := act'(pre-activation); dact multiplies by aux_in as stored
+  uint32_t* drop_bits;     // optional keep-bit cache [rows][N/32] (tcgen05 epilogues, 32-column chunks)
+  int64_t drop_bits_ld;    // words per row = N / 32 (set by the launcher)
 };
 
 // Applies the epilogue to `n` consecutive columns [col, col+n) of row `row` whose accumulators are acc[0..n).
@@ -258,12 +260,15 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
     }
   }
   if (e.drop_p > 0.0f) {
-    const float inv = 1.0f / (1.0f - e.drop_p);
+    const float inv = drop_keep_scale(e.drop_p);
+    uint32_t bits = 0;
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
       const bool keep = dropout_keep(e.drop_seed, e.drop_stream, (uint64_t)(row * e.ldo + col + j), e.drop_p);
       acc[j] = keep ? acc[j] * inv : 0.0f;
+      if (NV == 32) bits |= (keep ? 1u : 0u) << (j & 31);
     }
+    if (NV == 32 && e.drop_bits != nullptr) e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] = bits;
   }
   if (e.residual) {
 #pragma unroll

@@ -431,14 +431,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             }
           }
           if (epi.drop_p > 0.f) {
-            const float inv = 1.0f / (1.0f - epi.drop_p);
-            const uint64_t e0 = (uint64_t)(row * epi.ldo + col);
+            const float inv = drop_keep_scale(epi.drop_p);
+            const uint32_t thr15 = drop_thr15(epi.drop_p);
+            const uint64_t e0 = (uint64_t)(row * epi.ldo + col);  // multiple of 8 (ldo % 8 == 0, col % 32 == 0)
+            uint32_t bits = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint32_t m4 = dropout_keep4(epi.drop_seed, epi.drop_stream, e0 + 4 * j, epi.drop_p);
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t m8 = dropout_keep8(epi.drop_seed, epi.drop_stream, e0 + 8 * j, thr15);
+              bits |= m8 << (8 * j);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) v[4 * j + k] = ((m4 >> k) & 1u) ? v[4 * j + k] * inv : 0.f;
+              for (int k = 0; k < 8; ++k) v[8 * j + k] = ((m8 >> k) & 1u) ? v[8 * j + k] * inv : 0.f;
             }
+            if (epi.drop_bits != nullptr && row < q.M) epi.drop_bits[row * epi.drop_bits_ld + (col >> 5)] = bits;
           }
           if (q.in_is_residual) {
 #pragma unroll
@@ -620,7 +624,7 @@ bool epilogue_is_fast(const m3ae_gemm_problem_t& g) {
   if (e.residual && (e.res_dtype != M3AE_BF16 || !tma_ok(e.residual, e.ldr))) return false;
   if (e.aux_in && (e.aux_in_dtype != M3AE_BF16 || !tma_ok(e.aux_in, e.ld_aux_in))) return false;
   if (e.dact != M3AE_ACT_NONE && !e.aux_in) return false;
-  if (e.drop_p > 0.f && (e.ldo % 4) != 0) return false;
+  if (e.drop_p > 0.f && (e.ldo % 8) != 0) return false;
   return true;
 }
 
@@ -693,6 +697,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     else rc = encode_map(&q.map_b, g.b, g.K, g.N, g.ldb, BK);
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
+    q.epi.drop_bits_ld = g.N / 32;
     q.epi_fast = (!force_generic_epilogue && epilogue_is_fast(g)) ? 1 : 0;
     if (!force_generic_epilogue && epilogue_is_reduce(g)) q.epi_fast = 2;
     q.has_in = 0;

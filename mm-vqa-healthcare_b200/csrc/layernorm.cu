@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                               float* __restrict__ dcolsum, int64_t M, int H,
                                                               T* __restrict__ dx_drop, float drop_p, uint64_t drop_seed,
-                                                              uint64_t drop_stream) {
+                                                              uint64_t drop_stream, const uint8_t* __restrict__ drop_bits) {
   constexpr int VN = Vec<T>::N;
   extern __shared__ float red[];  // [LN_WARPS][H]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -128,12 +128,20 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
   const int64_t stride = (int64_t)gridDim.x * LN_WARPS;
   int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp;
   uint4 rx[HV], rdy[HV];
+  // keep bits cached by the forward GEMM epilogue: byte (i*32+lane)*VN/8 of the row covers this lane's VN columns
+  constexpr int NB = VN == 8 ? HV : 1;
+  uint8_t kb[NB];
+  const bool cached = VN == 8 && drop_bits != nullptr;
   float mu = 0.f, rs = 0.f;
   if (row < M) {
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
       rx[i] = ld_raw(x + row * H + (i * 32 + lane) * VN);
       rdy[i] = ld_raw(dy + row * H + (i * 32 + lane) * VN);
+    }
+    if (cached) {
+#pragma unroll
+      for (int i = 0; i < NB; ++i) kb[i] = drop_bits[row * (H / 8) + i * 32 + lane];
     }
     mu = mean[row]; rs = rstd[row];
   }
@@ -157,11 +165,18 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
       }
     }
     const int64_t nrow = row + stride;
+    uint8_t kc[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) kc[i] = cached ? kb[i] : (uint8_t)0;
     if (nrow < M) {  // prefetch: the loads fly during the reductions and the dropout regeneration below
 #pragma unroll
       for (int i = 0; i < HV; ++i) {
         rx[i] = ld_raw(x + nrow * H + (i * 32 + lane) * VN);
         rdy[i] = ld_raw(dy + nrow * H + (i * 32 + lane) * VN);
+      }
+      if (cached) {
+#pragma unroll
+        for (int i = 0; i < NB; ++i) kb[i] = drop_bits[nrow * (H / 8) + i * 32 + lane];
       }
       mu = mean[nrow]; rs = rstd[nrow];
     }
@@ -176,12 +191,24 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
       Vec<T>::store(dx + row * H + c, o);
       if (dx_drop != nullptr) {
         // gradient through the hidden dropout of the producing GEMM epilogue: same Philox stream, element = row*H+col
-        const float inv = 1.0f / (1.0f - drop_p);
+        const float inv = drop_keep_scale(drop_p);
+        if (cached) {
+          const uint32_t m8 = kc[NB == 1 ? 0 : i];
 #pragma unroll
-        for (int q = 0; q < VN / 4; ++q) {
-          const uint32_t m4 = dropout_keep4(drop_seed, drop_stream, (uint64_t)(row * H + c + 4 * q), drop_p);
+          for (int j = 0; j < VN; ++j) o[j] = ((m8 >> (j & 7)) & 1u) ? o[j] * inv : 0.f;
+        } else {
+          if (VN == 8) {  // c % 8 == 0 and H % 8 == 0: one Philox evaluation covers the lane's 8 columns
+            const uint32_t m8 = dropout_keep8(drop_seed, drop_stream, (uint64_t)(row * H + c), drop_thr15(drop_p));
 #pragma unroll
-          for (int j = 0; j < 4; ++j) o[4 * q + j] = ((m4 >> j) & 1u) ? o[4 * q + j] * inv : 0.f;
+            for (int j = 0; j < VN; ++j) o[j] = ((m8 >> (j & 7)) & 1u) ? o[j] * inv : 0.f;
+          } else {
+#pragma unroll
+            for (int q = 0; q < VN / 4; ++q) {
+              const uint32_t m4 = dropout_keep4(drop_seed, drop_stream, (uint64_t)(row * H + c + 4 * q), drop_p);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) o[4 * q + j] = ((m4 >> j) & 1u) ? o[4 * q + j] * inv : 0.f;
+            }
+          }
         }
         Vec<T>::store(dx_drop + row * H + c, o);
       }
@@ -226,6 +253,59 @@ __global__ void colsum_kernel(const T* __restrict__ x, float* __restrict__ out, 
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
     atomicAdd(out + c, t);
+  }
+}
+
+// bf16 column sums with 16-byte loads: block = 32 lanes x 8 row lanes, a warp covers 256 consecutive columns of a row
+// (512 B), 4 rows in flight per thread.  Bias gradients of the fused QKV / KV / Q / FFN-up projections.
+__global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const bf16* __restrict__ x, float* __restrict__ out, int64_t M, int N,
+                                                              int64_t ld, int rows_per_cta) {
+  __shared__ float red[8][32][9];
+  const int c = (blockIdx.x * 32 + threadIdx.x) * 8;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+  const int64_t r1 = min(M, r0 + rows_per_cta);
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (c < N) {
+    int64_t r = r0 + threadIdx.y;
+    for (; r + 24 < r1; r += 32) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(x + (r + 8 * u) * ld + c));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = unpack_bf16x2(w[j]);
+          s[2 * j] += f.x;
+          s[2 * j + 1] += f.y;
+        }
+      }
+    }
+    for (; r < r1; r += 8) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + r * ld + c));
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        s[2 * j] += f.x;
+        s[2 * j + 1] += f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = s[j];
+  __syncthreads();
+  // 256 threads <-> 256 columns of the block
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  const int col = blockIdx.x * 256 + tid;
+  if (col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][tid >> 3][tid & 7];
+    atomicAdd(out + col, t);
   }
 }
 
@@ -302,7 +382,7 @@ template <typename T>
 __global__ void dropout_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int N, int64_t ld, float p,
                                      uint64_t seed, uint64_t stream_id) {
   const int64_t total = M * N;
-  const float inv = 1.0f / (1.0f - p);
+  const float inv = drop_keep_scale(p);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int64_t r = i / N, c = i % N;
@@ -331,9 +411,11 @@ int layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
 
 int layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx,
                   float* dgamma, float* dbeta, float* dcolsum, int64_t M, int H, int dtype, void* dx_drop, float drop_p,
-                  uint64_t drop_seed, uint64_t drop_stream, cudaStream_t st) {
+                  uint64_t drop_seed, uint64_t drop_stream, const uint32_t* drop_bits, cudaStream_t st) {
   M3AE_CHECK(drop_p >= 0.f && drop_p < 1.f, M3AE_ERR_INVALID, "layernorm_bwd: dropout %f not in [0,1)", drop_p);
   if (drop_p == 0.f) dx_drop = nullptr;
+  M3AE_CHECK(drop_bits == nullptr || (dtype == M3AE_BF16 && H % 32 == 0), M3AE_ERR_UNSUPPORTED,
+             "layernorm_bwd: cached dropout bits need bf16 activations and H %% 32 == 0");
   M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
   int64_t want = (M + LN_WARPS - 1) / LN_WARPS;
   const int64_t cap = (int64_t)sm_count() * LN_BWD_CTAS_PER_SM;  // persistent: exactly the resident CTAs
@@ -341,7 +423,7 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
 #define LN_BWD(T, HV)                                                                                                     \
   ln_bwd_kernel<T, HV><<<grid, LN_WARPS * 32, smem, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
-                                                          dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream)
+                                                          dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream, (const uint8_t*)drop_bits)
   if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3);
   else if (dtype == M3AE_BF16 && H == 1536) LN_BWD(bf16, 6);
   else if (dtype == M3AE_F32 && H == 768) LN_BWD(float, 6);
@@ -355,6 +437,17 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
 
 int colsum(const void* x, float* out, int64_t M, int N, int64_t ld, int dtype, cudaStream_t st) {
   M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "colsum: empty input");
+  if (dtype == M3AE_BF16 && N % 8 == 0 && ld % 8 == 0 && ((uintptr_t)x & 15) == 0) {
+    const int cb = (N + 255) / 256;
+    int rb = (int)((int64_t)sm_count() * 4 / cb);
+    if (rb < 1) rb = 1;
+    if ((int64_t)rb * 64 > M) rb = (int)((M + 63) / 64);
+    const int rows_per = (int)((M + rb - 1) / rb);
+    colsum_bf16_vec_kernel<<<dim3(cb, rb), dim3(32, 8), 0, st>>>((const bf16*)x, out, M, N, ld, rows_per);
+    count_launch();
+    M3AE_CUDA(cudaGetLastError());
+    return M3AE_OK;
+  }
   const int col_blocks = (N + 31) / 32;
   int row_blocks = (int)((int64_t)sm_count() * 8 / col_blocks);
   if (row_blocks < 1) row_blocks = 1;

@@ -248,6 +248,10 @@ def _forward_streams(cfg, training, streams, want_probs, will_train=True):
             if pa > 0.0 and dt == torch.bfloat16:  # dropout keep-bit caches: written by forward, read by backward
                 st.dm1 = st.buf("dm1", (st.B * nh * st.Lq * ops.drop_mask_ld(st.Lq),), torch.uint8, dev)
                 st.dm2 = st.buf("dm2", (st.B * nh * st.Lq * ops.drop_mask_ld(st.Lk),), torch.uint8, dev)
+            # keep bits of the three hidden dropouts: written by the GEMM epilogues, read by the LayerNorm backward
+            st.hb1 = st.hb2 = st.hb3 = None
+            if ph > 0.0 and dt == torch.bfloat16 and be != ops.GEMM_SIMT and H % 32 == 0:
+                st.hb1, st.hb2, st.hb3 = (st.buf(n, (M, H // 32), torch.int32, dev) for n in ("hb1", "hb2", "hb3"))
             st.h1 = st.buf("h1", (M, H), dt, dev)
             st.a1 = st.buf("a1", (M, H), dt, dev)
             st.mean1, st.rstd1 = st.buf("mean1", (M,), f32, dev), st.buf("rstd1", (M,), f32, dev)
@@ -264,15 +268,15 @@ def _forward_streams(cfg, training, streams, want_probs, will_train=True):
             st.mean3, st.rstd3 = st.buf("mean3", (M,), f32, dev), st.buf("rstd3", (M,), f32, dev)
         L_ = S0.launch
         L_["qkv"] = _Gemm([ops.GemmSpec(st.x, st.w.wqkv, st.qkv, bias=st.w.bqkv) for st in S])
-        L_["o1"] = _Gemm([ops.GemmSpec(st.ctx, st.w.wo, st.h1, bias=st.p[BO], residual=st.x, drop_p=ph, drop_stream=1) for st in S])
+        L_["o1"] = _Gemm([ops.GemmSpec(st.ctx, st.w.wo, st.h1, bias=st.p[BO], residual=st.x, drop_p=ph, drop_stream=1, drop_bits=st.hb1) for st in S])
         specs = []
         for st in S:
             specs.append(ops.GemmSpec(st.a1, st.w.wq2, st.qc, bias=st.p[BQ2]))
             specs.append(ops.GemmSpec(st.y, st.w.wkv2, st.kvc, bias=st.w.bkv2))
         L_["xproj"] = _Gemm(specs)
-        L_["o2"] = _Gemm([ops.GemmSpec(st.ctx2, st.w.wo2, st.h2, bias=st.p[BO2], residual=st.a1, drop_p=ph, drop_stream=3) for st in S])
+        L_["o2"] = _Gemm([ops.GemmSpec(st.ctx2, st.w.wo2, st.h2, bias=st.p[BO2], residual=st.a1, drop_p=ph, drop_stream=3, drop_bits=st.hb2) for st in S])
         L_["ffn1"] = _Gemm([ops.GemmSpec(st.a2, st.w.w1, st.g, bias=st.p[BI], act=ops.ACT_GELU, aux_out=st.u, aux_is_grad=True) for st in S])
-        L_["ffn2"] = _Gemm([ops.GemmSpec(st.g, st.w.w2, st.h3, bias=st.p[BO3], residual=st.a2, drop_p=ph, drop_stream=4) for st in S])
+        L_["ffn2"] = _Gemm([ops.GemmSpec(st.g, st.w.w2, st.h3, bias=st.p[BO3], residual=st.a2, drop_p=ph, drop_stream=4, drop_bits=st.hb3) for st in S])
         for st in S:
             H = st.H
             st.launch["att1"] = _Attn(ops.attn_params(st.qkv[:, :H], st.qkv[:, H:2 * H], st.qkv[:, 2 * H:], st.ctx, st.lse1,
@@ -416,25 +420,25 @@ def _backward_streams(cfg, S, douts):
 
     code = ops._code(dt)
 
-    def ln_bwd(st, d, h, mean, rstd, gamma, dg, db, dbias, dx, dxd, site):
+    def ln_bwd(st, d, h, mean, rstd, gamma, dg, db, dbias, dx, dxd, site, bits):
         """LayerNorm backward; dxd = gradient pushed back through the hidden dropout of the GEMM that produced h (same
         Philox stream as the forward epilogue); dbias accumulates that GEMM's bias gradient."""
         ops.L.check(lib.m3ae_layernorm_bwd(d.data_ptr(), h.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
                                            dx.data_ptr(), dg.data_ptr(), db.data_ptr(), dbias.data_ptr(), st.M, st.H, code,
-                                           dxd.data_ptr() if st.ph > 0 else None, st.ph, st.seed, site, stream),
+                                           dxd.data_ptr() if st.ph > 0 else None, st.ph, st.seed, site, _ptr(bits), stream),
                     "m3ae_layernorm_bwd")
 
     def colsum(x, out):
         ops.L.check(lib.m3ae_colsum(x.data_ptr(), out.data_ptr(), x.shape[0], x.shape[1], x.stride(0), code, stream), "m3ae_colsum")
 
     for st, d in zip(S, douts):   # ---- output LayerNorm + FFN
-        ln_bwd(st, d, st.h3, st.mean3, st.rstd3, st.p[G3], st.gb["g3"], st.gb["b3"], st.gb["bo3"], st.dh3, st.dh3d, 4)
+        ln_bwd(st, d, st.h3, st.mean3, st.rstd3, st.p[G3], st.gb["g3"], st.gb["b3"], st.gb["bo3"], st.dh3, st.dh3d, 4, st.hb3)
     B_["ffn2"].run(be, stream)
     for st in S:
         colsum(st.du, st.gb["bi"])
     B_["ffn1"].run(be, stream)
     for st in S:                  # ---- cross-attention block
-        ln_bwd(st, st.da2, st.h2, st.mean2, st.rstd2, st.p[G2], st.gb["g2"], st.gb["b2"], st.gb["bo2"], st.dh2, st.dh2d, 3)
+        ln_bwd(st, st.da2, st.h2, st.mean2, st.rstd2, st.p[G2], st.gb["g2"], st.gb["b2"], st.gb["bo2"], st.dh2, st.dh2d, 3, st.hb2)
     B_["o2"].run(be, stream)
     for st in S:
         st.launch["batt2"].run(stream)
@@ -443,7 +447,7 @@ def _backward_streams(cfg, S, douts):
     B_["xd"].run(be, stream)
     B_["xw"].run(be, stream)
     for st in S:                  # ---- self-attention block
-        ln_bwd(st, st.da1, st.h1, st.mean1, st.rstd1, st.p[G1], st.gb["g1"], st.gb["b1"], st.gb["bo"], st.dh1, st.dh1d, 1)
+        ln_bwd(st, st.da1, st.h1, st.mean1, st.rstd1, st.p[G1], st.gb["g1"], st.gb["b1"], st.gb["bo"], st.dh1, st.dh1d, 1, st.hb1)
     B_["o1"].run(be, stream)
     for st in S:
         st.launch["batt1"].run(stream)

@@ -58,8 +58,8 @@ class GemmSpec:
 
     def __init__(self, a, b, out, *, a_major=MAJOR_K, b_major=MAJOR_K, bias=None, act=ACT_NONE, aux_out=None,
                  aux_in=None, dact=ACT_NONE, residual=None, drop_p=0.0, drop_seed=0, drop_stream=0, accumulate=False,
-                 split_k=1, alpha=1.0, aux_is_grad=False):
-        _need_cuda(a, b, out, bias, aux_out, aux_in, residual)
+                 split_k=1, alpha=1.0, aux_is_grad=False, drop_bits=None):
+        _need_cuda(a, b, out, bias, aux_out, aux_in, residual, drop_bits)
         assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
         assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
         assert a.dtype == b.dtype
@@ -77,7 +77,9 @@ class GemmSpec:
         if aux_out is not None:
             assert aux_out.dtype == out.dtype and aux_out.stride(0) == out.stride(0)
         self.in_dtype = a.dtype
-        self.keep = (a, b, out, bias, aux_out, aux_in, residual)  # keep tensors alive until launch returns
+        if drop_bits is not None:  # keep bits of the epilogue dropout, [M, N/32] uint32 words (read by layernorm_bwd)
+            assert N % 32 == 0 and drop_bits.is_contiguous() and drop_bits.numel() * drop_bits.element_size() == M * (N // 32) * 4
+        self.keep = (a, b, out, bias, aux_out, aux_in, residual, drop_bits)  # keep tensors alive until launch returns
         p = L.GemmProblem()
         p.a, p.b = a.data_ptr(), b.data_ptr()
         p.lda, p.ldb = a.stride(0), b.stride(0)
@@ -98,6 +100,7 @@ class GemmSpec:
         e.accumulate = 1 if accumulate else 0
         e.alpha = float(alpha)
         e.aux_is_grad = 1 if aux_is_grad else 0
+        e.drop_bits = drop_bits.data_ptr() if drop_bits is not None else None
         self.problem = p
 
 
@@ -182,7 +185,7 @@ def layernorm_fwd(x, gamma, beta, eps, y=None, mean=None, rstd=None):
 
 
 def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma=None, dbeta=None, dcolsum=None, dx=None, drop_p=0.0, drop_seed=0,
-                  drop_stream=0):
+                  drop_stream=0, drop_bits=None):
     """dgamma / dbeta / dcolsum are accumulated into (+=); pass zeroed fp32 buffers for plain gradients.
     Returns dx, or (dx, dx_drop) when drop_p > 0 (dx_drop = dx pushed back through the producing GEMM's dropout)."""
     _need_cuda(dy, x, mean, rstd, gamma, dgamma, dbeta, dcolsum)
@@ -193,7 +196,7 @@ def layernorm_bwd(dy, x, mean, rstd, gamma, dgamma=None, dbeta=None, dcolsum=Non
     dx_drop = torch.empty_like(x) if drop_p > 0 else None
     L.check(L.load().m3ae_layernorm_bwd(_ptr(dy), _ptr(x), _ptr(mean), _ptr(rstd), _ptr(gamma), _ptr(dx), _ptr(dgamma),
                                         _ptr(dbeta), _ptr(dcolsum), M, H, _code(x.dtype), _ptr(dx_drop), float(drop_p),
-                                        int(drop_seed), int(drop_stream), _stream()),
+                                        int(drop_seed), int(drop_stream), _ptr(drop_bits), _stream()),
             "m3ae_layernorm_bwd")
     return (dx, dx_drop) if drop_p > 0 else dx
 

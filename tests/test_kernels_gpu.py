@@ -170,7 +170,8 @@ def test_gemm_dropout_epilogue_statistics():
     ops.gemm(a, w, drop, backend=ops.GEMM_SIMT, drop_p=0.1, drop_seed=123, drop_stream=7)
     kept = drop != 0
     assert abs(kept.float().mean().item() - 0.9) < 5e-3
-    assert torch.allclose(drop[kept], full[kept] / 0.9, rtol=1e-5, atol=1e-6)
+    keep_scale = 32768.0 / (32768 - round(0.1 * 32768))  # the drop rate is quantised to 1/32768
+    assert torch.allclose(drop[kept], full[kept] * keep_scale, rtol=1e-5, atol=1e-6)
     # the standalone dropout kernel regenerates the same mask (used by the backward pass)
     again = torch.empty_like(full)
     ops.dropout_apply(full, again, 0.1, 123, 7)
@@ -220,6 +221,12 @@ def test_elementwise_helpers():
     cs = torch.zeros(768, device=DEV)
     ops.colsum(xb, cs)
     assert rel_err(cs, xb.float().sum(0)) < 1e-5
+    for (M, N, ld) in [(2601, 3072, 3072), (333, 768, 2304), (64, 1536, 1536), (1000, 100, 100), (37, 768, 776)]:
+        big = rnd(M, ld, seed=7).to(torch.bfloat16)
+        view = big[:, :N]  # column slice of a wider buffer (the q|k|v gradient blocks): ld != N
+        cs = torch.full((N,), 2.0, device=DEV)
+        ops.colsum(view, cs)  # accumulates into the existing contents
+        assert rel_err(cs, view.float().sum(0) + 2.0) < 1e-5, (M, N, ld)
     lg = rnd(128, 30522)
     assert torch.equal(ops.argmax_rows(lg), lg.argmax(dim=1))
 
@@ -424,3 +431,42 @@ def test_gemm_cta_pair_matches_single_cta_tiles():
                     assert torch.equal(o1, o2), f"{name}: CTA-pair result differs from single-CTA result"
     finally:
         ops.set_gemm_cta_pair(0)
+
+
+@pytest.mark.parametrize("generic", [False, True])
+def test_hidden_dropout_keep_bits_cache(generic):
+    """The GEMM epilogue's cached keep bits are exactly the Philox mask it applied, and LayerNorm backward fed with the
+    cache returns bit-identical results to LayerNorm backward regenerating the stream."""
+    M, N, K = 1000, 768, 128  # ragged M: the last tile's out-of-range rows must not be written
+    bf = torch.bfloat16
+    a, w = rnd(M, K, dtype=bf), rnd(N, K, dtype=bf, seed=1)
+    res = rnd(M, N, dtype=bf, seed=2)
+    out = torch.empty(M, N, dtype=bf, device=DEV)
+    plain = torch.empty(M, N, dtype=bf, device=DEV)
+    bits = torch.full((M + 8, N // 32), -1, dtype=torch.int32, device=DEV)
+    try:
+        ops.set_gemm_epilogue(generic)
+        ops.gemm(a, w, plain, backend=ops.GEMM_TCGEN05)
+        ops.gemm(a, w, out, backend=ops.GEMM_TCGEN05, residual=res, drop_p=0.1, drop_seed=77, drop_stream=3, drop_bits=bits[:M])
+    finally:
+        ops.set_gemm_epilogue(False)
+    assert (bits[M:] == -1).all(), "rows beyond M were written"
+    shifts = torch.arange(32, device=DEV, dtype=torch.int64)
+    keep = ((bits[:M].to(torch.int64).unsqueeze(-1) >> shifts) & 1).reshape(M, N).bool()
+    regen = torch.empty(M, N, dtype=bf, device=DEV)
+    ops.dropout_apply(torch.ones(M, N, dtype=bf, device=DEV), regen, 0.1, 77, 3)
+    assert torch.equal(keep, regen != 0)
+    assert abs(keep.float().mean().item() - 0.9) < 5e-3
+    ref = torch.where(keep, plain.float() / 0.9, torch.zeros_like(plain, dtype=torch.float32)) + res.float()
+    assert rel_err(out, ref) < 8e-3
+    # LayerNorm backward: cached bits vs regenerated stream
+    x, dy = rnd(M, N, dtype=bf, seed=4), rnd(M, N, dtype=bf, seed=5)
+    gamma, beta = rnd(N, seed=6), rnd(N, seed=7)
+    _, mean, rstd = ops.layernorm_fwd(x, gamma, beta, 1e-12)
+    outs = []
+    for b in (None, bits[:M].contiguous()):
+        dg, db_, dc = (torch.zeros(N, device=DEV) for _ in range(3))
+        dx, dxd = ops.layernorm_bwd(dy, x, mean, rstd, gamma, dg, db_, dc, drop_p=0.1, drop_seed=77, drop_stream=3, drop_bits=b)
+        outs.append((dx, dxd, dc))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert rel_err(outs[1][2], outs[0][2]) < 1e-5
