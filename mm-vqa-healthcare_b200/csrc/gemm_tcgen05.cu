@@ -63,6 +63,7 @@ struct alignas(64) TcProblem {
   int M, N, K;
   int a_major, b_major;
   int tiles_m, tiles_n, split_k, kblocks, kb_per_split;
+  int n_fastest;         // tile order: 1 = the N tiles of one M tile are consecutive units (A panel read once), 0 = M fastest
   int unit_begin, unit_end;
 };
 struct TcParams {
@@ -94,8 +95,13 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& P, int unit) {
   const int local = unit - q.unit_begin;
   const int split = local % q.split_k;
   const int t = local / q.split_k;
-  u.m_blk = t % q.tiles_m;
-  u.n_blk = t / q.tiles_m;
+  if (q.n_fastest) {
+    u.n_blk = t % q.tiles_n;
+    u.m_blk = t / q.tiles_n;
+  } else {
+    u.m_blk = t % q.tiles_m;
+    u.n_blk = t / q.tiles_m;
+  }
   u.kb0 = split * q.kb_per_split;
   u.kb1 = min(q.kblocks, u.kb0 + q.kb_per_split);
   return u;
@@ -729,6 +735,13 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     int split = g.split_k < q.kblocks ? g.split_k : q.kblocks;
     q.kb_per_split = (q.kblocks + split - 1) / split;
     q.split_k = (q.kblocks + q.kb_per_split - 1) / q.kb_per_split;  // no empty splits
+    // Rasterisation.  Consecutive units run at the same time on neighbouring CTA pairs, so whatever they share is read
+    // from DRAM once and from L2 afterwards.  With M fastest the N tiles of one M tile are a whole sweep over M apart:
+    // for the K = 3072 GEMMs the A operand (140 MB at batch 64) exceeds the 126 MB L2 and was re-read once per N tile
+    // (ncu: 441 MB read against 180 MB algorithmic, profiles/r1_ncu_gemm_full_v9_cta_pair.txt).  N fastest whenever A
+    // is the larger operand (forward / dgrad: A = activations, B = weights); split-K weight gradients keep M fastest
+    // (their units form about one wave that walks K in lockstep).
+    q.n_fastest = (q.split_k == 1 && (int64_t)g.M >= (int64_t)g.N) ? 1 : 0;
     q.unit_begin = units;
     units += q.tiles_m * q.tiles_n * q.split_k;
     q.unit_end = units;
