@@ -224,6 +224,8 @@ int m3ae_set_gemm_epilogue(int32_t generic);
 /* tcgen05 GEMM tile mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2 on 256x256 tiles, unless every problem of the
  * launch has M <= 128), 1 = always one CTA per 128x256 tile, 2 = always CTA pairs.  Results are identical. */
 int m3ae_set_gemm_cta_pair(int32_t mode);
+/* Test hook: 1 = m3ae_layernorm_bwd loads rows through registers only (cross-checks the cp.async.bulk staging ring), 0 = auto. */
+int m3ae_set_layernorm_bwd_staging(int32_t registers_only);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

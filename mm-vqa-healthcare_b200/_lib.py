@@ -90,6 +90,7 @@ SIGNATURES = {
     "m3ae_set_attention_backend": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_cta_pair": (C.c_int, [C.c_int32]),
+    "m3ae_set_layernorm_bwd_staging": (C.c_int, [C.c_int32]),
 }
 
 _lib = None

@@ -77,6 +77,7 @@ int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, vo
 
 extern bool force_generic_epilogue;
 extern int gemm_cta_pair_mode;
+extern bool ln_bwd_force_registers;
 static int g_attn_backend = M3AE_GEMM_AUTO;
 
 }  // namespace m3ae
@@ -121,6 +122,8 @@ int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n, int32_t in_dtype, 
 /* Test hook: 0 = auto (tensor-core kernels for bf16), 2 = force the generic fp32-math attention kernels. */
 int m3ae_set_attention_backend(int32_t backend) { g_attn_backend = backend; return M3AE_OK; }
 int m3ae_set_gemm_epilogue(int32_t generic) { force_generic_epilogue = generic != 0; return M3AE_OK; }
+/* Test hook: 1 = LayerNorm backward loads rows through registers only (cross-checks the bulk-copy ring), 0 = auto. */
+int m3ae_set_layernorm_bwd_staging(int32_t registers_only) { ln_bwd_force_registers = registers_only != 0; return M3AE_OK; }
 int m3ae_set_gemm_cta_pair(int32_t mode) {
   M3AE_CHECK(mode >= 0 && mode <= 2, M3AE_ERR_INVALID, "m3ae_set_gemm_cta_pair: mode %d not in {0 auto, 1 single CTA, 2 CTA pair}", mode);
   gemm_cta_pair_mode = mode;

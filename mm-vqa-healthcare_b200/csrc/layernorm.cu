@@ -1,6 +1,8 @@
 // LayerNorm forward/backward, one warp per row, 128-bit vector loads, fp32 two-pass statistics.
 // HBM-bound: forward moves 2*M*H*sizeof(T) (+8*M) bytes, backward 3*M*H*sizeof(T) (+8*M).
 // Reference: nn.LayerNorm at bert_model.py:363,441 (eps=1e-12), m3ae_module.py:122, m3ae_decoder.py:46-49.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace m3ae {
@@ -105,8 +107,18 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const T* __restri
 // Backward: each warp walks rows row0, row0+stride, ... and keeps per-lane column partials of
 // dgamma / dbeta / colsum(dx) in registers; one smem reduction + one atomicAdd per column per CTA.
 // The next row's x and dy are already in flight (packed, 2*HV registers) while the current row is reduced.
+// RING (bf16): rows are staged through a per-warp shared-memory ring of LN_RING rows (x and dy, 2 x H x 2 B each) filled
+// by cp.async.bulk with one mbarrier per slot.  The register version keeps ONE 3 KB row in flight per warp and the kernel
+// needs 168 registers (12 warps/SM): 36 KB in flight per SM capped it at ~2.7 TB/s; the ring keeps LN_RING rows in flight
+// per warp without spending registers on them.
 constexpr int LN_BWD_CTAS_PER_SM = 3;
-template <typename T, int HV>
+constexpr int LN_RING = 3;
+__device__ __forceinline__ void bulk_load_row(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"((uint64_t)gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+template <typename T, int HV, bool RING>
 __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
                                                               const float* __restrict__ gamma, T* __restrict__ dx,
@@ -115,8 +127,18 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
                                                               T* __restrict__ dx_drop, float drop_p, uint64_t drop_seed,
                                                               uint64_t drop_stream, const uint8_t* __restrict__ drop_bits) {
   constexpr int VN = Vec<T>::N;
-  extern __shared__ float red[];  // [LN_WARPS][H]
+  extern __shared__ __align__(128) float red[];  // [LN_WARPS][H] floats | RING: [LN_WARPS][LN_RING][2][H] T | [LN_WARPS][LN_RING] barriers
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t row_bytes = (uint32_t)(H * sizeof(T));
+  uint8_t* ring = reinterpret_cast<uint8_t*>(red + LN_WARPS * H) + (size_t)warp * LN_RING * 2 * row_bytes;
+  uint64_t* rbar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(red + LN_WARPS * H) + (size_t)LN_WARPS * LN_RING * 2 * row_bytes) + warp * LN_RING;
+  if (RING) {
+    if (lane == 0) {
+      for (int s = 0; s < LN_RING; ++s) mbar_init(&rbar[s], 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+  }
   float g[HV][VN], pg[HV][VN], pb[HV][VN], pc[HV][VN];
 #pragma unroll
   for (int i = 0; i < HV; ++i) {
@@ -133,11 +155,27 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
   uint8_t kb[NB];
   const bool cached = VN == 8 && drop_bits != nullptr;
   float mu = 0.f, rs = 0.f;
+  // RING: lane 0 starts the copies of row `r` into slot `k % LN_RING`
+  auto ring_issue = [&](int k, int64_t r) {
+    uint8_t* slot = ring + (size_t)(k % LN_RING) * 2 * row_bytes;
+    uint64_t* bar = &rbar[k % LN_RING];
+    mbar_expect_tx(bar, 2 * row_bytes);
+    bulk_load_row(slot, x + r * H, row_bytes, bar);
+    bulk_load_row(slot + row_bytes, dy + r * H, row_bytes, bar);
+  };
+  int kiter = 0;
+  if (RING) {
+    if (lane == 0)
+      for (int k = 0; k < LN_RING; ++k)
+        if (row + k * stride < M) ring_issue(k, row + k * stride);
+  }
   if (row < M) {
+    if (!RING) {
 #pragma unroll
-    for (int i = 0; i < HV; ++i) {
-      rx[i] = ld_raw(x + row * H + (i * 32 + lane) * VN);
-      rdy[i] = ld_raw(dy + row * H + (i * 32 + lane) * VN);
+      for (int i = 0; i < HV; ++i) {
+        rx[i] = ld_raw(x + row * H + (i * 32 + lane) * VN);
+        rdy[i] = ld_raw(dy + row * H + (i * 32 + lane) * VN);
+      }
     }
     if (cached) {
 #pragma unroll
@@ -145,9 +183,25 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
     }
     mu = mean[row]; rs = rstd[row];
   }
-  for (; row < M; row += stride) {
+  for (; row < M; row += stride, ++kiter) {
     float xh[HV][VN], gd[HV][VN];
     float c1 = 0.f, c2 = 0.f;
+    if (RING) {
+      const int slot_i = kiter % LN_RING;
+      mbar_wait(&rbar[slot_i], (uint32_t)((kiter / LN_RING) & 1));
+      const uint8_t* slot = ring + (size_t)slot_i * 2 * row_bytes;
+#pragma unroll
+      for (int i = 0; i < HV; ++i) {
+        rx[i] = *reinterpret_cast<const uint4*>(slot + (i * 32 + lane) * 16);
+        rdy[i] = *reinterpret_cast<const uint4*>(slot + row_bytes + (i * 32 + lane) * 16);
+      }
+      __syncwarp();  // every lane holds its share in registers: the slot may be refilled
+      const int64_t rr = row + (int64_t)LN_RING * stride;
+      if (lane == 0 && rr < M) {
+        fence_proxy_async();
+        ring_issue(kiter + LN_RING, rr);
+      }
+    }
     const float mu_c = mu, rs_c = rs;
 #pragma unroll
     for (int i = 0; i < HV; ++i) {
@@ -169,10 +223,12 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
 #pragma unroll
     for (int i = 0; i < NB; ++i) kc[i] = cached ? kb[i] : (uint8_t)0;
     if (nrow < M) {  // prefetch: the loads fly during the reductions and the dropout regeneration below
+      if (!RING) {
 #pragma unroll
-      for (int i = 0; i < HV; ++i) {
-        rx[i] = ld_raw(x + nrow * H + (i * 32 + lane) * VN);
-        rdy[i] = ld_raw(dy + nrow * H + (i * 32 + lane) * VN);
+        for (int i = 0; i < HV; ++i) {
+          rx[i] = ld_raw(x + nrow * H + (i * 32 + lane) * VN);
+          rdy[i] = ld_raw(dy + nrow * H + (i * 32 + lane) * VN);
+        }
       }
       if (cached) {
 #pragma unroll
@@ -409,6 +465,8 @@ int layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
   return M3AE_OK;
 }
 
+bool ln_bwd_force_registers = false;  // test hook (m3ae_set_layernorm_bwd_staging): bypass the shared-memory ring
+
 int layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, void* dx,
                   float* dgamma, float* dbeta, float* dcolsum, int64_t M, int H, int dtype, void* dx_drop, float drop_p,
                   uint64_t drop_seed, uint64_t drop_stream, const uint32_t* drop_bits, cudaStream_t st) {
@@ -421,13 +479,24 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   const int64_t cap = (int64_t)sm_count() * LN_BWD_CTAS_PER_SM;  // persistent: exactly the resident CTAs
   const unsigned grid = (unsigned)(want < cap ? want : cap);
   const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
-#define LN_BWD(T, HV)                                                                                                     \
-  ln_bwd_kernel<T, HV><<<grid, LN_WARPS * 32, smem, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
-                                                          dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream, (const uint8_t*)drop_bits)
-  if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3);
-  else if (dtype == M3AE_BF16 && H == 1536) LN_BWD(bf16, 6);
-  else if (dtype == M3AE_F32 && H == 768) LN_BWD(float, 6);
-  else if (dtype == M3AE_F32 && H == 1536) LN_BWD(float, 12);
+#define LN_BWD(T, HV, RING, SMEM)                                                                                              \
+  ln_bwd_kernel<T, HV, RING><<<grid, LN_WARPS * 32, SMEM, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
+                                                                dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream, (const uint8_t*)drop_bits)
+  // the fusion stack's case (bf16, H = 768): rows staged through the bulk-copy ring (needs 16-byte aligned rows)
+  const bool ring_ok = dtype == M3AE_BF16 && H == 768 && !ln_bwd_force_registers && ((((uintptr_t)x) | ((uintptr_t)dy)) & 15) == 0;
+  if (ring_ok) {
+    const size_t smem_ring = smem + (size_t)LN_WARPS * LN_RING * 2 * H * sizeof(bf16) + (size_t)LN_WARPS * LN_RING * sizeof(uint64_t);
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(once, [smem_ring] {
+      attr_err = cudaFuncSetAttribute(ln_bwd_kernel<bf16, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ring);
+    });
+    M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(ln_bwd ring smem) failed: %s", cudaGetErrorString(attr_err));
+    LN_BWD(bf16, 3, true, smem_ring);
+  } else if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3, false, smem);
+  else if (dtype == M3AE_BF16 && H == 1536) LN_BWD(bf16, 6, false, smem);
+  else if (dtype == M3AE_F32 && H == 768) LN_BWD(float, 6, false, smem);
+  else if (dtype == M3AE_F32 && H == 1536) LN_BWD(float, 12, false, smem);
   else M3AE_CHECK(false, M3AE_ERR_UNSUPPORTED, "layernorm: unsupported (dtype=%d, H=%d); H must be 768 or 1536", dtype, H);
 #undef LN_BWD
   count_launch();

@@ -45,6 +45,11 @@ def set_gemm_epilogue(generic):
     L.check(L.load().m3ae_set_gemm_epilogue(1 if generic else 0), "m3ae_set_gemm_epilogue")
 
 
+def set_layernorm_bwd_staging(registers_only):
+    """Test hook: True = LayerNorm backward without the bulk-copy staging ring."""
+    L.check(L.load().m3ae_set_layernorm_bwd_staging(1 if registers_only else 0), "m3ae_set_layernorm_bwd_staging")
+
+
 def set_gemm_cta_pair(mode):
     """0 auto, 1 one CTA per 128x256 tile, 2 CTA pairs (tcgen05.mma.cta_group::2, 256x256 tiles)."""
     L.check(L.load().m3ae_set_gemm_cta_pair(int(mode)), "m3ae_set_gemm_cta_pair")

@@ -470,3 +470,30 @@ def test_hidden_dropout_keep_bits_cache(generic):
         outs.append((dx, dxd, dc))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
     assert rel_err(outs[1][2], outs[0][2]) < 1e-5
+
+
+@pytest.mark.parametrize("M", [1, 5, 1777, 20800])
+@pytest.mark.parametrize("drop", [0.0, 0.1])
+def test_layernorm_bwd_staging_ring_matches_register_path(M, drop):
+    """bf16 / H = 768 LayerNorm backward stages rows through a cp.async.bulk shared-memory ring; the register-prefetch
+    variant computes every row with the same instructions, so dx / dx_drop must be bit-identical and the column
+    reductions (fp32 atomics in arrival order) equal to rounding.  M = 1, 5: fewer rows than warps / ring slots."""
+    H = 768
+    bf = torch.bfloat16
+    x, dy = rnd(M, H, dtype=bf, seed=1), rnd(M, H, dtype=bf, seed=2)
+    gamma, beta = rnd(H, seed=3), rnd(H, seed=4)
+    _, mean, rstd = ops.layernorm_fwd(x, gamma, beta, 1e-12)
+    res = []
+    try:
+        for regs_only in (True, False):
+            ops.set_layernorm_bwd_staging(regs_only)
+            dg, db_, dc = (torch.zeros(H, device=DEV) for _ in range(3))
+            r = ops.layernorm_bwd(dy, x, mean, rstd, gamma, dg, db_, dc, drop_p=drop, drop_seed=5, drop_stream=1)
+            torch.cuda.synchronize()
+            res.append((r if isinstance(r, tuple) else (r,), dg, db_, dc))
+    finally:
+        ops.set_layernorm_bwd_staging(False)
+    for a, b in zip(res[0][0], res[1][0]):
+        assert torch.equal(a, b)
+    for a, b in zip(res[0][1:], res[1][1:]):
+        assert rel_err(b, a) < 1e-5
