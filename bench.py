@@ -106,9 +106,12 @@ def run_ours(args):
     torch.manual_seed(0)
     model = M3AEFusion({"drop_rate": 0.1, "precision": 16 if dtype == torch.bfloat16 else 32}, compute_dtype=dtype).to(dev).train()
     params = [p for p in model.parameters()]
+    init_probe = params[0].detach().clone()
     opt = torch.optim.AdamW(params, lr=5e-6, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01, fused=True)
     from m3ae_b200.ddp import GradientAllReducer
-    reducer = GradientAllReducer(params, world) if world > 1 else None
+    # M3AE_BENCH_FORCE_REDUCER=1: diagnostic — run the N>1 gradient bookkeeping (bucket views, accumulate, zero) on one GPU
+    force_reducer = os.environ.get("M3AE_BENCH_FORCE_REDUCER", "0") == "1"
+    reducer = GradientAllReducer(params, world) if (world > 1 or force_reducer) else None
 
     def step(b):
         if reducer is not None:
@@ -177,38 +180,52 @@ def run_ours(args):
         sampler.join(timeout=2)
 
     # ---- roofline of the dominant kernel (tcgen05 GEMM): instrumented pass, CUDA events around every GEMM launch
+    # EVERY rank runs these steps: each step launches the gradient all-reduce, so a rank-0-only pass deadlocks N > 1
+    # (rank 0 inside the collective, the others in the barrier below).  Only rank 0 reports.
     gemm_time_ms, gemm_flops, gemm_n = 0.0, 0.0, 0
-    if rank == 0:
-        records = []
-        import m3ae_b200.functional as Fn
-        orig_group, orig_run = ops.gemm_group, Fn._Gemm.run
+    records = []
+    import m3ae_b200.functional as Fn
+    orig_group, orig_run = ops.gemm_group, Fn._Gemm.run
 
-        def timed_launch(launch, flops):
-            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            launch()
-            b_.record()
-            records.append((a, b_, flops))
+    def timed_launch(launch, flops):
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        launch()
+        b_.record()
+        records.append((a, b_, flops))
 
-        def group_instrumented(specs, backend=ops.GEMM_AUTO):
-            timed_launch(lambda: orig_group(specs, backend), sum(2.0 * s.problem.M * s.problem.N * s.problem.K for s in specs))
+    def group_instrumented(specs, backend=ops.GEMM_AUTO):
+        timed_launch(lambda: orig_group(specs, backend), sum(2.0 * s.problem.M * s.problem.N * s.problem.K for s in specs))
 
-        def run_instrumented(self, be, stream):
-            timed_launch(lambda: orig_run(self, be, stream), sum(2.0 * q.M * q.N * q.K for q in self.arr))
+    def run_instrumented(self, be, stream):
+        timed_launch(lambda: orig_run(self, be, stream), sum(2.0 * q.M * q.N * q.K for q in self.arr))
 
-        ops.gemm_group = group_instrumented  # looked up on the module at call time
-        Fn._Gemm.run = run_instrumented       # cached launches of the fused layer node
-        try:
-            n_prof = min(args.steps, 3)
-            for i in range(n_prof):
-                step(batches[i % 2])
-            torch.cuda.synchronize()
-        finally:
-            ops.gemm_group, Fn._Gemm.run = orig_group, orig_run
-        gemm_time_ms = sum(a.elapsed_time(b_) for a, b_, _ in records)
-        gemm_flops = sum(f for _, _, f in records)
-        gemm_n = len(records) // max(1, n_prof)
+    ops.gemm_group = group_instrumented  # looked up on the module at call time
+    Fn._Gemm.run = run_instrumented       # cached launches of the fused layer node
+    try:
+        n_prof = min(args.steps, 3)
+        for i in range(n_prof):
+            step(batches[i % 2])
+        torch.cuda.synchronize()
+    finally:
+        ops.gemm_group, Fn._Gemm.run = orig_group, orig_run
+    gemm_time_ms = sum(a.elapsed_time(b_) for a, b_, _ in records)
+    gemm_flops = sum(f for _, _, f in records)
+    gemm_n = len(records) // max(1, n_prof)
     barrier()
+    # N > 1: every rank started from the same seed and saw different batches, so the replicas are still bit-identical
+    # if and only if every step applied the same (averaged) gradients — the GPU-side check of the gradient exchange.
+    in_sync = None
+    if world > 1:
+        with torch.no_grad():
+            digest = torch.stack([p.detach().double().sum() for p in params] + [p.detach().double().abs().sum() for p in params])
+        lo, hi = digest.clone(), digest.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        in_sync = bool(torch.equal(lo, hi))
+        moved = bool((params[0].detach() != init_probe).any().item())  # and the optimizer did move the weights
+        if not (in_sync and moved):
+            raise RuntimeError(f"data-parallel replicas diverged or did not train (in_sync={in_sync}, moved={moved}): the gradient exchange is broken")
 
     if rank == 0:
         pk = peaks()
@@ -229,6 +246,7 @@ def run_ours(args):
             "e2e": {"value": round(sps_e2e, 2), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(ms_e2e / args.steps, 3)},
             "gpu_launches": int(launches), "host_issue_ms_per_step": round(host_issue_ms, 3),
+            "replicas_in_sync": in_sync,
             "roofline": {"bound": "tensor", "achieved": round(achieved, 1) if achieved else None, "peak": pk["tflops"], "unit": "TFLOP/s",
                          "frac": round(achieved / pk["tflops"], 4) if achieved else None, "traffic": None,
                          "kernel": "gemm_tcgen05_kernel", "launches_per_step": gemm_n, "peak_source": pk["source"],
@@ -366,9 +384,14 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="per-GPU batch (BASELINE config[1]: 64)")
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--watchdog", type=int, default=1500,
+                    help="seconds after which a stuck rank dumps every thread's Python stack to stderr and exits 1 (0 = off)")
     ap.add_argument("--workload", default="finetune", choices=["finetune", "decoder"],
                     help="finetune = BASELINE config[1] (default, the headline); decoder = config[2] greedy decoding")
     args = ap.parse_args()
+    if args.watchdog > 0:  # a hung collective or kernel must fail loudly, not hang the caller
+        import faulthandler
+        faulthandler.dump_traceback_later(args.watchdog, exit=True)
     if args.workload == "decoder":
         run_decoder(args)
     elif args.impl == "reference":

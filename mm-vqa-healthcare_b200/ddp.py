@@ -12,16 +12,54 @@ import torch.distributed as dist
 
 
 class GradientAllReducer:
-    def __init__(self, params, world_size=None, bucket_mb=64, group=None):
+    """Gradient exchange for one-process-per-GPU data parallelism.
+
+    Zero-copy groups.  The fused BertCrossLayer node returns the 26 parameter gradients of a layer as views of ONE flat
+    fp32 buffer (functional.py::_backward_streams).  When `.grad` is None, autograd adopts such a view without copying,
+    so the reducer all-reduces the layer's buffer IN PLACE as soon as the layer's last gradient has landed: no bucket
+    copy, no per-parameter accumulate kernel, no bucket zero fill (those cost 1.4 ms of a 15.2 ms step when every
+    gradient was accumulated into pre-assigned bucket views — measured with M3AE_BENCH_FORCE_REDUCER=1).
+    Groups are discovered on the first exchange: parameters whose gradients share one storage that they cover exactly.
+    Bucketed parameters.  Everything else (heads, poolers, projections; every parameter of a model whose gradients do
+    not share storage) keeps `.grad` as a view into flat fp32 buckets that are all-reduced when complete.
+
+    Use: `zero_grad()` before every backward, `wait()` after it, then the optimizer step.  One backward per exchange.
+    """
+
+    def __init__(self, params, world_size=None, bucket_mb=None, group=None, overlap=None, zero_copy=None):
+        """overlap=True: an exchange starts from the grad hook of its last gradient, concurrently with the rest of
+        backward; False: everything is exchanged from wait().  Defaults: environment M3AE_DDP_OVERLAP (0/1, default 1),
+        M3AE_DDP_BUCKET_MB (default 64; size does not matter between 16 and 128, profiles/r1_ddp_ab_n2.txt),
+        M3AE_DDP_ZERO_COPY (0/1, default 1)."""
+        import os
+        if overlap is None:
+            overlap = os.environ.get("M3AE_DDP_OVERLAP", "1") != "0"
+        if zero_copy is None:
+            zero_copy = os.environ.get("M3AE_DDP_ZERO_COPY", "1") != "0"
+        if bucket_mb is None:
+            bucket_mb = float(os.environ.get("M3AE_DDP_BUCKET_MB", "64"))
+        self.overlap, self.zero_copy, self.bucket_mb = bool(overlap), bool(zero_copy), bucket_mb
         self.params = [p for p in params if p.requires_grad]
         self.world = world_size if world_size is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.group = group
-        self.buckets = []  # (flat, [params])
-        self._pending = {}
-        self._works = []
-        cap = bucket_mb * (1 << 20) // 4
+        self.cuda = self.params[0].is_cuda
+        self.comm_stream = torch.cuda.Stream() if self.cuda else None
+        self.buckets = []        # (flat, [params]) — bucketed parameters
+        self.groups = []         # [params] — zero-copy groups
+        self._slot = {}          # id(param) -> ("b", bucket index) | ("g", group index)
+        self._pending, self._launched, self._works = {}, {}, []
+        self._learned = not self.zero_copy
+        for p in self.params:
+            p.register_post_accumulate_grad_hook(self._hook)
+        if self._learned:
+            self._build_buckets(self.params)
+        self.zero_grad()
+
+    # ------------------------------------------------------------------ construction
+    def _build_buckets(self, ps_all):
+        cap = int(self.bucket_mb * (1 << 20)) // 4
         cur, cur_n = [], 0
-        for p in reversed(self.params):
+        for p in reversed(ps_all):  # reverse registration order ~ reverse execution order
             if cur and cur_n + p.numel() > cap:
                 self._make_bucket(cur)
                 cur, cur_n = [], 0
@@ -29,60 +67,108 @@ class GradientAllReducer:
             cur_n += p.numel()
         if cur:
             self._make_bucket(cur)
-        self.cuda = self.params[0].is_cuda
-        self.comm_stream = torch.cuda.Stream() if self.cuda else None
-        for bi, (_, ps) in enumerate(self.buckets):
-            for p in ps:
-                p.register_post_accumulate_grad_hook(self._make_hook(bi))
-        self.zero_grad()
 
     def _make_bucket(self, ps):
         n = sum(p.numel() for p in ps)
         flat = torch.zeros(n, dtype=torch.float32, device=ps[0].device)
         off = 0
         for p in ps:
-            p.grad = flat[off:off + p.numel()].view_as(p)
+            view = flat[off:off + p.numel()].view_as(p)
+            if p.grad is not None:
+                view.copy_(p.grad)
+            p.grad = view
+            self._slot[id(p)] = ("b", len(self.buckets))
             off += p.numel()
         self.buckets.append((flat, list(ps)))
 
-    def _make_hook(self, bi):
-        def hook(param):
-            self._pending[bi] -= 1
-            if self._pending[bi] == 0:
-                self._launch(bi)
-        return hook
+    def _learn(self):
+        """First exchange: find the parameters whose gradients tile one storage exactly (a fused layer's flat buffer)."""
+        by_storage = {}
+        for p in self.params:
+            if p.grad is not None and p.grad.is_contiguous() and p.grad.dtype == torch.float32:
+                by_storage.setdefault(p.grad.untyped_storage().data_ptr(), []).append(p)
+        grouped = set()
+        for ps in by_storage.values():
+            if len(ps) >= 2 and sum(p.numel() for p in ps) * 4 == ps[0].grad.untyped_storage().nbytes():
+                for p in ps:
+                    self._slot[id(p)] = ("g", len(self.groups))
+                    grouped.add(id(p))
+                self.groups.append(list(ps))
+        self._build_buckets([p for p in self.params if id(p) not in grouped])
+        self._learned = True
 
+    # ------------------------------------------------------------------ per step
     def zero_grad(self):
         self._works = []
+        if not self._learned:
+            for p in self.params:
+                p.grad = None
+            return
+        for gi, ps in enumerate(self.groups):
+            for p in ps:
+                p.grad = None  # autograd adopts the layer's flat-buffer views: no copy
+            self._pending["g", gi], self._launched["g", gi] = len(ps), False
         for bi, (flat, ps) in enumerate(self.buckets):
             flat.zero_()
-            self._pending[bi] = len(ps)
+            self._pending["b", bi], self._launched["b", bi] = len(ps), False
             off = 0
             for p in ps:  # re-attach views if an optimizer/zero_grad(set_to_none=True) dropped them
                 if p.grad is None or p.grad.data_ptr() != flat.data_ptr() + 4 * off:
                     p.grad = flat[off:off + p.numel()].view_as(p)
                 off += p.numel()
 
-    def _launch(self, bi):
+    def _hook(self, param):
+        if not self._learned:
+            return
+        key = self._slot[id(param)]
+        self._pending[key] -= 1
+        if self._pending[key] == 0 and self.overlap:
+            self._launched[key] = True
+            self._launch(key)
+
+    def _flat_of(self, key):
+        kind, i = key
+        if kind == "b":
+            return self.buckets[i][0]
+        ps = [p for p in self.groups[i] if p.grad is not None]
+        if not ps:
+            return None  # the layer took no part in this backward
+        st = ps[0].grad.untyped_storage()
+        same = all(p.grad.untyped_storage().data_ptr() == st.data_ptr() for p in ps)
+        if not same or len(ps) != len(self.groups[i]) or sum(p.numel() for p in ps) * 4 != st.nbytes():
+            return [p.grad for p in ps]  # layout changed since the first step: exchange the gradients one by one
+        return torch.empty(0, dtype=torch.float32, device=ps[0].device).set_(st)
+
+    def _launch(self, key):
         if self.world == 1:
             return
-        flat = self.buckets[bi][0]
+        flat = self._flat_of(key)
+        if flat is None:
+            return
+        tensors = flat if isinstance(flat, list) else [flat]
         if self.cuda:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.comm_stream):
-                flat.mul_(1.0 / self.world)
-                self._works.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+                for t in tensors:  # NCCL averages inside the reduction: no separate pre-scale pass
+                    self._works.append(dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
         else:
-            flat.mul_(1.0 / self.world)
-            self._works.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            for t in tensors:
+                t.mul_(1.0 / self.world)
+                self._works.append(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
 
     def wait(self):
-        """Call after backward(): launches any bucket whose hook count did not reach zero (unused parameters) and makes
-        the compute stream wait for all exchanges."""
-        for bi in range(len(self.buckets)):
-            if self._pending[bi] > 0:
-                self._pending[bi] = 0
-                self._launch(bi)
+        """Call after backward(): starts every exchange that has not started (first step, overlap=False, parameters
+        without a gradient) and makes the compute stream wait for all of them."""
+        if not self._learned:
+            self._learn()
+            for gi in range(len(self.groups)):
+                self._launched["g", gi] = False
+            for bi in range(len(self.buckets)):
+                self._launched["b", bi] = False
+        for key in [("g", i) for i in range(len(self.groups))] + [("b", i) for i in range(len(self.buckets))]:
+            if not self._launched.get(key, False):
+                self._launched[key] = True
+                self._launch(key)
         for w in self._works:
             w.wait()
         if self.cuda and self.world > 1:
@@ -90,4 +176,4 @@ class GradientAllReducer:
         self._works = []
 
     def payload_bytes(self):
-        return sum(f.numel() * 4 for f, _ in self.buckets)
+        return sum(p.numel() * 4 for p in self.params)
