@@ -40,6 +40,16 @@ def peaks():
     return {"tflops": 1400.0, "tflops_burst": 1590.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def gemm_traffic():
+    """Per-launch DRAM bytes of the dominant kernel from the committed `ncu --set full` capture (tools/gemm_traffic.py)."""
+    p = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    d = json.load(open(p))
+    return d.get("avg_dram_bytes_per_launch"), (f"profiles/r1_gemm_traffic.json: mean of 6 forward launches of one layer pair, "
+                                                 f"algorithmic mean {d.get('avg_algorithmic_bytes_per_launch')} B")
+
+
 def synth_batch(B, device, seed, pin=False):
     """Seeded synthetic hot-path inputs: uni-modal encoder outputs of the shapes RoBERTa-base / CLIP ViT-B/16 give at
     288 px / 32 tokens, ragged text masks (valid length uniform in [8,32]), one-hot VQA targets."""
@@ -248,7 +258,8 @@ def run_ours(args):
             "gpu_launches": int(launches), "host_issue_ms_per_step": round(host_issue_ms, 3),
             "replicas_in_sync": in_sync,
             "roofline": {"bound": "tensor", "achieved": round(achieved, 1) if achieved else None, "peak": pk["tflops"], "unit": "TFLOP/s",
-                         "frac": round(achieved / pk["tflops"], 4) if achieved else None, "traffic": None,
+                         "frac": round(achieved / pk["tflops"], 4) if achieved else None, "traffic": gemm_traffic()[0],
+                         "traffic_source": gemm_traffic()[1],
                          "kernel": "gemm_tcgen05_kernel", "launches_per_step": gemm_n, "peak_source": pk["source"],
                          "how": "sum of 2MNK over every GEMM launch of a step / sum of CUDA-event durations (instrumented pass, same stream)"},
             "fusion_stack_tflops": round(stack_tflops, 1),
