@@ -293,7 +293,7 @@ def run_decoder(args):
     for i in range(max(args.warmup, 3)):
         dec.search_path(mems[i % 2], Tok)
     torch.cuda.synchronize()
-    l0 = ops.launch_count()
+    l0, g0 = ops.launch_count(), dec.graph_replayed_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
@@ -301,7 +301,7 @@ def run_decoder(args):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / args.steps
-    launches = ops.launch_count() - l0
+    launches = (ops.launch_count() - l0) + (dec.graph_replayed_launches - g0)  # eager calls + kernels replayed from the CUDA graph
     pk = peaks()
     # algorithmic bytes per greedy step (bf16): live layer weights + vocab projection + cross K/V cache + self K/V cache
     w_bytes = (3 * 768 * 768 + 768 * 768 + 768 * 768 + 768 * 768 + 2 * 768 * 3072 + 30522 * 768) * 2

@@ -405,6 +405,132 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
   }
 }
 
+// bf16 decode attention built for bandwidth (the cross-attention step streams B*Lm*1536*2 B = 141 MB of cached K/V).
+// The generic kernel above walks the keys one by one per warp (2-byte loads -> shuffle reduction -> exp -> V loads, a
+// dependent chain per key: ~1 us per key, 102 us per call at B=128, Lm=359).  Here every phase issues independent 16-byte
+// loads: (1) scores, 4 lanes per key, 32 keys per CTA iteration; (2) block softmax over the scores in shared memory;
+// (3) O = P V with one thread per (16-byte slice of the head dimension, key residue), reduced through shared memory.
+constexpr int DEC_MAX_LEN = 1024;
+template <int DH>
+__global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __restrict__ q, int64_t ldq, const bf16* __restrict__ kc,
+                                                              const bf16* __restrict__ vc, int64_t ldk, int64_t ldv, int64_t bsk,
+                                                              int64_t bsv, bf16* __restrict__ out, int64_t ldo, int H, int len,
+                                                              float scale) {
+  constexpr int NCH = DH / 8;        // 16-byte chunks per row (12 for dh 96, 8 for dh 64)
+  constexpr int CPL = NCH / 4;       // chunks per lane in the score phase (4 lanes per key)
+  constexpr int NG = 128 / NCH;      // key residues in the P V phase (10 / 16)
+  __shared__ float sc[DEC_MAX_LEN];
+  __shared__ float red[4];
+  __shared__ float part[NG][DH];
+  const int b = blockIdx.x / H, h = blockIdx.x % H;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bf16* Q = q + (size_t)b * ldq + (size_t)h * DH;
+  const bf16* K = kc + (size_t)b * bsk + (size_t)h * DH;
+  const bf16* V = vc + (size_t)b * bsv + (size_t)h * DH;
+  // ---- (1) scores: lane quad `kq` of the CTA takes keys kq, kq+32, ...; lane `sub` of the quad takes chunks sub*CPL..
+  const int kq = tid >> 2, sub = tid & 3;
+  float qf[CPL][8];
+#pragma unroll
+  for (int c = 0; c < CPL; ++c) {
+    const uint4 w = *reinterpret_cast<const uint4*>(Q + (sub * CPL + c) * 8);
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(ww[j]);
+      qf[c][2 * j] = f.x * scale;
+      qf[c][2 * j + 1] = f.y * scale;
+    }
+  }
+  float mloc = -INFINITY;
+  for (int j0 = 0; j0 < len; j0 += 64) {  // two keys in flight per thread
+    float s2[2] = {0.f, 0.f};
+    uint4 kw[2][CPL];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int j = j0 + u * 32 + kq;
+      if (j < len) {
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) kw[u][c] = __ldg(reinterpret_cast<const uint4*>(K + (size_t)j * ldk + (sub * CPL + c) * 8));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int j = j0 + u * 32 + kq;
+      if (j < len) {
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) {
+          const uint32_t ww[4] = {kw[u][c].x, kw[u][c].y, kw[u][c].z, kw[u][c].w};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float2 f = unpack_bf16x2(ww[t]);
+            s2[u] = fmaf(qf[c][2 * t], f.x, s2[u]);
+            s2[u] = fmaf(qf[c][2 * t + 1], f.y, s2[u]);
+          }
+        }
+      }
+      // the 4 lanes of a quad hold partial dot products of the same key (all 32 lanes take part in the shuffles)
+      s2[u] += __shfl_xor_sync(0xffffffffu, s2[u], 1);
+      s2[u] += __shfl_xor_sync(0xffffffffu, s2[u], 2);
+      if (j < len) {
+        if (sub == 0) sc[j] = s2[u];
+        mloc = fmaxf(mloc, s2[u]);
+      }
+    }
+  }
+  // ---- (2) softmax over sc[0..len)
+  mloc = warp_max(mloc);
+  if (lane == 0) red[warp] = mloc;
+  __syncthreads();
+  const float m = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+  __syncthreads();
+  float lsum = 0.f;
+  for (int j = tid; j < len; j += 128) {
+    const float p = __expf(sc[j] - m);
+    sc[j] = p;
+    lsum += p;
+  }
+  lsum = warp_sum(lsum);
+  if (lane == 0) red[warp] = lsum;
+  __syncthreads();
+  const float inv_l = 1.0f / ((red[0] + red[1]) + (red[2] + red[3]));
+  // ---- (3) O = P V: thread = (chunk ch, key residue g); keys g, g+NG, ...; 4 keys in flight
+  const int ch = tid % NCH, g = tid / NCH;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (g < NG) {
+    for (int j0 = g; j0 < len; j0 += 4 * NG) {
+      uint4 vw[4];
+      float p[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + u * NG;
+        p[u] = j < len ? sc[j] : 0.f;
+        vw[u] = j < len ? __ldg(reinterpret_cast<const uint4*>(V + (size_t)j * ldv + ch * 8)) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t ww[4] = {vw[u].x, vw[u].y, vw[u].z, vw[u].w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = unpack_bf16x2(ww[t]);
+          acc[2 * t] = fmaf(p[u], f.x, acc[2 * t]);
+          acc[2 * t + 1] = fmaf(p[u], f.y, acc[2 * t + 1]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) part[g][ch * 8 + i] = acc[i];
+  }
+  __syncthreads();
+  if (tid < DH) {
+    float o = 0.f;
+#pragma unroll
+    for (int gg = 0; gg < NG; ++gg) o += part[gg][tid];
+    out[(size_t)b * ldo + (size_t)h * DH + tid] = __float2bfloat16_rn(o * inv_l);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) argmax_rows_kernel(const T* __restrict__ x, int64_t ld, int64_t* __restrict__ out, int N) {
   __shared__ float sv[8];
@@ -544,6 +670,15 @@ int decode_attn(const void* q, int64_t ldq, const void* kc, const void* vc, int6
                 void* out, int64_t ldo, int B, int H, int len, int dh, float scale, int dtype, cudaStream_t st) {
   M3AE_CHECK(B > 0 && H > 0 && len > 0, M3AE_ERR_INVALID, "decode_attn: empty shape");
   M3AE_CHECK(dh == 64 || dh == 96, M3AE_ERR_UNSUPPORTED, "decode_attn: head dim %d unsupported", dh);
+  // bf16 with 16-byte aligned rows and a cache that fits the score buffer: the bandwidth kernel
+  if (dtype == M3AE_BF16 && len <= DEC_MAX_LEN && ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && bsk % 8 == 0 && bsv % 8 == 0 &&
+      ((((uintptr_t)q) | ((uintptr_t)kc) | ((uintptr_t)vc)) & 15) == 0) {
+    if (dh == 64) decode_attn_bf16_kernel<64><<<B * H, 128, 0, st>>>((const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
+    else decode_attn_bf16_kernel<96><<<B * H, 128, 0, st>>>((const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
+    count_launch();
+    M3AE_CUDA(cudaGetLastError());
+    return M3AE_OK;
+  }
 #define DA(T, DH) decode_attn_kernel<T, DH><<<B * H, 128, 0, st>>>((const T*)q, ldq, (const T*)kc, (const T*)vc, ldk, ldv, bsk, bsv, (T*)out, ldo, H, len, scale)
   if (dtype == M3AE_BF16) { if (dh == 64) DA(bf16, 64); else DA(bf16, 96); }
   else { if (dh == 64) DA(float, 64); else DA(float, 96); }

@@ -123,3 +123,30 @@ def test_greedy_batch128_matches_oracle_fp32_and_bf16_agreement():
     first = (ids16[:, 0] == ids[:, 0]).float().mean().item()
     print(f"bf16 vs fp32 greedy: identical sequences {agree:.3f}, identical first token {first:.3f}")
     assert first > 0.9
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_greedy_cuda_graph_replay_equals_eager_program(dtype):
+    """search_path replays a captured CUDA graph of the greedy program: it must return exactly what the eager program
+    returns — on the capturing call, on replays with other inputs, after an in-place change of an fp32 master
+    (read at replay time) and after a differentiated forward (operand cache invalidated -> re-capture)."""
+    sd = O.make_decoder_state(31)
+    dec = make_decoder(sd, dtype)
+    g = torch.Generator().manual_seed(77)
+    mems = [torch.randn(4, 359, 768, generator=g).to(DEV) for _ in range(3)]
+    for m in mems + [mems[0]]:  # first call captures, the rest replay
+        assert torch.equal(dec.search_path(m, Tok), dec.search_path(m, Tok, use_graph=False))
+    assert len(dec._graphs) == 1
+    with torch.no_grad():
+        dec.final_linear.bias[102] += 6.0  # makes [SEP] win early: the output must change and still match eager
+    a, b = dec.search_path(mems[1], Tok), dec.search_path(mems[1], Tok, use_graph=False)
+    assert torch.equal(a, b) and (a == 102).any()
+    assert len(dec._graphs) == 1
+    # a training forward invalidates the bf16 operand cache (the optimizer will move the weights): graphs are dropped
+    tgt = torch.randint(1000, 30000, (4, 6), device=DEV)
+    dec.train()(tgt, None, mems[0])[0].float().square().mean().backward()
+    with torch.no_grad():
+        dec.dec_layers[-1].ffn[0].weight.mul_(1.5)  # stands in for an optimizer step
+    dec.eval()
+    assert len(dec._graphs) == 0
+    assert torch.equal(dec.search_path(mems[2], Tok), dec.search_path(mems[2], Tok, use_graph=False))

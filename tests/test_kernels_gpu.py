@@ -351,6 +351,23 @@ def test_decode_attention_step():
         assert rel_err(out, ref) < tol
 
 
+@pytest.mark.parametrize("dh,H", [(96, 8), (64, 12)])
+@pytest.mark.parametrize("length", [1, 7, 33, 64, 359, 1100])
+def test_decode_attention_bf16_bandwidth_kernel(dh, H, length):
+    """bf16 decode attention (4 lanes per key, 16-byte loads, smem softmax) on the layouts the decoder uses: K and V are
+    the two column halves of ONE fused projection buffer [B, Lmax, 2*H*dh] (row stride 2*D, V offset by D), the cache is
+    longer than the valid length.  length 1100 exceeds the 1024-entry score buffer -> generic kernel."""
+    B, D = 3, H * dh
+    Lmax = max(length, 16) + 5
+    kv = rnd(B, Lmax, 2 * D, dtype=torch.bfloat16, seed=1)
+    kc, vc = kv[:, :, :D], kv[:, :, D:]
+    q = rnd(B, D, dtype=torch.bfloat16)
+    out = torch.empty_like(q)
+    ops.decode_attn(q, kc, vc, out, H=H, length=length, dh=dh)
+    ref, _ = _attn_ref(q, kc[:, :length].reshape(B * length, D), vc[:, :length].reshape(B * length, D), None, B, H, 1, length, dh, False)
+    assert rel_err(out, ref) < 1e-2
+
+
 def test_gemm_tma_staged_epilogue_matches_generic_epilogue():
     """The tcgen05 kernel has two epilogues (TMA-staged bf16 tiles vs per-element); same inputs must agree, including
     the dropout mask (same Philox element mapping) and ragged M / N < 256 tails."""
