@@ -1,12 +1,17 @@
-// Persistent, warp-specialised bf16 GEMM for sm_100a:
-//   TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> 3-stage smem ring -> tcgen05.mma (cta_group::1, 128x256x16,
-//   fp32 accumulators double-buffered in TMEM) -> tcgen05.ld epilogue (bias / GELU / act' / dropout / residual).
+// Persistent, warp-specialised bf16 GEMM for sm_100a.
+//   Default (CTAS = 2): a CTA PAIR (cluster of 2 on one TPC) computes a 256x256 tile with tcgen05.mma.cta_group::2.
+//     TMA (cp.async.bulk.tensor.2d.cta_group::2, SWIZZLE_128B) -> 4-stage smem ring, each CTA staging its 128 rows of A and
+//     half of B -> MMAs issued by one lane of the leader CTA (fp32 accumulators double-buffered in the TMEM of both CTAs,
+//     multicast commits) -> per-CTA tcgen05.ld epilogue (bias / GELU / act' / dropout with cached keep bits / residual).
+//   CTAS = 1: one CTA per 128x256 tile (cta_group::1, 3 stages) — launches whose problems all have M <= 128, and the
+//     cross-check of the pair kernel (bit-identical results, tests/test_kernels_gpu.py).
 //   bf16 outputs leave through swizzled 32x32 smem staging tiles and TMA stores, residual / pre-activation inputs
 //   arrive through TMA loads into the same kind of tile (each lane owns one accumulator ROW, so direct global
-//   accesses would touch 32 different lines per instruction); fp32 / split-K outputs use per-element atomics.
+//   accesses would touch 32 different lines per instruction); split-K fp32 outputs are added by TMA reduce-add tiles.
 // One launch runs up to M3AE_MAX_GROUP independent problems (the text and image streams of a fusion
 // layer pair, reference m3ae_module.py:276-277), each with K-major or MN-major operands so the same kernel
 // serves forward (A K-major, B K-major), dgrad (B MN-major) and wgrad (A and B MN-major, split-K).
+// Tiles are rasterised N-fastest when A is the larger operand, so an A panel is read from DRAM once (see the launcher).
 //
 // Algorithmic traffic per problem: (M*K + N*K) * 2 B in, M*N * sizeof(out) out; 2*M*N*K flop.
 #include <cudaTypedefs.h>
