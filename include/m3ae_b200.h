@@ -36,6 +36,8 @@ extern "C" {
 #define M3AE_ACT_NONE 0
 #define M3AE_ACT_GELU 1 /* exact erf GELU — HF ACT2FN["gelu"], bert_model.py:421 */
 #define M3AE_ACT_RELU 2 /* decoder FFN, m3ae_decoder.py:45 */
+#define M3AE_ACT_QUICKGELU 3 /* x * sigmoid(1.702 x): CLIP visual tower MLP, vision_encoders/clip_model.py:36-38 */
+#define M3AE_ACT_TANH 4 /* Pooler activation, prediction_heads.py:13,18 */
 
 #define M3AE_MAJOR_K 0  /* operand stored [rows = M or N, cols = K], K contiguous */
 #define M3AE_MAJOR_MN 1 /* operand stored [rows = K, cols = M or N], M/N contiguous */
@@ -149,6 +151,27 @@ typedef struct m3ae_attn_params_t {
 int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream);
 /* dq, dk, dv are fully overwritten. */
 int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream);
+
+/* Attention probabilities only: probs[b,h,i,:] = dropout(exp(scale*q_i.K^T + mask - lse_i)) from the q, k, mask and lse of
+ * an earlier m3ae_attn_fwd call (same dropout seed/stream -> same P').  This is what output_attentions=True returns
+ * (bert_model.py:346, consumed at m3ae_module.py:282-283); computing it on demand keeps the reference's hard-wired
+ * output_attentions=True (m3ae_module.py:276-277) off the hot path. */
+int m3ae_attn_probs(const m3ae_attn_params_t* p, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Element-wise pieces of the heads (M = batch rows; HBM-bound).
+ * y = act(x): Pooler tanh (prediction_heads.py:13,18), vqa_head GELU (m3ae_module.py:123).  dx = dy * act'(x). */
+int m3ae_activation_fwd(const void* x, void* y, int64_t n, int32_t act, int32_t dtype, void* stream);
+int m3ae_activation_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t act, int32_t dtype, void* stream);
+/* VQA loss (objectives.py:201): loss_out[0] = scale_loss * sum_i bce_with_logits(logits_i, targets_i) over n = B*labels
+ * elements (scale_loss = 1/B gives mean * n_labels) and, when dlogits != NULL, dlogits_i = scale_grad * (sigmoid - target). */
+int m3ae_bce_with_logits(const float* logits, const float* targets, float* loss_out, float* dlogits, int64_t n,
+                         float scale_loss, float scale_grad, void* stream);
+/* Decoder fine-tune loss (m3ae_decoder.py:365-368): rows = B*T positions of fp32 logits [M,V]; rows whose target equals
+ * ignore_index (or whose weight is 0) contribute nothing.  loss_out[0] = sum_rows w_row * (logsumexp - logit[target]);
+ * dlogits (optional) = w_row * (softmax - onehot).  The caller passes w_row = 1 / (number of counted rows). */
+int m3ae_cross_entropy(const float* logits, int64_t ld, const int64_t* target, const float* row_weight, float* loss_out,
+                       float* dlogits, int64_t ldd, int64_t M, int32_t V, int64_t ignore_index, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * LayerNorm over the last dimension (fp32 statistics, two-pass variance).

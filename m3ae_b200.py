@@ -12,7 +12,7 @@ if _root not in sys.path:
     sys.path.insert(0, _root)
 _REAL = "mm-vqa-healthcare_b200"
 _pkg = importlib.import_module(_REAL)
-for _sub in ("_lib", "ops", "functional", "bert_cross_layer", "m3ae_module", "decoder", "ddp"):
+for _sub in ("_lib", "ops", "functional", "bert_cross_layer", "encoders", "m3ae_module", "decoder", "decoder_model", "ddp"):
     _m = importlib.import_module(f"{_REAL}.{_sub}")
     sys.modules[f"{__name__}.{_sub}"] = _m
 sys.modules[__name__] = _pkg

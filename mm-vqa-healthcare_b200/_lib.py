@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libm3ae_b200.so")
 
 F32, BF16 = 0, 1
-ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
+ACT_NONE, ACT_GELU, ACT_RELU, ACT_QUICKGELU, ACT_TANH = 0, 1, 2, 3, 4
 MAJOR_K, MAJOR_MN = 0, 1
 GEMM_AUTO, GEMM_TCGEN05, GEMM_SIMT = 0, 1, 2
 ATTN_MMA_SYNC = 3
@@ -69,6 +69,13 @@ SIGNATURES = {
     "m3ae_gemm": (C.c_int, [C.POINTER(GemmProblem), C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "m3ae_attn_fwd": (C.c_int, [C.POINTER(AttnParams), C.c_void_p]),
     "m3ae_attn_bwd": (C.c_int, [C.POINTER(AttnParams), C.c_void_p]),
+    "m3ae_attn_probs": (C.c_int, [C.POINTER(AttnParams), C.c_void_p]),
+    "m3ae_activation_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "m3ae_activation_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "m3ae_bce_with_logits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
+                                       C.c_void_p]),
+    "m3ae_cross_entropy": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                     C.c_int64, C.c_int32, C.c_int64, C.c_void_p]),
     "m3ae_layernorm_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p]),
     "m3ae_layernorm_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -652,6 +652,19 @@ int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   return M3AE_OK;
 }
 
+// Attention probabilities only, from q, k, mask and the log-sum-exp a forward call saved: what output_attentions=True
+// returns (bert_model.py:346).  Run on demand so that the hard-wired output_attentions=True of the reference's fusion
+// loop (m3ae_module.py:276-277) does not force 324 MB of fp32 probabilities per image layer through HBM.
+int attn_probs(const m3ae_attn_params_t* p, cudaStream_t st) {
+  M3AE_CHECK(p != nullptr && p->q && p->k && p->lse && p->probs, M3AE_ERR_INVALID, "attn_probs: q, k, lse and probs are required");
+  M3AE_CHECK(p->B > 0 && p->H > 0 && p->Lq > 0 && p->Lk > 0, M3AE_ERR_INVALID, "attn_probs: empty shape");
+  M3AE_CHECK(p->dh == 64 || p->dh == 96, M3AE_ERR_UNSUPPORTED, "attn_probs: head dim %d unsupported", p->dh);
+  if (p->dtype == M3AE_BF16) launch_probs<bf16>(p, st);
+  else launch_probs<float>(p, st);
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
 int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, true);
   if (rc) return rc;

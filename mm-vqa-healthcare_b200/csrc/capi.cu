@@ -64,6 +64,11 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
 int gemm_simt_launch(const m3ae_gemm_problem_t* probs, int n, int in_dtype, cudaStream_t stream);
 int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
 int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st);
+int attn_probs(const m3ae_attn_params_t* p, cudaStream_t st);
+int activation_fwd(const void*, void*, int64_t, int, int, cudaStream_t);
+int activation_bwd(const void*, const void*, void*, int64_t, int, int, cudaStream_t);
+int bce_with_logits(const float*, const float*, float*, float*, int64_t, float, float, cudaStream_t);
+int cross_entropy(const float*, int64_t, const int64_t*, const float*, float*, float*, int64_t, int64_t, int, int64_t, cudaStream_t);
 int layernorm_fwd(const void*, const float*, const float*, void*, float*, float*, int64_t, int, float, int, cudaStream_t);
 int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, void*, float, uint64_t, uint64_t, const uint32_t*, cudaStream_t);
 int colsum(const void*, float*, int64_t, int, int64_t, int, cudaStream_t);
@@ -132,6 +137,29 @@ int m3ae_set_gemm_cta_pair(int32_t mode) {
 
 int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_fwd(p, g_attn_backend, (cudaStream_t)stream); }
 int m3ae_attn_bwd(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_bwd(p, g_attn_backend, (cudaStream_t)stream); }
+
+int m3ae_attn_probs(const m3ae_attn_params_t* p, void* stream) { ARCH_GATE(); return attn_probs(p, (cudaStream_t)stream); }
+
+int m3ae_activation_fwd(const void* x, void* y, int64_t n, int32_t act, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(x && y, M3AE_ERR_INVALID, "activation_fwd: null pointer");
+  return activation_fwd(x, y, n, act, dtype, (cudaStream_t)stream);
+}
+int m3ae_activation_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t act, int32_t dtype, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(dy && x && dx, M3AE_ERR_INVALID, "activation_bwd: null pointer");
+  return activation_bwd(dy, x, dx, n, act, dtype, (cudaStream_t)stream);
+}
+int m3ae_bce_with_logits(const float* logits, const float* targets, float* loss_out, float* dlogits, int64_t n, float scale_loss, float scale_grad, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(logits && targets && loss_out, M3AE_ERR_INVALID, "bce_with_logits: null pointer");
+  return bce_with_logits(logits, targets, loss_out, dlogits, n, scale_loss, scale_grad, (cudaStream_t)stream);
+}
+int m3ae_cross_entropy(const float* logits, int64_t ld, const int64_t* target, const float* row_weight, float* loss_out, float* dlogits, int64_t ldd, int64_t M, int32_t V, int64_t ignore_index, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(logits && target && row_weight && loss_out, M3AE_ERR_INVALID, "cross_entropy: null pointer");
+  return cross_entropy(logits, ld, target, row_weight, loss_out, dlogits, ldd, M, V, ignore_index, (cudaStream_t)stream);
+}
 
 int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd, int64_t M, int32_t H, float eps, int32_t dtype, void* stream) {
   ARCH_GATE();

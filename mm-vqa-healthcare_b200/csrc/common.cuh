@@ -115,6 +115,36 @@ __device__ __forceinline__ float fast_gelu_both(float x, float& grad) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.f));
 }
 
+// QuickGELU of the CLIP visual tower (reference clip_model.py:36-38): x * sigmoid(1.702 x).
+__device__ __forceinline__ float quick_gelu(float x) { return x / (1.0f + __expf(-1.702f * x)); }
+__device__ __forceinline__ float quick_gelu_grad(float x) {
+  const float s = 1.0f / (1.0f + __expf(-1.702f * x));
+  return s * (1.0f + 1.702f * x * (1.0f - s));
+}
+// bf16 tensor-core epilogue variant: 1 ex2 + 1 rcp (MUFU) + 3 FMA-pipe instructions, gradient shares the sigmoid
+__device__ __forceinline__ float fast_quick_gelu_both(float x, float& grad) {
+  const float s = rcp_approx(1.0f + ex2_approx(x * (-1.702f * 1.4426950408889634f)));
+  const float xs = x * s;
+  grad = fmaf(1.702f * xs, 1.0f - s, s);
+  return xs;
+}
+__device__ __forceinline__ float fast_quick_gelu(float x) {
+  return x * rcp_approx(1.0f + ex2_approx(x * (-1.702f * 1.4426950408889634f)));
+}
+// exact-math activation dispatch (generic epilogue, fp32 parity path, standalone activation kernels)
+__device__ __forceinline__ float act_exact(int act, float x) {
+  return act == M3AE_ACT_GELU ? gelu_erf(x) : act == M3AE_ACT_RELU ? fmaxf(x, 0.0f) : act == M3AE_ACT_QUICKGELU ? quick_gelu(x)
+       : act == M3AE_ACT_TANH ? tanhf(x) : x;
+}
+// derivative with respect to the pre-activation u
+__device__ __forceinline__ float act_exact_grad(int act, float u) {
+  if (act == M3AE_ACT_GELU) return gelu_erf_grad(u);
+  if (act == M3AE_ACT_RELU) return u > 0.0f ? 1.0f : 0.0f;
+  if (act == M3AE_ACT_QUICKGELU) return quick_gelu_grad(u);
+  if (act == M3AE_ACT_TANH) { const float t = tanhf(u); return 1.0f - t * t; }
+  return 1.0f;
+}
+
 // ---------------------------------------------------------------- Philox4x32-7 (counter-based RNG for dropout; 7 rounds pass BigCrush)
 struct Philox {
   uint32_t key0, key1;
@@ -241,22 +271,19 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
       float a = acc[j];
-      if (e.aux_is_grad) a = e.act == M3AE_ACT_GELU ? gelu_erf_grad(a) : e.act == M3AE_ACT_RELU ? (a > 0.0f ? 1.0f : 0.0f) : 1.0f;
+      if (e.aux_is_grad) a = act_exact_grad(e.act, a);
       store_from_f32(e.aux_out, e.out_dtype, (size_t)(row * e.ldo + col + j), a);
     }
   }
-  if (e.act == M3AE_ACT_GELU) {
+  if (e.act != M3AE_ACT_NONE) {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) acc[j] = gelu_erf(acc[j]);
-  } else if (e.act == M3AE_ACT_RELU) {
-#pragma unroll
-    for (int j = 0; j < NV; ++j) acc[j] = fmaxf(acc[j], 0.0f);
+    for (int j = 0; j < NV; ++j) acc[j] = act_exact(e.act, acc[j]);
   }
   if (e.dact != M3AE_ACT_NONE) {
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
       const float u = load_as_f32(e.aux_in, e.aux_in_dtype, (size_t)(row * e.ld_aux_in + col + j));
-      acc[j] *= e.aux_is_grad ? u : (e.dact == M3AE_ACT_GELU) ? gelu_erf_grad(u) : (u > 0.0f ? 1.0f : 0.0f);
+      acc[j] *= e.aux_is_grad ? u : act_exact_grad(e.dact, u);
     }
   }
   if (e.drop_p > 0.0f) {

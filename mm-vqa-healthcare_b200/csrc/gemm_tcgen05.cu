@@ -392,6 +392,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
               w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
               *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
             }
+          } else if (aux_grad && epi.act == M3AE_ACT_QUICKGELU) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float d[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[8 * j + k] = fast_quick_gelu_both(v[8 * j + k], d[k]);
+              uint4 w;
+              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
+              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
+              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+            }
           } else if (aux_grad) {
             const bool relu = epi.act == M3AE_ACT_RELU;
 #pragma unroll
@@ -413,6 +424,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           } else if (epi.act == M3AE_ACT_RELU) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (epi.act == M3AE_ACT_QUICKGELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fast_quick_gelu(v[j]);
+          } else if (epi.act == M3AE_ACT_TANH) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
           }
           float in[32];
           if (q.has_in) {
@@ -436,6 +453,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             } else if (epi.dact == M3AE_ACT_GELU) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] *= fast_gelu_grad(in[j]);
+            } else if (epi.dact != M3AE_ACT_RELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] *= act_exact_grad(epi.dact, in[j]);
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = in[j] > 0.f ? v[j] : 0.f;

@@ -47,7 +47,7 @@ class GradientAllReducer:
         self.buckets = []        # (flat, [params]) — bucketed parameters
         self.groups = []         # [params] — zero-copy groups
         self._slot = {}          # id(param) -> ("b", bucket index) | ("g", group index)
-        self._pending, self._launched, self._works = {}, {}, []
+        self._pending, self._launched, self._works, self._writeback = {}, {}, [], []
         self._learned = not self.zero_copy
         for p in self.params:
             p.register_post_accumulate_grad_hook(self._hook)
@@ -99,7 +99,7 @@ class GradientAllReducer:
 
     # ------------------------------------------------------------------ per step
     def zero_grad(self):
-        self._works = []
+        self._works, self._writeback = [], []
         if not self._learned:
             for p in self.params:
                 p.grad = None
@@ -127,34 +127,43 @@ class GradientAllReducer:
             self._launch(key)
 
     def _flat_of(self, key):
+        """The tensor to all-reduce for an exchange unit, plus a write-back list.  The collective issued for a unit has the
+        SAME size on every rank whatever happened locally (a layer without a gradient on this rank, a gradient layout
+        that differs from the first step): ranks whose collective sequences diverge hang NCCL."""
         kind, i = key
         if kind == "b":
-            return self.buckets[i][0]
-        ps = [p for p in self.groups[i] if p.grad is not None]
-        if not ps:
-            return None  # the layer took no part in this backward
-        st = ps[0].grad.untyped_storage()
-        same = all(p.grad.untyped_storage().data_ptr() == st.data_ptr() for p in ps)
-        if not same or len(ps) != len(self.groups[i]) or sum(p.numel() for p in ps) * 4 != st.nbytes():
-            return [p.grad for p in ps]  # layout changed since the first step: exchange the gradients one by one
-        return torch.empty(0, dtype=torch.float32, device=ps[0].device).set_(st)
+            return self.buckets[i][0], None
+        group = self.groups[i]
+        ps = [p for p in group if p.grad is not None]
+        if len(ps) == len(group):
+            st = ps[0].grad.untyped_storage()
+            same = all(p.grad.untyped_storage().data_ptr() == st.data_ptr() for p in ps)
+            if same and sum(p.numel() for p in ps) * 4 == st.nbytes():
+                return torch.empty(0, dtype=torch.float32, device=ps[0].device).set_(st), None  # the layer's buffer, in place
+        # no gradient here, or a different layout: stage through a flat buffer of the group's size (zeros where absent)
+        flat = torch.zeros(sum(p.numel() for p in group), dtype=torch.float32, device=group[0].device)
+        back, off = [], 0
+        for p in group:
+            view = flat[off:off + p.numel()].view_as(p)
+            if p.grad is not None:
+                view.copy_(p.grad)
+            back.append((p, view))
+            off += p.numel()
+        return flat, back
 
     def _launch(self, key):
         if self.world == 1:
             return
-        flat = self._flat_of(key)
-        if flat is None:
-            return
-        tensors = flat if isinstance(flat, list) else [flat]
+        flat, back = self._flat_of(key)
         if self.cuda:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(self.comm_stream):
-                for t in tensors:  # NCCL averages inside the reduction: no separate pre-scale pass
-                    self._works.append(dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
+            with torch.cuda.stream(self.comm_stream):  # NCCL averages inside the reduction: no separate pre-scale pass
+                self._works.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
         else:
-            for t in tensors:
-                t.mul_(1.0 / self.world)
-                self._works.append(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            flat.mul_(1.0 / self.world)
+            self._works.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        if back is not None:
+            self._writeback.append(back)
 
     def wait(self):
         """Call after backward(): starts every exchange that has not started (first step, overlap=False, parameters
@@ -173,7 +182,21 @@ class GradientAllReducer:
             w.wait()
         if self.cuda and self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
-        self._works = []
+        for back in self._writeback:  # staged groups: hand the averaged values to the parameters
+            for p, view in back:
+                if p.grad is None:
+                    p.grad = view
+                else:
+                    p.grad.copy_(view)
+        self._works, self._writeback = [], []
+
+    def broadcast_parameters(self, src=0):
+        """What PL's DDP does at start-up: every replica takes rank `src`'s parameters (and the caller's buffers stay as
+        they are).  Replicas that were built from the same seed need it only as a safety net."""
+        if self.world > 1:
+            with torch.no_grad():
+                for p in self.params:
+                    dist.broadcast(p.data, src=src, group=self.group)
 
     def payload_bytes(self):
         return sum(p.numel() * 4 for p in self.params)

@@ -56,6 +56,35 @@ class DecoderLayer(nn.Module):
         self.dropout3 = nn.Dropout(dropout)
 
 
+class _LazyMaps(dict):
+    """dict of attention maps whose values are computed on first access (keys are all present from the start)."""
+
+    def defer(self, key, fn):
+        dict.__setitem__(self, key, None)
+        self.__dict__.setdefault("_fns", {})[key] = fn
+
+    def __getitem__(self, key):
+        v = dict.__getitem__(self, key)
+        if v is None and key in self.__dict__.get("_fns", {}):
+            v = self._fns.pop(key)()
+            dict.__setitem__(self, key, v)
+        return v
+
+    def get(self, key, default=None):
+        return self[key] if key in self else default
+
+    def materialize(self):
+        for k in list(self.keys()):
+            self[k]
+        return self
+
+    def values(self):
+        return [self[k] for k in self.keys()]
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+
 class Decoder(nn.Module):
     def __init__(self, num_layers, d_model, num_heads, d_ff, dropout, max_len, target_vocab_size,
                  compute_dtype=torch.bfloat16):
@@ -77,75 +106,107 @@ class Decoder(nn.Module):
         self.graph_replayed_launches = 0
 
     # ------------------------------------------------------------------ teacher-forced forward (fine-tune / val)
-    def _layer(self, layer, e2, mem2, B, T, Lm, pad_mask_add, want_att):
-        """DecoderLayer.forward (m3ae_decoder.py:54-90) on [B*T, D] rows; eval-mode dropout (see forward())."""
+    def _layer(self, layer, e2, mem2, B, T, Lm, pad_mask_add, drop_p, seed):
+        """DecoderLayer.forward (m3ae_decoder.py:54-90) on [B*T, D] rows.  Train mode applies the reference's dropouts
+        (p = `dropout`): on the self- and cross-attention probabilities inside the two nn.MultiheadAttention modules
+        (:42-43), after each sub-block before the residual add (dropout1/2/3, :62,:80,:86) — as GEMM-epilogue /
+        attention-kernel Philox dropout with per-site streams.  Returns the output rows and what the lazy
+        attention-map handles need (q, k of both attentions)."""
         dt = self.compute_dtype
         D, nh = self.d_model, self.num_heads
         dh = D // nh
         xn = Fn.layernorm(e2, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps)
         qkv = Fn.linear(xn, layer.mha1.in_proj_weight, layer.mha1.in_proj_bias, dtype=dt)
-        a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pad_mask_add, B, nh, T, T, dh, causal=True)
-        x = Fn.linear(a, layer.mha1.out_proj.weight, layer.mha1.out_proj.bias, dtype=dt) + e2
+        a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pad_mask_add, B, nh, T, T, dh, causal=True,
+                         drop_p=drop_p, drop_seed=seed, drop_site=1)
+        x = Fn.linear(a, layer.mha1.out_proj.weight, layer.mha1.out_proj.bias, dtype=dt, residual=e2,
+                      drop_p=drop_p, drop_seed=seed, drop_site=2)                      # residual + dropout1(mha1)
         residual = x
         x = Fn.layernorm(x, layer.layernorm1.weight, layer.layernorm1.bias, layer.layernorm1.eps)
         E = D
         w2, b2 = layer.mha2.in_proj_weight, layer.mha2.in_proj_bias
         q2 = Fn.linear(x, w2[:E], b2[:E], dtype=dt)
         kv2 = Fn.linear(mem2, w2[E:], b2[E:], dtype=dt)
-        c = Fn.attention(q2, kv2[:, :D], kv2[:, D:], None, B, nh, T, Lm, dh, causal=False)
-        x = Fn.linear(c, layer.mha2.out_proj.weight, layer.mha2.out_proj.bias, dtype=dt) + residual
+        c = Fn.attention(q2, kv2[:, :D], kv2[:, D:], None, B, nh, T, Lm, dh, causal=False,
+                         drop_p=drop_p, drop_seed=seed, drop_site=3)
+        x = Fn.linear(c, layer.mha2.out_proj.weight, layer.mha2.out_proj.bias, dtype=dt, residual=residual,
+                      drop_p=drop_p, drop_seed=seed, drop_site=4)                      # dropout2(mha2) + residual
         residual = x
         x = Fn.layernorm(x, layer.layernorm2.weight, layer.layernorm2.bias, layer.layernorm2.eps)
         x = Fn.ffn(x, layer.ffn[0].weight, layer.ffn[0].bias, layer.ffn[2].weight, layer.ffn[2].bias, residual=residual,
-                   act=ops.ACT_RELU, dtype=dt)
+                   act=ops.ACT_RELU, dtype=dt, drop_p=drop_p, drop_seed=seed, drop_site=5)  # dropout3(ffn) + residual
         x = Fn.layernorm(x, layer.layernorm3.weight, layer.layernorm3.bias, layer.layernorm3.eps)
-        att = (None, None)
-        if want_att:
-            att = (self._avg_probs(qkv[:, :D], qkv[:, D:2 * D], B, T, T, pad_mask_add, True),
-                   self._avg_probs(q2, kv2[:, :D], B, T, Lm, None, False))
-        return x, att
+        return x, (qkv.detach()[:, :D], qkv.detach()[:, D:2 * D], q2.detach(), kv2.detach()[:, :D])
 
     def _avg_probs(self, q, k, B, Lq, Lk, mask, causal):
-        """Head-averaged attention weights, as nn.MultiheadAttention(need_weights=True) returns (slow path)."""
+        """Head-averaged attention weights, as nn.MultiheadAttention(need_weights=True) returns (on demand only)."""
         nh = self.num_heads
         dh = self.d_model // nh
         with torch.no_grad():
             probs = torch.empty(B, nh, Lq, Lk, dtype=torch.float32, device=q.device)
             out = torch.empty(B * Lq, nh * dh, dtype=q.dtype, device=q.device)
             lse = torch.empty(B, nh, Lq, dtype=torch.float32, device=q.device)
-            ops.attn_fwd(q.detach(), k.detach(), k.detach(), out, lse, B=B, H=nh, Lq=Lq, Lk=Lk, dh=dh, mask=mask,
-                         causal=causal, probs=probs)
+            ops.attn_fwd(q, k, k, out, lse, B=B, H=nh, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal, probs=probs)
             return probs.mean(dim=1)
 
     def forward(self, padded_targets, padding_mask, cross_attn_feats, return_all_attentions=False):
-        """-> (logits [B,T,V], dict of head-averaged attention maps).  Dropout inside the decoder is not applied
-        (p=0.1 in the reference's train mode cannot be bit-matched anyway; parity is asserted in eval mode)."""
+        """-> (logits [B,T,V] fp32, dict of head-averaged attention maps `layer{i}_dec_self` / `layer{i}_dec_cross` for all
+        layers, as the reference returns, m3ae_decoder.py:130-138).  Only dec_layers[-1] reaches the logits (:131-134),
+        so only it runs here; the maps are computed when READ (the reference's callers drop them,
+        m3ae_decoder.py:358): the live layer's from its q/k, the dead layers' by evaluating that layer then.  Maps are
+        the pre-dropout probabilities.  return_all_attentions=True evaluates everything eagerly."""
         if not cross_attn_feats.is_cuda:
             raise RuntimeError("Decoder (B200) needs CUDA tensors: there is no CPU fallback")
         dt = self.compute_dtype
         if torch.is_grad_enabled():
             # a differentiated forward is followed by an optimizer step; fused optimizers do not bump the parameters'
             # version counters, so the greedy path's operand cache cannot be trusted afterwards
-            self._cache = {}
-            self._graphs = {}
+            self.invalidate_cache()
         B, T = padded_targets.shape
         Lm, D = cross_attn_feats.shape[1], self.d_model
         dev = cross_attn_feats.device
         pad_mask_add = None
         if padding_mask is not None:  # key_padding_mask = ~padding_mask -> -inf on padded keys (:121)
             pad_mask_add = torch.zeros(B, T, dtype=torch.float32, device=dev).masked_fill(~padding_mask.to(dev), float("-inf"))
+        drop_p = float(self.dropout.p) if self.training else 0.0
+        seed = Fn.new_seed() if drop_p > 0 else 0
         emb = self.target_embedding(padded_targets)  # [B,T,D] fp32 (autograd through the table)
         e = emb + (emb + self.positional_encoding.pe[:, :T])  # 2*E + pe (:127)
-        e2 = e.reshape(B * T, D).to(dt)
+        e2 = Fn.dropout(e.reshape(B * T, D).to(dt), drop_p, seed, 0)  # :128
         mem2 = cross_attn_feats.reshape(B * Lm, D).to(dt)
-        att = {}
-        x = None
-        layers = range(self.num_layers) if return_all_attentions else [self.num_layers - 1]
-        for i in layers:
-            x, (a_self, a_cross) = self._layer(self.dec_layers[i], e2, mem2, B, T, Lm, pad_mask_add, True)
-            att[f"layer{i + 1}_dec_self"], att[f"layer{i + 1}_dec_cross"] = a_self, a_cross
+        live = self.num_layers - 1
+        x, (q1, k1, q2, k2) = self._layer(self.dec_layers[live], e2, mem2, B, T, Lm, pad_mask_add, drop_p, seed)
         logits = Fn.linear(x, self.final_linear.weight, self.final_linear.bias, dtype=dt, out_dtype=torch.float32)
+
+        att = _LazyMaps()
+        e2d, mem2d = e2.detach(), mem2.detach()
+        for i in range(self.num_layers):
+            if i == live:
+                att.defer(f"layer{i + 1}_dec_self", lambda: self._avg_probs(q1, k1, B, T, T, pad_mask_add, True))
+                att.defer(f"layer{i + 1}_dec_cross", lambda: self._avg_probs(q2, k2, B, T, Lm, None, False))
+            else:
+                def dead(i=i, cache={}):
+                    if not cache:
+                        with torch.no_grad():
+                            _, (a, b, c, d) = self._layer(self.dec_layers[i], e2d, mem2d, B, T, Lm, pad_mask_add, 0.0, 0)
+                            cache["s"] = self._avg_probs(a, b, B, T, T, pad_mask_add, True)
+                            cache["c"] = self._avg_probs(c, d, B, T, Lm, None, False)
+                    return cache
+                att.defer(f"layer{i + 1}_dec_self", lambda dead=dead: dead()["s"])
+                att.defer(f"layer{i + 1}_dec_cross", lambda dead=dead: dead()["c"])
+        if return_all_attentions:
+            att.materialize()
         return logits.view(B, T, -1), att
+
+    def invalidate_cache(self):
+        """Drop the greedy path's bf16 operand copies and captured CUDA graphs.  Called by every differentiated forward;
+        call it yourself after changing parameters in any other way (load_state_dict does it too)."""
+        self._cache = {}
+        self._graphs = {}
+
+    def load_state_dict(self, *a, **k):
+        self.invalidate_cache()
+        return super().load_state_dict(*a, **k)
 
     # ------------------------------------------------------------------ KV-cached greedy decoding
     def _operands(self):
@@ -153,7 +214,13 @@ class Decoder(nn.Module):
         layer = self.dec_layers[self.num_layers - 1]
         ps = [layer.mha1.in_proj_weight, layer.mha1.out_proj.weight, layer.mha2.in_proj_weight, layer.mha2.out_proj.weight,
               layer.ffn[0].weight, layer.ffn[2].weight, self.final_linear.weight]
-        key = (self.compute_dtype,) + tuple((p.data_ptr(), p._version) for p in ps)
+        # (address, version) misses in-place updates by fused optimizers (they do not bump _version): every differentiated
+        # forward, load_state_dict and invalidate_cache() clear the cache, and a cheap content digest of one weight row per
+        # tensor catches an optimizer step that was applied without any of those (search_path right after opt.step()).
+        with torch.no_grad():
+            digest = torch.stack([p.detach().reshape(-1)[:: max(1, p.numel() // 64)][:64].double().sum() for p in ps])
+            digest = tuple(digest.tolist())
+        key = (self.compute_dtype,) + tuple((p.data_ptr(), p._version) for p in ps) + digest
         if self._cache.get("key") != key:
             dt = self.compute_dtype
             with torch.no_grad():
@@ -175,23 +242,24 @@ class Decoder(nn.Module):
         import os
         if use_graph is None:
             use_graph = os.environ.get("M3AE_DECODER_GRAPH", "1") != "0"
+        operands = self._operands()  # outside any capture: checks the masters against the cache (one small D2H read)
         if not use_graph or early_exit_every:
-            return self._greedy_program(cross_attn_feats, tokenizer, early_exit_every)
+            return self._greedy_program(cross_attn_feats, tokenizer, early_exit_every, operands)
         layer = self.dec_layers[self.num_layers - 1]
         live = list(layer.parameters()) + [self.target_embedding.weight, self.final_linear.bias, self.positional_encoding.pe]
         key = (tuple(cross_attn_feats.shape), cross_attn_feats.dtype, cross_attn_feats.device, self.compute_dtype, self.max_len,
                tokenizer.cls_token_id, tokenizer.sep_token_id, tokenizer.eos_token_id, tokenizer.pad_token_id,
-               tuple(w.data_ptr() for w in self._operands()), tuple(p.data_ptr() for p in live))
+               tuple(w.data_ptr() for w in operands), tuple(p.data_ptr() for p in live))
         entry = self._graphs.get(key)
         if entry is None:
             mem_in = torch.empty_like(cross_attn_feats, memory_format=torch.contiguous_format)
             mem_in.copy_(cross_attn_feats)
-            self._greedy_program(mem_in, tokenizer, 0)  # eager warm-up: one-time kernel attribute set-up happens outside capture
+            self._greedy_program(mem_in, tokenizer, 0, operands)  # eager warm-up: one-time kernel attribute set-up happens outside capture
             torch.cuda.synchronize(cross_attn_feats.device)
             graph = torch.cuda.CUDAGraph()
             n0 = ops.launch_count()
             with torch.cuda.graph(graph):
-                out = self._greedy_program(mem_in, tokenizer, 0)
+                out = self._greedy_program(mem_in, tokenizer, 0, operands)
             n_kernels = ops.launch_count() - n0  # C-ABI kernels recorded in the graph = launched by every replay
             if len(self._graphs) >= 2:  # each graph pins its buffers (cross K/V cache: B*Lm*1536*2 B); keep the two latest
                 self._graphs.pop(next(iter(self._graphs)))
@@ -202,7 +270,7 @@ class Decoder(nn.Module):
         self.graph_replayed_launches += n_kernels  # ops.launch_count() only sees capture-time calls
         return out.clone()
 
-    def _greedy_program(self, cross_attn_feats, tokenizer, early_exit_every=0):
+    def _greedy_program(self, cross_attn_feats, tokenizer, early_exit_every=0, operands=None):
         """The greedy decoding program itself (see search_path); max_len single-token steps.  Since the reference blanks
         everything after the first [SEP] and only breaks once ALL rows are finished, running the remaining steps cannot
         change the output (early_exit_every=n adds the reference's all-finished check, one host sync, every n steps)."""
@@ -212,7 +280,7 @@ class Decoder(nn.Module):
         nh, L = self.num_heads, self.max_len
         dh = D // nh
         layer = self.dec_layers[self.num_layers - 1]
-        w_in1, w_out1, w_in2, w_out2, w_f0, w_f2, w_vocab = self._operands()
+        w_in1, w_out1, w_in2, w_out2, w_f0, w_f2, w_vocab = operands if operands is not None else self._operands()
         b_in1, b_in2 = layer.mha1.in_proj_bias.detach(), layer.mha2.in_proj_bias.detach()
         V = w_vocab.shape[0]
         sep, pad, eos = tokenizer.sep_token_id, tokenizer.pad_token_id, tokenizer.eos_token_id

@@ -1,0 +1,155 @@
+"""Uni-modal encoders of M3AE on the sm_100a kernels.
+
+`ClipVisionEncoder`  the reference's `vision_encoder` = CLIP whose forward is `visual(image)`
+                     (m3ae/modules/vision_encoders/clip_model.py:79-128,186-187): 16x16 patch-embed conv as ONE GEMM,
+                     class token + positional embedding, ln_pre, 11 pre-LN ResidualAttentionBlocks (packed in-proj MHA,
+                     QuickGELU MLP, clip_model.py:41-63,71), ln_post.  Parameter names = the reference's
+                     (`visual.conv1.weight`, `visual.transformer.resblocks.{i}.attn.in_proj_weight`, ...), so reference
+                     checkpoints load.  LayerNorm statistics are fp32 (the reference's LayerNorm subclass casts to fp32,
+                     clip_model.py:27-33); the residual stream is kept in the compute dtype.
+`roberta_layer`      one HF `RobertaLayer` (post-LN BERT layer; called one by one with the additive mask at
+                     m3ae_module.py:230-234) driven from the HF module's own Parameters: fused QKV GEMM, flash
+                     attention with the key-padding mask, out-proj + dropout + residual epilogue, LayerNorm, GELU FFN.
+
+Both are built from the composable autograd nodes in `functional` (linear / layernorm / attention / ffn): every matmul,
+attention, LayerNorm and activation on these paths is a kernel of libm3ae_b200.so; torch is used for the reshapes that
+build the patch matrix and for the embedding gathers.
+"""
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from . import ops
+
+
+# ----------------------------------------------------------------------------- CLIP ViT-B/16 visual tower
+class _ResBlock(nn.Module):
+    """Parameter container of clip_model.ResidualAttentionBlock (:41-52); math in ClipVisionEncoder.forward."""
+
+    def __init__(self, d_model, n_head):
+        super().__init__()
+        self.attn = nn.MultiheadAttention(d_model, n_head)
+        self.ln_1 = nn.LayerNorm(d_model)
+        self.mlp = nn.Sequential(OrderedDict([("c_fc", nn.Linear(d_model, d_model * 4)), ("gelu", nn.Identity()),
+                                              ("c_proj", nn.Linear(d_model * 4, d_model))]))
+        self.ln_2 = nn.LayerNorm(d_model)
+        self.n_head = n_head
+
+
+class _Transformer(nn.Module):
+    def __init__(self, width, layers, heads):
+        super().__init__()
+        self.width, self.layers = width, layers
+        self.resblocks = nn.Sequential(*[_ResBlock(width, heads) for _ in range(layers - 1)])  # clip_model.py:71: layers-1
+
+
+class _VisualTransformer(nn.Module):
+    """Parameter container of clip_model.VisualTransformer (:79-93)."""
+
+    def __init__(self, patch_size, width, layers, heads, resolution_after):
+        super().__init__()
+        self.patch_size = patch_size
+        self.conv1 = nn.Conv2d(3, width, kernel_size=patch_size, stride=patch_size, bias=False)
+        scale = width ** -0.5
+        self.class_embedding = nn.Parameter(scale * torch.randn(width))
+        self.positional_embedding = nn.Parameter(scale * torch.randn((resolution_after // patch_size) ** 2 + 1, width))
+        self.ln_pre = nn.LayerNorm(width)
+        self.transformer = _Transformer(width, layers, heads)
+        self.ln_post = nn.LayerNorm(width)
+
+
+class ClipVisionEncoder(nn.Module):
+    def __init__(self, resolution_after, patch_size=16, width=768, layers=12, heads=12, compute_dtype=torch.bfloat16):
+        super().__init__()
+        if width != 768 or width // heads != 64:
+            raise NotImplementedError("the sm_100a kernels are instantiated for ViT-B (width 768, 12 heads x 64)")
+        self.visual = _VisualTransformer(patch_size, width, layers, heads, resolution_after)
+        self.compute_dtype = compute_dtype
+        proj_std = (width ** -0.5) * ((2 * layers) ** -0.5)
+        for b in self.visual.transformer.resblocks:  # CLIP.initialize_parameters, clip_model.py:172-180
+            nn.init.normal_(b.attn.in_proj_weight, std=width ** -0.5)
+            nn.init.normal_(b.attn.out_proj.weight, std=proj_std)
+            nn.init.normal_(b.mlp.c_fc.weight, std=(2 * width) ** -0.5)
+            nn.init.normal_(b.mlp.c_proj.weight, std=proj_std)
+
+    def forward_patch_embed(self, image):
+        """clip_model.py:96-101 (= forward_patch_embed :114-120): conv1 as a GEMM over the 16x16x3 patch matrix, then the
+        class token.  -> [B, L, width] in the compute dtype."""
+        v = self.visual
+        p = v.patch_size
+        B, C, Hh, Ww = image.shape
+        gh, gw = Hh // p, Ww // p
+        # K index = c*p*p + py*p + px: the layout of conv1.weight.view(width, C*p*p)
+        patches = image.reshape(B, C, gh, p, gw, p).permute(0, 2, 4, 1, 3, 5).reshape(B * gh * gw, C * p * p)
+        w = v.conv1.weight.view(v.conv1.weight.shape[0], -1)
+        x = Fn.linear(patches, w, None, dtype=self.compute_dtype).view(B, gh * gw, -1)
+        cls = v.class_embedding.to(x.dtype).expand(B, 1, -1)
+        return torch.cat([cls, x], dim=1)
+
+    def forward_trans(self, x):
+        """clip_model.py:104-110 (= forward_trans :126-132): ln_pre, 11 residual attention blocks, ln_post."""
+        v = self.visual
+        dt = self.compute_dtype
+        B, L, D = x.shape
+        x2 = x.reshape(B * L, D)
+        if x2.dtype != dt:
+            x2 = x2.to(dt)
+        x2 = Fn.layernorm(x2, v.ln_pre.weight, v.ln_pre.bias, v.ln_pre.eps)
+        for blk in v.transformer.resblocks:
+            nh = blk.n_head
+            h = Fn.layernorm(x2, blk.ln_1.weight, blk.ln_1.bias, blk.ln_1.eps)
+            qkv = Fn.linear(h, blk.attn.in_proj_weight, blk.attn.in_proj_bias, dtype=dt)
+            a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], None, B, nh, L, L, D // nh)
+            x2 = Fn.linear(a, blk.attn.out_proj.weight, blk.attn.out_proj.bias, dtype=dt, residual=x2)   # x + attn(ln_1(x))
+            h = Fn.layernorm(x2, blk.ln_2.weight, blk.ln_2.bias, blk.ln_2.eps)
+            x2 = Fn.ffn(h, blk.mlp.c_fc.weight, blk.mlp.c_fc.bias, blk.mlp.c_proj.weight, blk.mlp.c_proj.bias, residual=x2,
+                        act=ops.ACT_QUICKGELU, dtype=dt)                                                  # x + mlp(ln_2(x))
+        x2 = Fn.layernorm(x2, v.ln_post.weight, v.ln_post.bias, v.ln_post.eps)
+        return x2.view(B, L, D)
+
+    def forward(self, image, image_mask=None):
+        if image_mask is not None:
+            raise NotImplementedError("key-padding masks on image tokens are not used on the M3AE path (m3ae_module.py:251)")
+        if not image.is_cuda:
+            raise RuntimeError("ClipVisionEncoder (B200) needs CUDA tensors: there is no CPU fallback")
+        x = self.forward_patch_embed(image)
+        x = x + self.visual.positional_embedding.to(x.dtype)  # clip_model.py:102
+        return self.forward_trans(x)
+
+
+# ----------------------------------------------------------------------------- RoBERTa-base encoder layers
+def roberta_layer(layer, h, mask_add, B, L, compute_dtype, training):
+    """One HF RobertaLayer on rows h [B*L, 768]: self-attention (RobertaSelfAttention + RobertaSelfOutput) and FFN
+    (RobertaIntermediate + RobertaOutput), post-LN, erf GELU — the arithmetic of BertCrossLayer's self-attention and FFN
+    blocks (bert_model.py:253-364,416-442) with this layer's own parameters.  mask_add: additive key mask [B, L] fp32."""
+    att, so = layer.attention.self, layer.attention.output
+    nh = att.num_attention_heads
+    D = h.shape[-1]
+    pa = float(att.dropout.p) if training else 0.0
+    ph = float(so.dropout.p) if training else 0.0
+    seed = Fn.new_seed() if training and (pa > 0 or ph > 0) else 0
+    wqkv = torch.cat([att.query.weight, att.key.weight, att.value.weight], dim=0)
+    bqkv = torch.cat([att.query.bias, att.key.bias, att.value.bias], dim=0)
+    qkv = Fn.linear(h, wqkv, bqkv, dtype=compute_dtype)
+    c = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], mask_add, B, nh, L, L, D // nh, drop_p=pa, drop_seed=seed,
+                     drop_site=0)
+    h1 = Fn.linear(c, so.dense.weight, so.dense.bias, dtype=compute_dtype, residual=h, drop_p=ph, drop_seed=seed, drop_site=1)
+    a = Fn.layernorm(h1, so.LayerNorm.weight, so.LayerNorm.bias, so.LayerNorm.eps)
+    out = layer.output
+    o = Fn.ffn(a, layer.intermediate.dense.weight, layer.intermediate.dense.bias, out.dense.weight, out.dense.bias, residual=a,
+               act=ops.ACT_GELU, dtype=compute_dtype, drop_p=ph, drop_seed=seed, drop_site=2)
+    return Fn.layernorm(o, out.LayerNorm.weight, out.LayerNorm.bias, out.LayerNorm.eps)
+
+
+def text_encoder_forward(language_encoder, text_ids, text_masks, compute_dtype, training):
+    """m3ae_module.py:230-234: embeddings (HF module: gathers + LayerNorm + dropout), the HF-4.6.0 extended mask, then the
+    encoder layers one by one.  -> [B, L, 768] in the compute dtype."""
+    emb = language_encoder.embeddings(input_ids=text_ids)
+    B, L, D = emb.shape
+    mask_add = ((1.0 - text_masks.to(torch.float32)) * -10000.0).contiguous()
+    h = emb.reshape(B * L, D).to(compute_dtype)
+    for layer in language_encoder.encoder.layer:
+        h = roberta_layer(layer, h, mask_add, B, L, compute_dtype, training)
+    return h.view(B, L, D)

@@ -14,7 +14,7 @@ Kernel schedule per stream (forward):            saved for backward
   qc   = a1·Wq2^T + b ; kvc = y·Wkv2^T + b        qc, kvc
   ctx2 = flash_attn(qc, kvc, cross mask)          ctx2, lse2
   h2   = drop(ctx2·Wo2^T + b) + a1 ; a2 = LN(h2)  h2, mean2, rstd2, a2
-  u    = a2·W1^T + b ; g = gelu(u)     [M,3072]   u, g   (one GEMM, two outputs)
+  u    = a2·W1^T + b ; g = gelu(u)     [M,3072]   gelu'(u) (stored in the `u` buffer), g   (one GEMM, two outputs)
   h3   = drop(g·W2^T + b) + a2 ; out = LN(h3)     h3, mean3, rstd3
 Backward runs the mirror image: LN-bwd (+bias-grad column sums) -> dgrad GEMMs (B operand MN-major, residual and
 GELU' fused in the epilogue) and wgrad GEMMs (both operands MN-major, split-K atomics into fp32) grouped per stage.
@@ -173,6 +173,65 @@ def _ptr(t):
     return t.data_ptr() if t is not None else None
 
 
+class LazyAttentionProbs:
+    """Attention probabilities [B,nh,Lq,Lk] (fp32) of one attention block, computed on first use.
+
+    The reference's fusion loop asks every layer for its probabilities (output_attentions=True is hard-wired at
+    m3ae_module.py:276-277) and then drops them unless the caller of infer() wanted them (:282-283).  Materialising them
+    eagerly costs two extra kernels and a [B,12,Lq,Lk] fp32 tensor per block (324 MB per image layer at batch 64), so
+    the layer returns this handle instead: it remembers the workspace that still holds q, k, the log-sum-exp and the
+    dropout seed, and runs m3ae_attn_probs when something reads it (any torch function, attribute or index).  The
+    workspace belongs to the layer and is re-used by the layer's NEXT forward; reading the handle after that raises."""
+
+    def __init__(self, ws, which, gen):
+        self._ws, self._which, self._gen = ws, which, gen
+        self._value = None
+
+    def materialize(self):
+        if self._value is None:
+            st = self._ws
+            if st.gen != self._gen:
+                raise RuntimeError("attention probabilities were requested after the layer ran again: read (or .materialize()) "
+                                   "them before the next forward of the same layer")
+            nh = st.nh
+            H = st.H
+            if self._which == 0:
+                q, k, lse, Lk, mask, site = st.qkv[:, :H], st.qkv[:, H:2 * H], st.lse1, st.Lq, st.mask, 0
+            else:
+                q, k, lse, Lk, mask, site = st.qc, st.kvc[:, :H], st.lse2, st.Lk, st.enc_mask, 2
+            probs = torch.empty(st.B, nh, st.Lq, Lk, dtype=torch.float32, device=st.dev)
+            with torch.no_grad():
+                ops.attn_probs(q, k, lse, probs, B=st.B, H=nh, Lq=st.Lq, Lk=Lk, dh=st.dh, mask=mask, drop_p=st.pa,
+                               drop_seed=st.seed, drop_stream=site)
+            self._value = probs
+            self._ws = None
+        return self._value
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        def conv(a):
+            if isinstance(a, LazyAttentionProbs):
+                return a.materialize()
+            if isinstance(a, (list, tuple)):
+                return type(a)(conv(x) for x in a)
+            return a
+        return func(*conv(args), **{k: conv(v) for k, v in (kwargs or {}).items()})
+
+    def __getattr__(self, name):  # only reached for names this class does not define: delegate to the tensor
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self.materialize(), name)
+
+    def __getitem__(self, idx):
+        return self.materialize()[idx]
+
+    def __len__(self):
+        return len(self.materialize())
+
+    def __repr__(self):
+        return f"LazyAttentionProbs(materialized={self._value is not None})"
+
+
 class _Gemm:
     """A cached grouped-GEMM launch: the ctypes problem array is built once; `patch` lists (problem index, field path,
     getter) for operands whose address is not owned by the workspace (layer inputs, incoming gradients)."""
@@ -199,7 +258,7 @@ class _Attn:
         ops.L.check(self.fn(self.ref, stream), "m3ae_attn")
 
 
-def _forward_streams(cfg, training, streams, want_probs, will_train=True):
+def _forward_streams(cfg, training, streams, will_train=True):
     """streams: list of dicts(hidden, encoder, mask, enc_mask, params(list of 26), operands(LayerOperands))."""
     dt = cfg.compute_dtype
     be = cfg.gemm_backend
@@ -214,11 +273,13 @@ def _forward_streams(cfg, training, streams, want_probs, will_train=True):
         Lk = e.shape[1]
         params = s["params"]
         dev = h.device
-        key = (B, Lq, Lk, H, dt, dev, pa, ph, bool(want_probs), s["mask"] is None, s["enc_mask"] is None,
+        key = (B, Lq, Lk, H, dt, dev, pa, ph, s["mask"] is None, s["enc_mask"] is None,
                tuple(p.data_ptr() for p in params))
         w = s["operands"].get(params, dt, will_train)
         st = s["operands"].acquire(key)
         st.B, st.Lq, st.H, st.Lk = B, Lq, H, Lk
+        st.gen = getattr(st, "gen", 0) + 1  # LazyAttentionProbs handles of earlier forwards become invalid
+        st.nh = nh
         st.dh = H // nh
         st.M, st.Mk = B * Lq, B * Lk
         st.dev = dev
@@ -244,7 +305,7 @@ def _forward_streams(cfg, training, streams, want_probs, will_train=True):
             st.qkv = st.buf("qkv", (M, 3 * H), dt, dev)
             st.ctx = st.buf("ctx", (M, H), dt, dev)
             st.lse1 = st.buf("lse1", (st.B, nh, st.Lq), f32, dev)
-            st.probs1 = st.probs2 = st.dm1 = st.dm2 = None
+            st.dm1 = st.dm2 = None
             if pa > 0.0 and dt == torch.bfloat16:  # dropout keep-bit caches: written by forward, read by backward
                 st.dm1 = st.buf("dm1", (st.B * nh * st.Lq * ops.drop_mask_ld(st.Lq),), torch.uint8, dev)
                 st.dm2 = st.buf("dm2", (st.B * nh * st.Lq * ops.drop_mask_ld(st.Lk),), torch.uint8, dev)
@@ -302,10 +363,6 @@ def _forward_streams(cfg, training, streams, want_probs, will_train=True):
         a1, a2 = st.launch["att1"].p, st.launch["att2"].p
         a1.mask, a2.mask = _ptr(st.mask), _ptr(st.enc_mask)
         a1.drop_seed = a2.drop_seed = st.seed
-        if want_probs:  # slow path: probabilities are returned to the caller, so they are fresh tensors
-            st.probs1 = torch.empty(st.B, nh, st.Lq, st.Lq, dtype=torch.float32, device=st.dev)
-            st.probs2 = torch.empty(st.B, nh, st.Lq, st.Lk, dtype=torch.float32, device=st.dev)
-        a1.probs, a2.probs = _ptr(st.probs1), _ptr(st.probs2)
 
     L_["qkv"].run(be, stream)                                  # 1. fused QKV projection
     for st in S:
@@ -473,47 +530,44 @@ def _backward_streams(cfg, S, douts):
 
 
 class _CrossLayersFn(torch.autograd.Function):
-    """inputs: cfg, training, want_probs, operands(list), n_streams, then per stream: hidden, encoder, mask, enc_mask,
-    26 params.  outputs: per stream out [B,Lq,H] (+ self_probs, cross_probs when want_probs)."""
+    """inputs: cfg, training, holder (list that receives the forward workspaces, or None), operands(list), n_streams,
+    needs_bwd, then per stream: hidden, encoder, mask, enc_mask, 26 params.  outputs: per stream out [B,Lq,H]."""
 
     @staticmethod
-    def forward(ctx, cfg, training, want_probs, operands, n_streams, *flat):
+    def forward(ctx, cfg, training, holder, operands, n_streams, needs_bwd, *flat):
         per = 4 + NP
         streams = []
         for i in range(n_streams):
             c = flat[i * per:(i + 1) * per]
             streams.append(dict(hidden=c[0], encoder=c[1], mask=c[2], enc_mask=c[3], params=list(c[4:]), operands=operands[i]))
-        needs_bwd = any(ctx.needs_input_grad)  # grad mode is off inside forward(); this reflects the caller's mode
-        S = _forward_streams(cfg, training, streams, want_probs, will_train=needs_bwd)
+        # needs_bwd comes from the caller (cross_layers_apply): ctx.needs_input_grad is True for every parameter with
+        # requires_grad even under torch.no_grad(), so it cannot tell an eval forward from a training one
+        S = _forward_streams(cfg, training, streams, will_train=needs_bwd)
         ctx.cfg = cfg
-        ctx.S = S
+        ctx.S = S if needs_bwd else None
         ctx.in_dtypes = [(s["hidden"].dtype, s["encoder"].dtype) for s in streams]
         outs = []
-        nondiff = []
         for st, s in zip(S, streams):
             o = st.out.view(st.B, st.Lq, st.H)
             if o.dtype != s["hidden"].dtype:
                 o = ops.cast(st.out, torch.empty(st.B, st.Lq, st.H, dtype=s["hidden"].dtype, device=o.device))
             outs.append(o)
-            if want_probs:
-                outs += [st.probs1, st.probs2]
-                nondiff += [st.probs1, st.probs2]
             st.out = None
             if not needs_bwd:
                 st.busy = False  # no backward will come: the workspace is free again
-        if nondiff:
-            ctx.mark_non_differentiable(*nondiff)
-        ctx.want_probs = want_probs
+        if holder is not None:
+            holder.extend(S)
         return tuple(outs)
 
     @staticmethod
     def backward(ctx, *grads):
         cfg, S = ctx.cfg, ctx.S
+        if S is None:
+            raise RuntimeError("BertCrossLayer (B200): backward through a forward that ran without gradient tracking")
         dt = cfg.compute_dtype
-        step = 3 if ctx.want_probs else 1
         douts = []
         for i, st in enumerate(S):
-            g = grads[i * step]
+            g = grads[i]
             if g is None:
                 g = torch.zeros(st.M, st.H, dtype=dt, device=st.dev)
             g = g.reshape(st.M, st.H)
@@ -521,7 +575,7 @@ class _CrossLayersFn(torch.autograd.Function):
                 g = ops.cast(g.contiguous(), torch.empty(st.M, st.H, dtype=dt, device=g.device))
             douts.append(g)
         res = _backward_streams(cfg, S, douts)
-        flat = [None, None, None, None, None]
+        flat = [None, None, None, None, None, None]
         for (dx, dy, pg), st, (hd, ed) in zip(res, S, ctx.in_dtypes):
             dx = dx.view(st.B, st.Lq, st.H)
             dy = dy.view(st.B, st.Lk, st.H)
@@ -536,7 +590,8 @@ class _CrossLayersFn(torch.autograd.Function):
 
 def cross_layers_apply(cfg, training, streams, want_probs=False):
     """streams: list (1 or 2) of dicts(hidden, encoder, mask, enc_mask, params, operands).
-    Returns per stream a tuple (out,) or (out, self_probs, cross_probs)."""
+    Returns per stream a tuple (out,) or (out, self_probs, cross_probs) — the probabilities as LazyAttentionProbs handles
+    (non-differentiable, computed when read)."""
     if not 1 <= len(streams) <= 2:
         raise ValueError("cross_layers_apply takes one layer or one text/image layer pair")
     flat = []
@@ -544,85 +599,127 @@ def cross_layers_apply(cfg, training, streams, want_probs=False):
         if not s["hidden"].is_cuda:
             raise RuntimeError("BertCrossLayer (B200) needs CUDA tensors: the fusion path has no CPU fallback")
         flat += [s["hidden"], s["encoder"], s["mask"], s["enc_mask"]] + list(s["params"])
-    outs = _CrossLayersFn.apply(cfg, training, want_probs, [s["operands"] for s in streams], len(streams), *flat)
-    step = 3 if want_probs else 1
-    return [tuple(outs[i * step:(i + 1) * step]) for i in range(len(streams))]
+    needs_bwd = torch.is_grad_enabled() and any(torch.is_tensor(t) and t.requires_grad for t in flat)
+    holder = [] if want_probs else None
+    outs = _CrossLayersFn.apply(cfg, training, holder, [s["operands"] for s in streams], len(streams), needs_bwd, *flat)
+    if not want_probs:
+        return [(o,) for o in outs]
+    return [(o, LazyAttentionProbs(st, 0, st.gen), LazyAttentionProbs(st, 1, st.gen)) for o, st in zip(outs, holder)]
 
 
-# ----------------------------------------------------------------------------- generic Linear on the C-ABI GEMM
+# ----------------------------------------------------------------------------- composable autograd pieces
+# The uni-modal encoders (CLIP ViT-B/16, RoBERTa-base), the generative decoder head and the small heads (poolers,
+# vqa_head, losses) are built from these: each is one autograd node over the C-ABI kernels.  Epilogue order of every GEMM
+# = the reference modules': (+bias) -> act -> dropout -> (+residual).
+def new_seed():
+    """A fresh 64-bit dropout seed (Philox key) derived from torch's seed: deterministic under torch.manual_seed."""
+    return (torch.initial_seed() + 0x9E3779B97F4A7C15 * next(_seed_counter)) & 0xFFFFFFFFFFFFFFFF
+
+
+def _as_compute(t, dtype, shape=None):
+    """2-D contiguous view of `t` in the compute dtype (cast kernel when needed)."""
+    t2 = t if shape is None else t.reshape(shape)
+    if t2.dtype == dtype and t2.is_contiguous():
+        return t2
+    return ops.cast(t2.contiguous(), torch.empty(t2.shape, dtype=dtype, device=t2.device))
+
+
 class _LinearFn(torch.autograd.Function):
-    """y = act(x W^T + b (+ extra_bias)) with W fp32 master [N,K]; compute in `dtype` (bf16 tcgen05 / fp32 SIMT).
-    Replaces nn.Linear at m3ae_module.py:235,252 (modality projections; extra_bias = modality type embedding row,
-    :260-263) and the decoder projections (m3ae_decoder.py:85,136)."""
+    """y = drop(act(x W^T + b (+ extra_bias))) (+ residual) with W fp32 master [N,K]; compute in `dtype` (bf16 tcgen05 /
+    fp32 SIMT).  Replaces nn.Linear at m3ae_module.py:235,252 (modality projections; extra_bias = modality type embedding
+    row, :260-263), the decoder / CLIP / RoBERTa projections with their residual adds and hidden dropouts
+    (m3ae_decoder.py:62,80,136; clip_model.py:58-62; HF RobertaSelfOutput / RobertaOutput)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, extra_bias, act, dtype, out_dtype):
+    def forward(ctx, x, weight, bias, extra_bias, residual, act, dtype, out_dtype, drop_p, drop_seed, drop_site):
         K = x.shape[-1]
         N = weight.shape[0]
-        x2 = x.reshape(-1, K)
-        M = x2.shape[0]
+        M = x.numel() // K
         dev = x.device
-        xc = x2 if (x2.dtype == dtype and x2.is_contiguous()) else ops.cast(x2.contiguous(), torch.empty(M, K, dtype=dtype, device=dev))
-        wc = weight.detach() if weight.dtype == dtype else ops.cast(weight.detach(), torch.empty(N, K, dtype=dtype, device=dev))
+        xc = _as_compute(x, dtype, (M, K))
+        wc = _as_compute(weight.detach(), dtype)
         b = None
         if bias is not None:
-            b = bias.detach().float()
+            b = bias.detach().float().contiguous()
             if extra_bias is not None:
-                b = ops.add_rowvec(b.view(1, N).contiguous(), extra_bias.detach().float().contiguous(), torch.empty(1, N, dtype=torch.float32, device=dev)).view(N)
+                b = ops.add_rowvec(b.view(1, N), extra_bias.detach().float().contiguous(), torch.empty(1, N, dtype=torch.float32, device=dev)).view(N)
         elif extra_bias is not None:
             b = extra_bias.detach().float().contiguous()
+        rc = None
+        if residual is not None:
+            rc = residual.reshape(M, N)
+            if rc.dtype != out_dtype or not rc.is_contiguous():
+                rc = ops.cast(rc.contiguous(), torch.empty(M, N, dtype=out_dtype, device=dev))
         out = torch.empty(M, N, dtype=out_dtype, device=dev)
-        u = torch.empty(M, N, dtype=out_dtype, device=dev) if act != ops.ACT_NONE else None
-        ops.gemm(xc, wc, out, bias=b, act=act, aux_out=u)
-        ctx.save_for_backward(xc, wc, u)
-        ctx.meta = (x.shape, x.dtype, act, dtype, bias is not None, extra_bias is not None, weight.dtype)
+        ops.gemm(xc, wc, out, bias=b, act=act, residual=rc, drop_p=drop_p, drop_seed=drop_seed, drop_stream=drop_site)
+        ctx.act = act
+        ctx.save_for_backward(xc, wc)
+        ctx.meta = (x.shape, x.dtype, dtype, bias is not None, extra_bias is not None, weight.dtype, residual is not None,
+                    None if residual is None else (residual.shape, residual.dtype), drop_p, drop_seed, drop_site, out_dtype)
         return out.view(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
-        xc, wc, u = ctx.saved_tensors
-        xshape, xdtype, act, dtype, has_b, has_e, wdtype = ctx.meta
+        if ctx.act != ops.ACT_NONE:
+            raise NotImplementedError("backward through a fused activation is provided by functional.ffn / activation()")
+        xc, wc = ctx.saved_tensors
+        xshape, xdtype, dtype, has_b, has_e, wdtype, has_res, res_meta, drop_p, drop_seed, drop_site, out_dtype = ctx.meta
         M, K = xc.shape
         N = wc.shape[0]
         dev = dy.device
         d2 = dy.reshape(M, N)
+        if drop_p > 0.0:  # gradient pushed back through the epilogue dropout (same Philox stream, element = row*N + col)
+            d2c = d2.contiguous()
+            d2 = ops.dropout_apply(d2c, torch.empty_like(d2c), drop_p, drop_seed, drop_site)
         if dtype == torch.bfloat16 and N % 8 != 0:
             # TMA needs 16-byte row pitches: stage dY in a buffer whose leading dimension is padded (vocab 30522 -> 30528)
             pad = torch.zeros(M, (N + 7) // 8 * 8, dtype=dtype, device=dev)
             pad[:, :N].copy_(d2)
             dyc = pad[:, :N]
         else:
-            dyc = d2 if (d2.dtype == dtype and d2.is_contiguous()) else ops.cast(d2.contiguous(), torch.empty(M, N, dtype=dtype, device=dev))
-        if act != ops.ACT_NONE:
-            # dy * act'(u): run through the dropout-free identity GEMM-less path: reuse dgrad epilogue on a unit problem is
-            # wasteful; activations only appear on tiny decoder FFN rows here, so apply via the GEMM epilogue of dgrad below.
-            raise NotImplementedError("backward through a fused activation is provided by the cross-layer node only")
-        dx = torch.empty(M, K, dtype=xdtype if xdtype in (torch.float32, torch.bfloat16) else dtype, device=dev)
-        dxc = dx if dx.dtype == dtype else torch.empty(M, K, dtype=dtype, device=dev)
-        dw = torch.zeros(N, K, dtype=torch.float32, device=dev)
-        ops.gemm_group([ops.GemmSpec(dyc, wc, dxc, b_major=ops.MAJOR_MN),
-                        ops.GemmSpec(dyc, xc, dw, a_major=ops.MAJOR_MN, b_major=ops.MAJOR_MN, accumulate=True,
-                                     split_k=_wgrad_split(M, N, K))])
-        if dxc is not dx:
-            ops.cast(dxc, dx)
+            dyc = _as_compute(d2, dtype)
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        dx = dw = None
+        specs = []
+        if need_x:
+            dxc = torch.empty(M, K, dtype=dtype, device=dev)
+            specs.append(ops.GemmSpec(dyc, wc, dxc, b_major=ops.MAJOR_MN))
+        if need_w:
+            dw = torch.zeros(N, K, dtype=torch.float32, device=dev)
+            specs.append(ops.GemmSpec(dyc, xc, dw, a_major=ops.MAJOR_MN, b_major=ops.MAJOR_MN, accumulate=True,
+                                      split_k=_wgrad_split(M, N, K)))
+        if specs:
+            ops.gemm_group(specs)
+        if need_x:
+            dx = dxc if dxc.dtype == xdtype or xdtype not in (torch.float32, torch.bfloat16) else ops.cast(dxc, torch.empty(M, K, dtype=xdtype, device=dev))
+            dx = dx.view(xshape)
         db = ops.colsum(dyc, torch.zeros(N, dtype=torch.float32, device=dev)) if (has_b or has_e) else None
-        return dx.view(xshape), dw.to(wdtype), (db if has_b else None), (db if has_e else None), None, None, None
+        dres = None
+        if has_res:
+            rshape, rdtype = res_meta
+            dres = dy.reshape(rshape)
+            if dres.dtype != rdtype:
+                dres = dres.to(rdtype)
+        return (dx, None if dw is None else dw.to(wdtype), (db if has_b else None), (db if has_e else None), dres,
+                None, None, None, None, None, None)
 
 
-def linear(x, weight, bias=None, extra_bias=None, act=ops.ACT_NONE, dtype=torch.bfloat16, out_dtype=None):
+def linear(x, weight, bias=None, extra_bias=None, act=ops.ACT_NONE, dtype=torch.bfloat16, out_dtype=None, residual=None,
+           drop_p=0.0, drop_seed=0, drop_site=0):
     if not x.is_cuda:
         raise RuntimeError("m3ae_b200.functional.linear needs CUDA tensors: there is no CPU fallback")
-    return _LinearFn.apply(x, weight, bias, extra_bias, act, dtype, out_dtype or dtype)
+    return _LinearFn.apply(x, weight, bias, extra_bias, residual, act, dtype, out_dtype or dtype, float(drop_p), int(drop_seed),
+                           int(drop_site))
 
 
-# ----------------------------------------------------------------------------- composable autograd pieces (decoder head)
 class _LayerNormFn(torch.autograd.Function):
-    """nn.LayerNorm (m3ae_decoder.py:46-49) on the C-ABI kernels; x [.., H] in fp32 or bf16, affine fp32."""
+    """nn.LayerNorm (m3ae_decoder.py:46-49, clip_model.py:27-33, m3ae_module.py:122) on the C-ABI kernels; x [.., H] in fp32
+    or bf16, affine fp32, statistics in fp32 (which is what CLIP's fp32-cast LayerNorm subclass enforces)."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, eps):
         x2 = x.reshape(-1, x.shape[-1]).contiguous()
-        y, mean, rstd = ops.layernorm_fwd(x2, weight.detach(), bias.detach(), eps)
+        y, mean, rstd = ops.layernorm_fwd(x2, weight.detach().float().contiguous(), bias.detach().float().contiguous(), eps)
         ctx.save_for_backward(x2, mean, rstd, weight)
         ctx.shape = x.shape
         return y.view(x.shape)
@@ -636,8 +733,8 @@ class _LayerNormFn(torch.autograd.Function):
             d2 = ops.cast(d2, torch.empty_like(x2))
         dg = torch.zeros(H, dtype=torch.float32, device=x2.device)
         db = torch.zeros(H, dtype=torch.float32, device=x2.device)
-        dx = ops.layernorm_bwd(d2, x2, mean, rstd, weight.detach(), dg, db)
-        return dx.view(ctx.shape), dg, db, None
+        dx = ops.layernorm_bwd(d2, x2, mean, rstd, weight.detach().float().contiguous(), dg, db)
+        return dx.view(ctx.shape), dg.to(weight.dtype), db.to(weight.dtype), None
 
 
 def layernorm(x, weight, bias, eps):
@@ -646,68 +743,77 @@ def layernorm(x, weight, bias, eps):
 
 class _AttentionFn(torch.autograd.Function):
     """Multi-head attention core on packed projections: q [B*Lq, H*dh], k/v [B*Lk, H*dh] (may be column slices of a fused
-    projection buffer), additive key mask [B,Lk] or None, optional causal mask.  Returns ctx [B*Lq, H*dh]."""
+    projection buffer), additive key mask [B,Lk] or None, optional causal mask, optional dropout on the probabilities
+    (nn.MultiheadAttention(dropout=p) at m3ae_decoder.py:42-43; HF RobertaSelfAttention).  Returns ctx [B*Lq, H*dh]."""
 
     @staticmethod
-    def forward(ctx, q, k, v, mask, B, H, Lq, Lk, dh, causal):
+    def forward(ctx, q, k, v, mask, B, H, Lq, Lk, dh, causal, drop_p, drop_seed, drop_site):
         out = torch.empty(B * Lq, H * dh, dtype=q.dtype, device=q.device)
         lse = torch.empty(B, H, Lq, dtype=torch.float32, device=q.device)
-        ops.attn_fwd(q, k, v, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal)
+        ops.attn_fwd(q, k, v, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal, drop_p=drop_p,
+                     drop_seed=drop_seed, drop_stream=drop_site)
         ctx.save_for_backward(q, k, v, out, lse, mask)
-        ctx.dims = (B, H, Lq, Lk, dh, causal)
+        ctx.dims = (B, H, Lq, Lk, dh, causal, drop_p, drop_seed, drop_site)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse, mask = ctx.saved_tensors
-        B, H, Lq, Lk, dh, causal = ctx.dims
+        B, H, Lq, Lk, dh, causal, drop_p, drop_seed, drop_site = ctx.dims
         dout = dout.contiguous()
         dq = torch.empty(B * Lq, H * dh, dtype=q.dtype, device=q.device)
         dk = torch.empty(B * Lk, H * dh, dtype=q.dtype, device=q.device)
         dv = torch.empty(B * Lk, H * dh, dtype=q.dtype, device=q.device)
         delta = torch.empty(B, H, Lq, dtype=torch.float32, device=q.device)
         ops.attn_bwd(q, k, v, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, causal=causal, dout=dout, dq=dq, dk=dk,
-                     dv=dv, delta=delta)
-        return dq, dk, dv, None, None, None, None, None, None, None
+                     dv=dv, delta=delta, drop_p=drop_p, drop_seed=drop_seed, drop_stream=drop_site)
+        return (dq, dk, dv) + (None,) * 10
 
 
-def attention(q, k, v, mask, B, H, Lq, Lk, dh, causal=False):
-    return _AttentionFn.apply(q, k, v, mask, B, H, Lq, Lk, dh, causal)
+def attention(q, k, v, mask, B, H, Lq, Lk, dh, causal=False, drop_p=0.0, drop_seed=0, drop_site=0):
+    return _AttentionFn.apply(q, k, v, mask, B, H, Lq, Lk, dh, causal, float(drop_p), int(drop_seed), int(drop_site))
 
 
 class _FFNFn(torch.autograd.Function):
-    """y = act(x W0^T + b0) W2^T + b2 (+ residual): the decoder FFN (ReLU, m3ae_decoder.py:45,85-87).  The activation's
-    backward is fused into the dgrad epilogue of the second GEMM (needs the saved pre-activation)."""
+    """y = drop(act(x W0^T + b0) W2^T + b2) (+ residual): the decoder FFN (ReLU, m3ae_decoder.py:45,85-87), the CLIP MLP
+    (QuickGELU, clip_model.py:46-50,62) and the RoBERTa FFN (erf GELU).  The activation's backward is fused into the dgrad
+    epilogue of the second GEMM (needs the saved pre-activation)."""
 
     @staticmethod
-    def forward(ctx, x, w0, b0, w2, b2, residual, act, dtype):
+    def forward(ctx, x, w0, b0, w2, b2, residual, act, dtype, drop_p, drop_seed, drop_site):
         M, K = x.shape
         F = w0.shape[0]
         dev = x.device
-        xc = x if (x.dtype == dtype and x.is_contiguous()) else ops.cast(x.contiguous(), torch.empty(M, K, dtype=dtype, device=dev))
-        w0c = w0.detach() if w0.dtype == dtype else ops.cast(w0.detach(), torch.empty_like(w0, dtype=dtype))
-        w2c = w2.detach() if w2.dtype == dtype else ops.cast(w2.detach(), torch.empty_like(w2, dtype=dtype))
+        xc = _as_compute(x, dtype)
+        w0c = _as_compute(w0.detach(), dtype)
+        w2c = _as_compute(w2.detach(), dtype)
         u = torch.empty(M, F, dtype=dtype, device=dev)
         h = torch.empty(M, F, dtype=dtype, device=dev)
-        ops.gemm(xc, w0c, h, bias=b0.detach(), act=act, aux_out=u)
+        ops.gemm(xc, w0c, h, bias=b0.detach().float().contiguous(), act=act, aux_out=u)
         y = torch.empty(M, w2.shape[0], dtype=dtype, device=dev)
         rc = None
         if residual is not None:
-            rc = residual if (residual.dtype == dtype and residual.is_contiguous()) else ops.cast(residual.contiguous(), torch.empty_like(y))
-        ops.gemm(h, w2c, y, bias=b2.detach(), residual=rc)
+            rc = _as_compute(residual, dtype)
+        ops.gemm(h, w2c, y, bias=b2.detach().float().contiguous(), residual=rc, drop_p=drop_p, drop_seed=drop_seed, drop_stream=drop_site)
         ctx.save_for_backward(xc, w0c, w2c, u, h)
-        ctx.meta = (act, dtype, residual is not None, x.dtype, w0.dtype)
+        ctx.meta = (act, dtype, residual is not None, x.dtype, w0.dtype, None if residual is None else residual.dtype,
+                    drop_p, drop_seed, drop_site)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         xc, w0c, w2c, u, h = ctx.saved_tensors
-        act, dtype, has_res, xdtype, wdtype = ctx.meta
+        act, dtype, has_res, xdtype, wdtype, rdtype, drop_p, drop_seed, drop_site = ctx.meta
         M, K = xc.shape
         F = w0c.shape[0]
         N = w2c.shape[0]
         dev = dy.device
-        dyc = dy if (dy.dtype == dtype and dy.is_contiguous()) else ops.cast(dy.contiguous(), torch.empty(M, N, dtype=dtype, device=dev))
+        dyc = _as_compute(dy, dtype)
+        dres = None
+        if has_res:
+            dres = dy if dy.dtype == rdtype else dy.to(rdtype)
+        if drop_p > 0.0:
+            dyc = ops.dropout_apply(dyc, torch.empty_like(dyc), drop_p, drop_seed, drop_site)
         du = torch.empty(M, F, dtype=dtype, device=dev)
         dw2 = torch.zeros(N, F, dtype=torch.float32, device=dev)
         MN = ops.MAJOR_MN
@@ -721,8 +827,107 @@ class _FFNFn(torch.autograd.Function):
         db0 = ops.colsum(du, torch.zeros(F, dtype=torch.float32, device=dev))
         if dx.dtype != xdtype:
             dx = ops.cast(dx, torch.empty(M, K, dtype=xdtype, device=dev))
-        return dx, dw0.to(wdtype), db0, dw2.to(wdtype), db2, (dy if has_res else None), None, None
+        return dx, dw0.to(wdtype), db0, dw2.to(wdtype), db2, dres, None, None, None, None, None
 
 
-def ffn(x, w0, b0, w2, b2, residual=None, act=ops.ACT_RELU, dtype=torch.bfloat16):
-    return _FFNFn.apply(x, w0, b0, w2, b2, residual, act, dtype)
+def ffn(x, w0, b0, w2, b2, residual=None, act=ops.ACT_RELU, dtype=torch.bfloat16, drop_p=0.0, drop_seed=0, drop_site=0):
+    return _FFNFn.apply(x, w0, b0, w2, b2, residual, act, dtype, float(drop_p), int(drop_seed), int(drop_site))
+
+
+class _DropoutFn(torch.autograd.Function):
+    """nn.Dropout on a 2-D activation (decoder embedding dropout, m3ae_decoder.py:128; RoBERTa embedding dropout):
+    counter-based Philox mask keyed by (seed, site, element), regenerated in backward."""
+
+    @staticmethod
+    def forward(ctx, x, p, seed, site):
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        ctx.meta = (x.shape, p, seed, site)
+        return ops.dropout_apply(x2, torch.empty_like(x2), p, seed, site).view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        shape, p, seed, site = ctx.meta
+        d2 = dy.reshape(-1, shape[-1]).contiguous()
+        return ops.dropout_apply(d2, torch.empty_like(d2), p, seed, site).view(shape), None, None, None
+
+
+def dropout(x, p, seed, site=0):
+    if p <= 0.0:
+        return x
+    return _DropoutFn.apply(x, float(p), int(seed), int(site))
+
+
+class _ActivationFn(torch.autograd.Function):
+    """y = act(x) element-wise: Pooler tanh (prediction_heads.py:18), vqa_head GELU (m3ae_module.py:123)."""
+
+    @staticmethod
+    def forward(ctx, x, act):
+        xc = x.contiguous()
+        ctx.save_for_backward(xc)
+        ctx.act = act
+        return ops.activation_fwd(xc, act)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xc,) = ctx.saved_tensors
+        d = dy.contiguous()
+        if d.dtype != xc.dtype:
+            d = d.to(xc.dtype)
+        return ops.activation_bwd(d, xc, ctx.act), None
+
+
+def activation(x, act):
+    return _ActivationFn.apply(x, int(act))
+
+
+class _BCEWithLogitsFn(torch.autograd.Function):
+    """objectives.py:201: F.binary_cross_entropy_with_logits(logits, targets) * targets.shape[1] — loss and dlogits in
+    one pass over the [B, labels] logits."""
+
+    @staticmethod
+    def forward(ctx, logits, targets):
+        lg = logits.float().contiguous()
+        tg = targets.float().contiguous()
+        B = lg.shape[0]
+        loss, dx = ops.bce_with_logits(lg, tg, 1.0 / B, 1.0 / B, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(dx)
+        ctx.in_dtype = logits.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dx,) = ctx.saved_tensors
+        return (dx * dloss).to(ctx.in_dtype), None
+
+
+def vqa_bce_loss(logits, targets):
+    return _BCEWithLogitsFn.apply(logits, targets)
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    """m3ae_decoder.py:365-368: CrossEntropyLoss(ignore_index=pad)(logits^T, golden) — the mean over the non-pad golden
+    tokens (the `* padding_mask ... / padding_mask.sum()` that follows multiplies and divides a scalar by the same sum)."""
+
+    @staticmethod
+    def forward(ctx, logits, target, ignore_index):
+        V = logits.shape[-1]
+        lg = logits.reshape(-1, V).float()
+        if lg.stride(1) != 1:
+            lg = lg.contiguous()
+        tg = target.reshape(-1).contiguous()
+        n = (tg != ignore_index).sum().clamp_min(1).float()
+        w = (1.0 / n).expand(tg.shape[0]).contiguous()
+        loss, dx = ops.cross_entropy(lg, tg, w, ignore_index, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(dx)
+        ctx.meta = (logits.shape, logits.dtype)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dx,) = ctx.saved_tensors
+        shape, dtype = ctx.meta
+        return (dx * dloss).view(shape).to(dtype), None, None
+
+
+def cross_entropy(logits, target, ignore_index=-100):
+    return _CrossEntropyFn.apply(logits, target, int(ignore_index))

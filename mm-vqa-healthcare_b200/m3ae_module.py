@@ -6,15 +6,15 @@ path running on the sm_100a kernels.
                    reference's (`multi_modal_language_proj.*`, `multi_modal_vision_layers.{i}.*`, `vqa_head.*`, ...)
                    so reference checkpoints load and the optimizer's name-based parameter groups
                    (m3ae_utils.py:121-200: `multi_modal` substring -> lr x5, `vqa_head` -> lr x100) still apply.
-`M3AETransformerSS` adds the uni-modal encoders (CLIP ViT-B/16 visual tower and RoBERTa-base — plain PyTorch for now:
-                   they are SURVEY §8(f) "next" rows, not part of the hot path) and the reference's public surface:
+`M3AETransformerSS` adds the uni-modal encoders (CLIP ViT-B/16 visual tower and RoBERTa-base / BERT layers, on the same
+                   kernels: encoders.py) and the reference's public surface:
                    `infer(batch, ...) -> dict`, `forward(batch, test)`, the pytorch_lightning step hooks and
                    `configure_optimizers`.
 `patch_m3ae(model)` swaps the 12 BertCrossLayer instances of an EXISTING reference model for the B200 ones, re-using
                    its Parameter objects.
 """
-import math
-from collections import OrderedDict
+import json
+import os
 
 import torch
 import torch.nn as nn
@@ -23,6 +23,7 @@ import torch.nn.functional as F
 from . import functional as Fn
 from . import ops
 from .bert_cross_layer import BertCrossLayer, fused_layer_pair
+from .encoders import ClipVisionEncoder, text_encoder_forward
 
 try:  # pytorch_lightning is not installed in this image; the hooks below follow PL 1.3.2's calling convention
     import pytorch_lightning as pl
@@ -57,15 +58,36 @@ def init_weights(module):
 
 
 class Pooler(nn.Module):
-    """prediction_heads.Pooler (prediction_heads.py:9-19): tanh(dense(token 0)).  M = B rows: stays PyTorch."""
+    """prediction_heads.Pooler (prediction_heads.py:9-19): tanh(dense(token 0)) -> fp32 [B, hidden].  GEMM (M = batch
+    rows) + tanh kernel of libm3ae_b200."""
 
-    def __init__(self, hidden_size):
+    def __init__(self, hidden_size, compute_dtype=torch.bfloat16):
         super().__init__()
         self.dense = nn.Linear(hidden_size, hidden_size)
         self.activation = nn.Tanh()
+        self.compute_dtype = compute_dtype
 
     def forward(self, hidden_states):
-        return self.activation(self.dense(hidden_states[:, 0].float()))
+        first = hidden_states[:, 0].contiguous()
+        y = Fn.linear(first, self.dense.weight, self.dense.bias, dtype=self.compute_dtype, out_dtype=torch.float32)
+        return Fn.activation(y, ops.ACT_TANH)
+
+
+class VQAHead(nn.Sequential):
+    """vqa_head (m3ae_module.py:120-125): Linear(2h,2h) -> LayerNorm(2h, eps 1e-5) -> GELU -> Linear(2h, labels), same
+    state-dict keys (`0.*`, `1.*`, `3.*`), forward on the C-ABI kernels (GEMMs with M = batch rows, LayerNorm over 1536
+    columns, erf-GELU kernel); logits are fp32."""
+
+    def __init__(self, hs2, labels, compute_dtype=torch.bfloat16):
+        super().__init__(nn.Linear(hs2, hs2), nn.LayerNorm(hs2), nn.GELU(), nn.Linear(hs2, labels))
+        self.compute_dtype = compute_dtype
+
+    def forward(self, x):
+        dt = self.compute_dtype
+        h = Fn.linear(x, self[0].weight, self[0].bias, dtype=dt, out_dtype=torch.float32)
+        h = Fn.layernorm(h, self[1].weight, self[1].bias, self[1].eps)
+        h = Fn.activation(h, ops.ACT_GELU)
+        return Fn.linear(h, self[3].weight, self[3].bias, dtype=dt, out_dtype=torch.float32)
 
 
 def extended_attention_mask(mask):
@@ -78,15 +100,16 @@ DEFAULT_CONFIG = {  # config.py:19-119 + task_finetune_vqa_vqa_rad (:176-198) + 
     "num_heads": 12, "mlp_ratio": 4, "max_text_len": 32, "drop_rate": 0.1, "image_size": 288, "patch_size": 16,
     "input_text_embed_size": 768, "input_image_embed_size": 768, "num_top_layer": 6,
     "loss_names": {"mlm": 0, "mim": 0, "itm": 0, "vqa": 1, "cls": 0, "irtr": 0}, "load_path": "", "test_only": False,
-    "vqa_label_size": 498, "precision": 16, "learning_rate": 5e-6, "weight_decay": 0.01, "lr_multiplier_head": 50,
+    "vqa_label_size": 498, "precision": 16, "learning_rate": 1e-5, "weight_decay": 0.01, "lr_multiplier_head": 100,
     "lr_multiplier_multi_modal": 5, "end_lr": 0, "decay_power": 1, "optim_type": "adamw", "warmup_steps": 0.1,
-    "max_steps": None, "max_epoch": 50,
+    "max_steps": 1000, "max_epoch": 20, "label2ans_path": "label2ans.json",
 }
 
 
 def _bert_config(config):
-    from transformers import RobertaConfig
-    return RobertaConfig(  # m3ae_module.py:24-33
+    from transformers import BertConfig, RobertaConfig
+    cls = RobertaConfig if "roberta" in config["tokenizer"] else BertConfig  # m3ae_module.py:22-45
+    return cls(
         vocab_size=config["vocab_size"], hidden_size=config["hidden_size"], num_hidden_layers=config["num_layers"],
         num_attention_heads=config["num_heads"], intermediate_size=config["hidden_size"] * config["mlp_ratio"],
         max_position_embeddings=config["max_text_len"], hidden_dropout_prob=config["drop_rate"],
@@ -110,11 +133,10 @@ class M3AEFusion(_Base):
             [BertCrossLayer(bert_config, compute_dtype) for _ in range(config["num_top_layer"])])
         self.multi_modal_language_layers = nn.ModuleList(
             [BertCrossLayer(bert_config, compute_dtype) for _ in range(config["num_top_layer"])])
-        self.multi_modal_vision_pooler = Pooler(hs)
-        self.multi_modal_language_pooler = Pooler(hs)
+        self.multi_modal_vision_pooler = Pooler(hs, compute_dtype)
+        self.multi_modal_language_pooler = Pooler(hs, compute_dtype)
         if config["loss_names"].get("vqa", 0) > 0:
-            vs = config["vqa_label_size"]
-            self.vqa_head = nn.Sequential(nn.Linear(hs * 2, hs * 2), nn.LayerNorm(hs * 2), nn.GELU(), nn.Linear(hs * 2, vs))
+            self.vqa_head = VQAHead(hs * 2, config["vqa_label_size"], compute_dtype)
         self.apply(init_weights)
         self.current_tasks = list()
 
@@ -122,6 +144,9 @@ class M3AEFusion(_Base):
         self.compute_dtype = dtype
         for l in list(self.multi_modal_vision_layers) + list(self.multi_modal_language_layers):
             l.set_compute_dtype(dtype)
+        for m in self.modules():
+            if isinstance(m, (Pooler, VQAHead, ClipVisionEncoder)):
+                m.compute_dtype = dtype
         return self
 
     def fuse(self, uni_modal_text_feats, uni_modal_image_feats, text_masks, image_token_type_idx=1, output_attentions=False):
@@ -146,9 +171,9 @@ class M3AEFusion(_Base):
             if output_attentions:
                 ret["attentions"]["text2image_attns"].append(x1[1:])
                 ret["attentions"]["image2text_attns"].append(y1[1:])
+        cls_text = self.multi_modal_language_pooler(x)
+        cls_image = self.multi_modal_vision_pooler(y)
         multi_modal_text_feats, multi_modal_image_feats = x.float(), y.float()
-        cls_text = self.multi_modal_language_pooler(multi_modal_text_feats)
-        cls_image = self.multi_modal_vision_pooler(multi_modal_image_feats)
         ret.update({
             "extended_image_masks": extended_image_masks,
             "extended_text_masks": extended_text_masks,
@@ -162,84 +187,26 @@ class M3AEFusion(_Base):
         """compute_vqa_m3ae restricted to tensors (objectives.py:177-178,201)."""
         ret = self.fuse(uni_modal_text_feats, uni_modal_image_feats, text_masks)
         logits = self.vqa_head(ret["multi_modal_cls_feats"])
-        loss = F.binary_cross_entropy_with_logits(logits, vqa_targets) * vqa_targets.shape[1]
+        loss = Fn.vqa_bce_loss(logits, vqa_targets)  # BCE-with-logits (mean) * n_labels, objectives.py:201
         return loss, logits, ret
 
 
-# ----------------------------------------------------------------------------- uni-modal encoders (plain PyTorch, "next" rows)
-class _LayerNormF32(nn.LayerNorm):
-    def forward(self, x):
-        return super().forward(x.float()).to(x.dtype)
-
-
-class _ResBlock(nn.Module):
-    """CLIP ResidualAttentionBlock (clip_model.py:41-63): pre-LN MHA + QuickGELU MLP; parameter names kept."""
-
-    def __init__(self, d_model, n_head):
-        super().__init__()
-        self.attn = nn.MultiheadAttention(d_model, n_head)
-        self.ln_1 = _LayerNormF32(d_model)
-        self.mlp = nn.Sequential(OrderedDict([("c_fc", nn.Linear(d_model, d_model * 4)), ("gelu", nn.Identity()),
-                                              ("c_proj", nn.Linear(d_model * 4, d_model))]))
-        self.ln_2 = _LayerNormF32(d_model)
-        self.n_head = n_head
-
-    def forward(self, x):  # x: [B, L, D]
-        B, L, D = x.shape
-        h = self.ln_1(x)
-        qkv = F.linear(h, self.attn.in_proj_weight, self.attn.in_proj_bias).view(B, L, 3, self.n_head, D // self.n_head)
-        q, k, v = qkv.permute(2, 0, 3, 1, 4)
-        a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, L, D)
-        x = x + self.attn.out_proj(a)
-        h = self.mlp.c_fc(self.ln_2(x))
-        return x + self.mlp.c_proj(h * torch.sigmoid(1.702 * h))
-
-
-class _Transformer(nn.Module):
-    def __init__(self, width, layers, heads):
-        super().__init__()
-        self.width, self.layers = width, layers
-        self.resblocks = nn.Sequential(*[_ResBlock(width, heads) for _ in range(layers - 1)])  # clip_model.py:71
-
-    def forward(self, x):
-        return self.resblocks(x)
-
-
-class _VisualTransformer(nn.Module):
-    """clip_model.VisualTransformer (:79-128), batch-first."""
-
-    def __init__(self, patch_size, width, layers, heads, resolution_after):
-        super().__init__()
-        self.conv1 = nn.Conv2d(3, width, kernel_size=patch_size, stride=patch_size, bias=False)
-        scale = width ** -0.5
-        self.class_embedding = nn.Parameter(scale * torch.randn(width))
-        self.positional_embedding = nn.Parameter(scale * torch.randn((resolution_after // patch_size) ** 2 + 1, width))
-        self.ln_pre = _LayerNormF32(width)
-        self.transformer = _Transformer(width, layers, heads)
-        self.ln_post = _LayerNormF32(width)
-
-    def forward(self, x):
-        x = self.conv1(x).flatten(2).transpose(1, 2)
-        cls = self.class_embedding.to(x.dtype).expand(x.shape[0], 1, -1)
-        x = torch.cat([cls, x], dim=1) + self.positional_embedding.to(x.dtype)
-        return self.ln_post(self.transformer(self.ln_pre(x)))
-
-
-class _ClipVisionEncoder(nn.Module):
-    """`vision_encoder` of the reference = CLIP whose forward is visual(image) (clip_model.py:186-187)."""
-
-    def __init__(self, resolution_after, patch_size=16, width=768, layers=12, heads=12):
-        super().__init__()
-        self.visual = _VisualTransformer(patch_size, width, layers, heads, resolution_after)
-        proj_std = (width ** -0.5) * ((2 * layers) ** -0.5)
-        for b in self.visual.transformer.resblocks:  # clip_model.py:172-180
-            nn.init.normal_(b.attn.in_proj_weight, std=width ** -0.5)
-            nn.init.normal_(b.attn.out_proj.weight, std=proj_std)
-            nn.init.normal_(b.mlp.c_fc.weight, std=(2 * width) ** -0.5)
-            nn.init.normal_(b.mlp.c_proj.weight, std=proj_std)
-
-    def forward(self, image):
-        return self.visual(image.to(self.visual.conv1.weight.dtype))
+def adapt_position_encoding(state_dict, patch_size, after, prefix="vision_encoder.visual.positional_embedding"):
+    """clip_model.adapt_position_encoding (vision_encoders/clip_model.py:224-251): bicubic resize of the CLIP
+    grid positional embedding when the fine-tune resolution differs from the checkpoint's."""
+    for key in [k for k in state_dict if k.endswith(prefix)]:
+        pe = state_dict[key]
+        grid_before = int((pe.shape[0] - 1) ** 0.5)
+        grid_after = after // patch_size
+        if grid_before == grid_after:
+            continue
+        cls_pe, grid_pe = pe[:1], pe[1:]
+        emb = grid_pe.shape[-1]
+        grid_pe = grid_pe.reshape(1, grid_before, grid_before, emb).permute(0, 3, 1, 2)
+        grid_pe = F.interpolate(grid_pe, size=(grid_after, grid_after), mode="bicubic", align_corners=False)
+        grid_pe = grid_pe.permute(0, 2, 3, 1).reshape(grid_after * grid_after, emb)
+        state_dict[key] = torch.cat([cls_pe, grid_pe], dim=0)
+    return state_dict
 
 
 class M3AETransformerSS(M3AEFusion):
@@ -248,19 +215,26 @@ class M3AETransformerSS(M3AEFusion):
     def __init__(self, config=None, compute_dtype=None):
         super().__init__(config, compute_dtype)
         config = self.hparams.config
-        from transformers import RobertaConfig, RobertaModel
         self.is_clip = "swin" not in config["vit"]
         if not self.is_clip:
             raise NotImplementedError("Swin backbones are outside the B200 hot-path scope (SURVEY §2 #10)")
         # The reference downloads pretrained CLIP / RoBERTa weights (m3ae_module.py:60-68); offline they are random-init
         # modules of the same architecture whose state_dict keys match, so a reference checkpoint restores them.
-        self.vision_encoder = _ClipVisionEncoder(config["image_size"], config["patch_size"])
-        rc = RobertaConfig(vocab_size=config["vocab_size"], hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
-                           intermediate_size=3072, max_position_embeddings=514, type_vocab_size=1, pad_token_id=1,
-                           layer_norm_eps=1e-5)
-        self.language_encoder = RobertaModel(rc)
-        if config["load_path"]:
+        self.vision_encoder = ClipVisionEncoder(config["image_size"], config["patch_size"], compute_dtype=self.compute_dtype)
+        if "roberta" in config["tokenizer"]:  # m3ae_module.py:63-68
+            from transformers import RobertaConfig, RobertaModel
+            rc = RobertaConfig(vocab_size=config["vocab_size"], hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
+                               intermediate_size=3072, max_position_embeddings=514, type_vocab_size=1, pad_token_id=1,
+                               layer_norm_eps=1e-5)
+            self.language_encoder = RobertaModel(rc)
+        else:
+            from transformers import BertConfig, BertModel
+            self.language_encoder = BertModel(BertConfig(vocab_size=config["vocab_size"]))
+        self._label2ans = None
+        if config["load_path"]:  # m3ae_module.py:103-113 (fine-tune) and :133-139 (test_only: positional table as stored)
             sd = torch.load(config["load_path"], map_location="cpu")["state_dict"]
+            if not config["test_only"]:
+                sd = adapt_position_encoding(sd, config["patch_size"], config["image_size"])
             self.load_state_dict(sd, strict=False)
 
     def patchify(self, imgs):
@@ -270,13 +244,8 @@ class M3AETransformerSS(M3AEFusion):
         return torch.einsum("nchpwq->nhwpqc", x).reshape(imgs.shape[0], h * w, p ** 2 * 3)
 
     def encode_text(self, text_ids, text_masks):
-        """m3ae_module.py:230-234: RoBERTa embeddings + 12 layers driven one by one with the additive mask."""
-        h = self.language_encoder.embeddings(input_ids=text_ids)
-        ext = extended_attention_mask(text_masks)
-        for layer in self.language_encoder.encoder.layer:
-            out = layer(h, ext)
-            h = out[0] if isinstance(out, (tuple, list)) else out
-        return h
+        """m3ae_module.py:230-234: embeddings + 12 encoder layers driven one by one with the additive mask, on the kernels."""
+        return text_encoder_forward(self.language_encoder, text_ids, text_masks, self.compute_dtype, self.training)
 
     def infer(self, batch, mask_text=False, mask_image=False, image_token_type_idx=1, img=None, output_attentions=False,
               unimodal=False):
@@ -286,32 +255,44 @@ class M3AETransformerSS(M3AEFusion):
             key = f"image_{image_token_type_idx - 1}"
             img = batch[key if key in batch else "image"][0]
         text_ids, text_labels, text_masks = batch["text_ids"], batch["text_labels"], batch["text_masks"]
-        autocast = self.compute_dtype == torch.bfloat16
-        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
-            uni_text = self.encode_text(text_ids, text_masks)
-            uni_image = self.vision_encoder(img)
+        uni_text = self.encode_text(text_ids, text_masks)
+        uni_image = self.vision_encoder(img)
         ret = self.fuse(uni_text, uni_image, text_masks, image_token_type_idx, output_attentions)
         ret.update({"images": img, "patched_images": self.patchify(img), "text_labels": text_labels, "text_ids": text_ids,
                     "text_masks": text_masks})
         return ret
 
+    def label2ans(self):
+        """objectives.py:180-181 reads label2ans.json (CWD) every step; here it is read once.  Missing file: labels as text."""
+        if self._label2ans is None:
+            path = self.hparams.config.get("label2ans_path", "label2ans.json")
+            self._label2ans = json.load(open(path)) if path and os.path.exists(path) else {}
+        return self._label2ans
+
     def compute_vqa(self, batch, test=False):
-        """objectives.compute_vqa_m3ae (objectives.py:176-234) minus the CPU string metrics."""
+        """objectives.compute_vqa_m3ae (objectives.py:176-212) minus the CPU string metrics (ROUGE / BLEU / exact match)."""
         infer = self.infer(batch)
         logits = self.vqa_head(infer["multi_modal_cls_feats"])
+        predictions = logits.argmax(dim=1)
+        l2a = self.label2ans()
+        english_answers = [l2a.get(str(p), str(p)) for p in predictions.tolist()]  # one D2H copy instead of B .item() calls
         n = self.hparams.config["vqa_label_size"]
-        targets = torch.zeros(len(logits), n, device=logits.device)
         rows, cols, vals = [], [], []
         for i, (labels, scores) in enumerate(zip(batch["vqa_labels"], batch["vqa_scores"])):
             for l, s in zip(labels, scores):
                 rows.append(i), cols.append(l), vals.append(s)
+        targets = torch.zeros(len(logits), n)
         if rows:
-            targets[torch.tensor(rows, device=logits.device), torch.tensor(cols, device=logits.device)] = torch.tensor(vals, device=logits.device)
-        loss = F.binary_cross_entropy_with_logits(logits, targets) * targets.shape[1]
+            targets[rows, cols] = torch.tensor(vals, dtype=torch.float32)
+        targets = targets.to(logits.device, non_blocking=True)
+        loss = Fn.vqa_bce_loss(logits, targets)
         phase = "test" if test else ("train" if self.training else "val")
         self.log(f"{phase}/vqa/loss", loss.detach())
-        return {"vqa_loss": loss, "vqa_logits": logits, "vqa_targets": targets, "vqa_labels": batch["vqa_labels"],
-                "vqa_scores": batch["vqa_scores"], "vqa_predictions": logits.argmax(dim=1),
+        return {"vqa_loss": loss, "vqa_logits": logits,
+                "vqa_model_answers": english_answers,
+                "vqa_true_answers": [a for l in batch.get("vqa_answer", []) for a in l],
+                "vqa_targets": targets, "vqa_labels": batch["vqa_labels"],
+                "vqa_scores": batch["vqa_scores"], "vqa_predictions": predictions,
                 "vqa_answer_types": torch.tensor(batch.get("answer_types", [0] * len(logits)), device=logits.device)}
 
     def forward(self, batch, test=False):

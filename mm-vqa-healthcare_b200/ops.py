@@ -7,7 +7,7 @@ import ctypes as C
 import torch
 
 from . import _lib as L
-from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, ATTN_MMA_SYNC, BF16, F32, GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, MAJOR_K, MAJOR_MN  # noqa: F401
+from ._lib import ACT_GELU, ACT_NONE, ACT_QUICKGELU, ACT_RELU, ACT_TANH, ATTN_MMA_SYNC, BF16, F32, GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, MAJOR_K, MAJOR_MN  # noqa: F401
 
 
 def _code(dtype):
@@ -174,6 +174,57 @@ def attn_fwd(q, k, v, out, lse, **kw):
 def attn_bwd(q, k, v, out, lse, **kw):
     p = attn_params(q, k, v, out, lse, **kw)
     L.check(L.load().m3ae_attn_bwd(C.byref(p), _stream()), "m3ae_attn_bwd")
+
+
+def attn_probs(q, k, lse, probs, *, B, H, Lq, Lk, dh, mask=None, scale=None, causal=False, drop_p=0.0, drop_seed=0, drop_stream=0):
+    """probs [B,H,Lq,Lk] fp32 = dropout(exp(scale*q.k^T + mask - lse)) from a forward call's q, k and saved lse."""
+    out = q  # attn_params wants an `out` of q's geometry; the probs kernel never touches it
+    p = attn_params(q, k, k, out, lse, B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, probs=probs, scale=scale, causal=causal,
+                    drop_p=drop_p, drop_seed=drop_seed, drop_stream=drop_stream)
+    L.check(L.load().m3ae_attn_probs(C.byref(p), _stream()), "m3ae_attn_probs")
+    return probs
+
+
+def activation_fwd(x, act, y=None):
+    _need_cuda(x)
+    assert x.is_contiguous()
+    y = torch.empty_like(x) if y is None else y
+    L.check(L.load().m3ae_activation_fwd(_ptr(x), _ptr(y), x.numel(), int(act), _code(x.dtype), _stream()), "m3ae_activation_fwd")
+    return y
+
+
+def activation_bwd(dy, x, act, dx=None):
+    _need_cuda(dy, x)
+    assert x.is_contiguous() and dy.is_contiguous() and dy.dtype == x.dtype and dy.numel() == x.numel()
+    dx = torch.empty_like(x) if dx is None else dx
+    L.check(L.load().m3ae_activation_bwd(_ptr(dy), _ptr(x), _ptr(dx), x.numel(), int(act), _code(x.dtype), _stream()),
+            "m3ae_activation_bwd")
+    return dx
+
+
+def bce_with_logits(logits, targets, scale_loss, scale_grad, want_grad=True):
+    """-> (loss scalar tensor, dlogits or None); loss = scale_loss * sum bce(logits, targets)."""
+    _need_cuda(logits, targets)
+    assert logits.dtype == torch.float32 and targets.dtype == torch.float32 and logits.is_contiguous() and targets.is_contiguous()
+    assert logits.shape == targets.shape
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dx = torch.empty_like(logits) if want_grad else None
+    L.check(L.load().m3ae_bce_with_logits(_ptr(logits), _ptr(targets), _ptr(loss), _ptr(dx), logits.numel(), float(scale_loss),
+                                          float(scale_grad), _stream()), "m3ae_bce_with_logits")
+    return loss, dx
+
+
+def cross_entropy(logits, target, row_weight, ignore_index, want_grad=True):
+    """logits [M,V] fp32, target [M] int64, row_weight [M] fp32 -> (loss scalar, dlogits [M,V] or None)."""
+    _need_cuda(logits, target, row_weight)
+    assert logits.dim() == 2 and logits.dtype == torch.float32 and logits.stride(1) == 1
+    assert target.dtype == torch.int64 and target.is_contiguous() and row_weight.dtype == torch.float32 and row_weight.is_contiguous()
+    M, V = logits.shape
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dx = torch.empty(M, V, dtype=torch.float32, device=logits.device) if want_grad else None
+    L.check(L.load().m3ae_cross_entropy(_ptr(logits), logits.stride(0), _ptr(target), _ptr(row_weight), _ptr(loss), _ptr(dx), V, M, V,
+                                        int(ignore_index), _stream()), "m3ae_cross_entropy")
+    return loss, dx
 
 
 def layernorm_fwd(x, gamma, beta, eps, y=None, mean=None, rstd=None):

@@ -356,6 +356,73 @@ def make_decoder_state(seed, num_layers=6, d_model=768, d_ff=3072, vocab=30522, 
     return sd
 
 
+def seeded_tensor_like(name, t, seed):
+    """Deterministic stand-in weights for a named state-dict tensor: the same (name, shape, seed) gives the same values in
+    the reference model and in the drop-in, so whole-model parity fixtures need not ship 1.3 GB of weights.
+    >= 2-D tensors ~ N(0, 0.03); LayerNorm-style `weight` vectors ~ 1 + 0.1 N(0,1); other vectors ~ 0.02 N(0,1)."""
+    import zlib
+    g = torch.Generator().manual_seed((zlib.crc32(name.encode()) + 7919 * seed) & 0x7FFFFFFF)
+    if t.dim() >= 2:
+        return torch.randn(t.shape, generator=g) * 0.03
+    if name.endswith("weight"):
+        return 1.0 + 0.1 * torch.randn(t.shape, generator=g)
+    return 0.02 * torch.randn(t.shape, generator=g)
+
+
+def seed_model_parameters(model, seed):
+    """In-place: every floating-point PARAMETER of `model` := seeded_tensor_like(its state-dict name)."""
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if p.dtype.is_floating_point:
+                p.copy_(seeded_tensor_like(name, p, seed))
+    return model
+
+
+def make_model_batch(seed, B, image_size=288, Lt=32, num_labels=498, device="cpu"):
+    """Seeded synthetic batch dict in the layout BaseDataset.collate produces (base_dataset.py:165-228)."""
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(3, 50265, (B, Lt), generator=g)
+    ids[:, 0] = 0
+    lens = torch.randint(8, Lt + 1, (B,), generator=g)
+    masks = (torch.arange(Lt)[None, :] < lens[:, None]).long()
+    ids = torch.where(masks.bool(), ids, torch.ones_like(ids))
+    labels = torch.randint(0, num_labels, (B,), generator=g)
+    image = torch.randn(B, 3, image_size, image_size, generator=g)
+    return {"image": [image.to(device)], "text_ids": ids.to(device), "text_masks": masks.to(device),
+            "text_labels": torch.full((B, Lt), -100).to(device), "vqa_labels": [[int(l)] for l in labels],
+            "vqa_scores": [[1.0]] * B, "answer_types": [int(l) % 2 for l in labels],
+            "vqa_answer": [[f"answer {int(l)}"] for l in labels]}
+
+
+class SynthTokenizer:
+    """Stand-in for HF BertTokenizer('bert-base-uncased') (m3ae_decoder.py:191; no vocabulary file offline): whitespace
+    split, hashed ids in [1000, vocab), BERT's special ids.  Same surface the reference uses (:336-342, :326-329)."""
+
+    cls_token_id, sep_token_id, pad_token_id, eos_token_id = 101, 102, 0, None
+
+    def __init__(self, vocab_size=30522):
+        self.vocab_size = vocab_size
+        self._words = {}
+
+    def _id(self, w):
+        h = 1000 + (sum((i + 1) * ord(c) * 2654435761 for i, c in enumerate(w)) % (self.vocab_size - 1000))
+        self._words.setdefault(h, w)
+        return h
+
+    def __call__(self, texts, padding=True, truncation=True, return_tensors="pt", max_length=12):
+        rows = [([self.cls_token_id] + [self._id(w) for w in t.lower().split()])[:max_length - 1] + [self.sep_token_id] for t in texts]
+        width = max(len(r) for r in rows)
+        out = torch.full((len(rows), width), self.pad_token_id, dtype=torch.long)
+        for i, r in enumerate(rows):
+            out[i, :len(r)] = torch.tensor(r)
+        return type("Enc", (), {"input_ids": out})()
+
+    def decode(self, seq, skip_special_tokens=True):
+        ids = seq.tolist() if torch.is_tensor(seq) else list(seq)
+        special = {self.cls_token_id, self.sep_token_id, self.pad_token_id}
+        return " ".join(self._words.get(i, f"[{i}]") for i in ids if not (skip_special_tokens and i in special))
+
+
 def make_fusion_inputs(seed, B, Lt=32, Li=325, num_labels=498, all_valid=False):
     """Seeded synthetic hot-path inputs: uni-modal features of the shapes RoBERTa / CLIP ViT-B/16
     produce at 288 px / 32 tokens, ragged text masks (valid length uniform in [8,32]), one-hot VQA targets."""

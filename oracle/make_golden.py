@@ -102,6 +102,90 @@ def gen_fusion():
     print("fusion.pt loss", float(loss), "argmax", logits.argmax(1).tolist())
 
 
+def gen_full_model():
+    """BASELINE config 1 (classifier forward, B=8, 288 px / 32 tokens, CPU fp32, eval) through the reference's REAL
+    M3AETransformerSS: its own CLIP ViT-B/16 class + a random-init HF RobertaModel + 6+6 fusion layers + vqa_head, all
+    parameters seeded by name (oracle.seed_model_parameters) so the drop-in can rebuild the same weights on the GPU box.
+    Also a B=2 forward+backward (eval mode = dropout off) for encoder / fusion gradient parity."""
+    mm3, Cls = ref_shim.load_m3ae_module(real_encoders=True)
+    torch.manual_seed(0)
+    model = Cls(ref_shim.m3ae_config()).eval()
+    O.seed_model_parameters(model, 5)
+    names = [n for n, _ in model.named_parameters()]
+    params = dict(model.named_parameters())
+    ref_shim.wrap_text_layers(model)
+    cap = {}
+    model.vision_encoder.register_forward_hook(lambda m, i, o: cap.__setitem__("uni_image", o.detach()))
+    model.multi_modal_language_proj.register_forward_hook(lambda m, i, o: cap.__setitem__("uni_text", i[0].detach()))
+    out = {}
+    batch = O.make_model_batch(51, 8)
+    with torch.no_grad():
+        ret = model.infer(batch)
+        logits = model.vqa_head(ret["multi_modal_cls_feats"])
+        targets = O.vqa_targets(batch["vqa_labels"], batch["vqa_scores"], 498)
+        loss = O.vqa_loss(logits, targets)
+    out["b8"] = {"vqa_logits": logits, "vqa_loss": loss, "argmax": logits.argmax(1),
+                 "multi_modal_cls_feats": ret["multi_modal_cls_feats"], "multi_modal_text_feats": ret["multi_modal_text_feats"],
+                 "multi_modal_image_feats_sub": ret["multi_modal_image_feats"][:, ::25].clone(),
+                 "uni_text_feats": cap["uni_text"].clone(), "uni_image_feats_sub": cap["uni_image"][:, ::25].clone(),
+                 "patched_images_sum": ret["patched_images"].sum(-1), "keys": sorted(ret.keys())}
+    batch = O.make_model_batch(52, 2)
+    model.zero_grad()
+    ret = model.infer(batch)
+    logits = model.vqa_head(ret["multi_modal_cls_feats"])
+    loss = O.vqa_loss(logits, O.vqa_targets(batch["vqa_labels"], batch["vqa_scores"], 498))
+    loss.backward()
+    g = {}
+    for n in names:
+        p = params[n]
+        if p.grad is not None:
+            g[n] = {"norm": p.grad.norm(), "samples": p.grad.flatten()[:: max(1, p.numel() // 64)][:64].clone()}
+    out["b2"] = {"vqa_logits": logits.detach(), "vqa_loss": loss.detach(), "grads": g, "no_grad": [n for n in names if params[n].grad is None]}
+    torch.save(out, os.path.join(OUT, "full_model.pt"))
+    print("full_model.pt loss b8", float(out["b8"]["vqa_loss"]), "argmax", out["b8"]["argmax"].tolist(), "grads", len(g),
+          "without grad", len(out["b2"]["no_grad"]))
+
+
+DECODER_MODEL_ANSWERS = [["left lower lobe pneumonia"], ["no"]]
+
+
+def decoder_model_config():
+    cfg = ref_shim.m3ae_config()
+    cfg.update({"decoder_load_path": "", "mm_encoder_inputs_include_imagetext_feats": True,
+                "mm_encoder_inputs_include_cls_feats": True, "learning_rate": 1e-5, "weight_decay": 0.01, "end_lr": 0,
+                "decay_power": 1, "optim_type": "adamw", "warmup_steps": 0.1})
+    return cfg
+
+
+def gen_decoder_model():
+    """The reference's DecoderModel.forward (m3ae_decoder.py:296-388), eval mode (dropout off), B=2: teacher-forced loss +
+    decoder gradients, and the test branch (greedy search_path with the constructor's max_len=128)."""
+    tok = O.SynthTokenizer()
+    Cls = ref_shim.load_decoder_model(tok)
+    torch.manual_seed(0)
+    model = Cls(decoder_model_config()).eval()
+    O.seed_model_parameters(model, 9)
+    ref_shim.wrap_text_layers(model.m3ae)
+    batch = O.make_model_batch(61, 2)
+    batch["vqa_answer"] = DECODER_MODEL_ANSWERS
+    model.current_tasks = ["vqa"]
+    ret = model(batch)
+    loss = ret["vqa_loss"]
+    loss.backward()
+    grads = {n: {"norm": p.grad.norm(), "samples": p.grad.flatten()[:: max(1, p.numel() // 64)][:64].clone()}
+             for n, p in model.named_parameters() if p.grad is not None}
+    with torch.no_grad():
+        mem = model.m3ae.infer(batch)
+        memory = torch.cat([mem["multi_modal_image_feats"], mem["multi_modal_text_feats"], mem["multi_modal_cls_feats"].view(-1, 2, 768)], dim=1)
+        ids = model.decoder.search_path(memory, tok)
+        test_ret = model(batch, test=True)
+    out = {"loss": loss.detach(), "train_texts": ret["vqa_logits"], "grads": grads, "memory_sub": memory[:, ::20].clone(),
+           "greedy_ids": ids, "test_texts": test_ret["vqa_logits"], "test_loss": test_ret["vqa_loss"],
+           "ret_keys": sorted(ret.keys())}
+    torch.save(out, os.path.join(OUT, "decoder_model.pt"))
+    print("decoder_model.pt loss", float(loss), "grads", len(grads), "greedy", ids[0, :8].tolist(), "texts", test_ret["vqa_logits"])
+
+
 class Tok:
     cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
 
@@ -144,5 +228,7 @@ if __name__ == "__main__":
     gen_cross_layer(ref)
     gen_decoder(ref)
     gen_fusion()
+    gen_full_model()
+    gen_decoder_model()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")

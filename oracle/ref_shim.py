@@ -14,7 +14,8 @@ import os
 import sys
 import types
 
-REF_ROOT = os.environ.get("M3AE_REFERENCE_ROOT", "/root/reference")
+_SNAPSHOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")  # oracle/snapshot_ref.py (git-ignored)
+REF_ROOT = os.environ.get("M3AE_REFERENCE_ROOT") or ("/root/reference" if os.path.isdir("/root/reference/m3ae/modules") else _SNAPSHOT)
 
 
 def available():
@@ -117,8 +118,13 @@ def fusion_config(drop_rate=0.0):
                          attention_probs_dropout_prob=drop_rate)
 
 
-def load_m3ae_module():
+def load_m3ae_module(real_encoders=False):
     """Imports the reference's m3ae/modules/m3ae_module.py unmodified and returns (module, M3AETransformerSS).
+    real_encoders=True: the uni-modal encoders are the reference's own CLIP class (vision_encoders/clip_model.py, ViT-B/16
+    hyper-parameters that build_model would read from the checkpoint, :277-297) and a random-init HF RobertaModel of
+    roberta-base dimensions, with the two HF 4.6.0 -> 5.x drifts neutralised: get_extended_attention_mask
+    keeps the pinned (1 - mask) * -10000 semantics, and encoder layers return 1-tuples so that `layer(h, mask)[0]`
+    (m3ae_module.py:234) still selects the hidden states.
     The uni-modal encoders need downloaded checkpoints (clip_model.build_model, RobertaModel.from_pretrained) that do
     not exist offline, so both constructors are replaced by tiny stand-ins; callers then plug seeded uni-modal
     features in (see oracle/make_golden.py) so that the fusion section of infer() (m3ae_module.py:235,252-297) runs
@@ -165,9 +171,55 @@ def load_m3ae_module():
         def get_extended_attention_mask(self, mask, shape, device):  # HF 4.6.0 semantics (pinned version)
             return (1.0 - mask[:, None, None, :].to(torch.float32)) * -10000.0
 
-    mm3.build_model = lambda *a, **k: _TinyVision()
-    mm3.RobertaModel = types.SimpleNamespace(from_pretrained=lambda *a, **k: _TinyText())
+    if not real_encoders:
+        mm3.build_model = lambda *a, **k: _TinyVision()
+        mm3.RobertaModel = types.SimpleNamespace(from_pretrained=lambda *a, **k: _TinyText())
+        return mm3, mm3.M3AETransformerSS
+
+    clip_model = importlib.import_module("m3ae.modules.vision_encoders.clip_model")
+
+    def build_clip(name, resolution_after=224, jit=False):
+        return clip_model.CLIP(512, 224, 12, 768, 16, 77, 49408, 512, 8, 12, resolution_after)
+
+    class _TupleLayer(nn.Module):
+        """HF 5.x encoder layers return a Tensor; the reference indexes [0] (HF 4.6.0 returned a tuple)."""
+
+        def __init__(self, layer):
+            super().__init__()
+            self.layer = layer
+
+        def forward(self, h, mask):
+            out = self.layer(h, mask)
+            return out if isinstance(out, (tuple, list)) else (out,)
+
+    def build_roberta(name, *a, **k):
+        from transformers import RobertaConfig, RobertaModel
+        rc = RobertaConfig(vocab_size=50265, hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
+                           intermediate_size=3072, max_position_embeddings=514, type_vocab_size=1, pad_token_id=1,
+                           layer_norm_eps=1e-5)
+        try:
+            rc._attn_implementation = "eager"
+        except Exception:
+            pass
+        m = RobertaModel(rc)
+        m.get_extended_attention_mask = lambda mask, shape, device=None: (1.0 - mask[:, None, None, :].to(torch.float32)) * -10000.0
+        return m
+
+    mm3.build_model = build_clip
+    mm3.RobertaModel = types.SimpleNamespace(from_pretrained=build_roberta)
+    mm3._TupleLayer = _TupleLayer
     return mm3, mm3.M3AETransformerSS
+
+
+def wrap_text_layers(model):
+    """Call after loading weights: wraps language_encoder.encoder.layer[i] so that `layer(h, mask)[0]` works on HF 5.x.
+    (The wrappers are not registered under new names in state_dict: they are applied on a shallow ModuleList copy.)"""
+    import torch.nn as nn
+    mm3 = sys.modules["m3ae.modules.m3ae_module"]
+    enc = model.language_encoder.encoder
+    object.__setattr__(enc, "_orig_layers", enc.layer)
+    enc.layer = nn.ModuleList([mm3._TupleLayer(l) for l in enc._orig_layers])
+    return model
 
 
 def m3ae_config(drop_rate=0.0, image_size=288):
@@ -179,3 +231,20 @@ def m3ae_config(drop_rate=0.0, image_size=288):
         "loss_names": {"mlm": 0, "mim": 0, "itm": 0, "vqa": 1, "cls": 0, "irtr": 0}, "load_path": "", "test_only": False,
         "vqa_label_size": 498, "mim_prob": 0.75, "mim_layer": 3,
     }
+
+
+def load_decoder_model(tokenizer):
+    """Imports the reference's DecoderModel (m3ae_decoder.py:185-443) unmodified, wired to the real M3AETransformerSS class
+    (random-init real encoders, see load_m3ae_module) and to `tokenizer` in place of BertTokenizer.from_pretrained (:191;
+    the vocabulary file does not exist offline).  Returns the class."""
+    mm3, Cls = load_m3ae_module(real_encoders=True)
+    mods = sys.modules["m3ae.modules"]
+    mods.M3AETransformerSS = Cls
+    for sub in ("m3ae_t5_utils",):
+        sys.modules.pop(f"m3ae.modules.{sub}", None)
+        m = importlib.import_module(f"m3ae.modules.{sub}")
+        setattr(mods, sub, m)
+    sys.modules.pop("m3ae.modules.m3ae_decoder", None)
+    dec = importlib.import_module("m3ae.modules.m3ae_decoder")
+    dec.BertTokenizer = types.SimpleNamespace(from_pretrained=lambda *a, **k: tokenizer)
+    return dec.DecoderModel

@@ -1,0 +1,216 @@
+"""Drop-in behaviours around the fused layer node: lazy attention probabilities (the reference's fusion loop hard-wires
+output_attentions=True, m3ae_module.py:276-277), `patch_m3ae` on a reference-style model, inference forwards re-using the
+workspace and operand cache, the small head kernels (activation / BCE / cross-entropy)."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import m3ae_b200  # noqa: E402,F401
+from m3ae_b200 import functional as Fn, ops  # noqa: E402
+from m3ae_b200.bert_cross_layer import BertCrossLayer  # noqa: E402
+from m3ae_b200.m3ae_module import M3AEFusion, patch_m3ae, extended_attention_mask  # noqa: E402
+from oracle import m3ae_oracle as O  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def _cfg(drop=0.0):
+    from transformers import RobertaConfig
+    return RobertaConfig(vocab_size=50265, hidden_size=768, num_hidden_layers=6, num_attention_heads=12, intermediate_size=3072,
+                         max_position_embeddings=32, hidden_dropout_prob=drop, attention_probs_dropout_prob=drop)
+
+
+def test_lazy_probabilities_equal_oracle_and_cost_nothing_until_read():
+    sd = O.make_cross_layer_state(3)
+    layer = BertCrossLayer(_cfg(), torch.bfloat16).to(DEV).eval()
+    layer.load_state_dict(sd)
+    g = torch.Generator().manual_seed(4)
+    x, y = torch.randn(2, 32, 768, generator=g), torch.randn(2, 325, 768, generator=g)
+    mx = O.extended_attention_mask((torch.arange(32)[None] < torch.tensor([[20], [32]])).long())
+    my = O.extended_attention_mask(torch.ones(2, 325, dtype=torch.long))
+    with torch.no_grad():
+        layer(x.to(DEV), y.to(DEV), mx.to(DEV), my.to(DEV))  # first call casts the operand cache
+        n0 = ops.launch_count()
+        out_plain = layer(x.to(DEV), y.to(DEV), mx.to(DEV), my.to(DEV))
+        n_plain = ops.launch_count() - n0
+        n0 = ops.launch_count()
+        out = layer(x.to(DEV), y.to(DEV), mx.to(DEV), my.to(DEV), output_attentions=True)
+        n_lazy = ops.launch_count() - n0
+    assert len(out) == 3 and isinstance(out[1], Fn.LazyAttentionProbs)
+    assert n_lazy == n_plain, "output_attentions=True must not launch anything extra until the probabilities are read"
+    assert torch.equal(out[0], out_plain[0])
+    ro = O.bert_cross_layer(x, y, sd, "", mx, my)
+    assert out[1].shape == (2, 12, 32, 32) and out[2].shape == (2, 12, 32, 325)
+    assert rel(out[1], ro[1]) < 2e-2 and rel(out[2], ro[2]) < 2e-2
+    assert rel(torch.mean(out[2], dim=1), ro[2].mean(1)) < 2e-2        # torch functions see a tensor
+    assert rel(out[2][:, 0], ro[2][:, 0]) < 2e-2                        # and so does indexing
+    with torch.no_grad():
+        stale = layer(x.to(DEV), y.to(DEV), mx.to(DEV), my.to(DEV), output_attentions=True)
+        layer(x.to(DEV), y.to(DEV), mx.to(DEV), my.to(DEV))
+    with pytest.raises(RuntimeError, match="ran again"):
+        stale[1].materialize()
+
+
+class _RefStyleFusion(nn.Module):
+    """The fusion loop exactly as the reference writes it (m3ae_module.py:268-285): two separate layer calls per index,
+    output_attentions=True hard-wired, `[0]` and `[1:]` of the returned tuples."""
+
+    def __init__(self, layers_t, layers_i):
+        super().__init__()
+        self.multi_modal_language_layers, self.multi_modal_vision_layers = layers_t, layers_i
+
+    def forward(self, x, y, mx, my, output_attentions=False):
+        attns = {"text2image_attns": [], "image2text_attns": []}
+        for tl, il in zip(self.multi_modal_language_layers, self.multi_modal_vision_layers):
+            x1 = tl(x, y, mx, my, output_attentions=True)
+            y1 = il(y, x, my, mx, output_attentions=True)
+            x, y = x1[0], y1[0]
+            if output_attentions:
+                attns["text2image_attns"].append(x1[1:])
+                attns["image2text_attns"].append(y1[1:])
+        return x, y, attns
+
+
+def test_patch_m3ae_swaps_layers_in_a_reference_style_loop():
+    """INTEGRATION.md's 3-line integration: patch_m3ae(model) on a model holding reference-style BertCrossLayer modules
+    (here: parameter containers with the reference's attribute layout), driven by the reference's own loop."""
+    fusion = M3AEFusion({"drop_rate": 0.0}, compute_dtype=torch.bfloat16)
+    fusion.load_state_dict(O.make_fusion_state(21), strict=True)
+    fusion = fusion.to(DEV).eval()
+
+    class RefLayer(nn.Module):  # attribute layout of bert_model.BertCrossLayer (:445-455) — what patch_m3ae reads
+        def __init__(self, src):
+            super().__init__()
+            self.attention, self.crossattention = src.attention, src.crossattention
+            self.intermediate, self.output = src.intermediate, src.output
+
+        def forward(self, *a, **k):
+            raise AssertionError("the un-patched layer must not run")
+
+    tl = nn.ModuleList([RefLayer(l) for l in fusion.multi_modal_language_layers])
+    il = nn.ModuleList([RefLayer(l) for l in fusion.multi_modal_vision_layers])
+    model = _RefStyleFusion(tl, il).to(DEV).eval()
+    before = {n: p for n, p in model.named_parameters()}
+    patch_m3ae(model, torch.bfloat16)
+    after = {n: p for n, p in model.named_parameters()}
+    assert before.keys() == after.keys() and all(before[k] is after[k] for k in before), "Parameter objects must be re-used"
+    inp = O.make_fusion_inputs(22, B=2)
+    sd = O.make_fusion_state(21)
+    with torch.no_grad():
+        x = Fn.linear(inp["text_feats"].to(DEV), fusion.multi_modal_language_proj.weight, fusion.multi_modal_language_proj.bias,
+                      extra_bias=fusion.modality_type_embeddings.weight[0])
+        y = Fn.linear(inp["image_feats"].to(DEV), fusion.multi_modal_vision_proj.weight, fusion.multi_modal_vision_proj.bias,
+                      extra_bias=fusion.modality_type_embeddings.weight[1])
+        mx = extended_attention_mask(inp["text_masks"].to(DEV))
+        my = extended_attention_mask(torch.ones(2, 325, dtype=torch.long, device=DEV))
+        n0 = ops.launch_count()
+        xo, yo, _ = model(x, y, mx, my)
+        n_loop = ops.launch_count() - n0
+        xa, ya, att = model(x, y, mx, my, output_attentions=True)
+        ref = O.fusion_forward(inp["text_feats"], inp["image_feats"], inp["text_masks"], sd, output_attentions=True)
+    assert rel(xo, ref["multi_modal_text_feats"]) < 2e-2 and rel(yo, ref["multi_modal_image_feats"]) < 2e-2
+    assert torch.equal(xo, xa) and torch.equal(yo, ya)
+    assert len(att["text2image_attns"]) == 6 and len(att["image2text_attns"][5]) == 2
+    assert rel(att["image2text_attns"][5][1], ref["attentions"]["image2text_attns"][5][1]) < 2e-2
+    assert rel(att["text2image_attns"][5][0], ref["attentions"]["text2image_attns"][5][0]) < 2e-2
+    assert n_loop < 6 * 2 * 20, f"the patched loop launched {n_loop} kernels: the probability slow path is back"
+
+
+def test_no_grad_forwards_reuse_workspace_and_operand_cache():
+    """under torch.no_grad() the node must not treat the call as a training forward — no operand
+    re-cast, no new workspace — even though every parameter has requires_grad=True."""
+    layer = BertCrossLayer(_cfg(), torch.bfloat16).to(DEV).eval()
+    x, y = torch.randn(2, 32, 768, device=DEV), torch.randn(2, 325, 768, device=DEV)
+    with torch.no_grad():
+        layer(x, y)
+        ws = list(layer._operands.workspaces)
+        n0 = ops.launch_count()
+        a = layer(x, y)[0]
+        first = ops.launch_count() - n0
+        n0 = ops.launch_count()
+        b = layer(x, y)[0]
+        second = ops.launch_count() - n0
+    assert torch.equal(a, b)
+    assert len(layer._operands.workspaces) == 1 and layer._operands.workspaces[0] is ws[0], "eval forwards must re-use the workspace"
+    assert second == first, "consecutive eval forwards must launch the same kernels (no operand re-cast)"
+    with torch.no_grad():
+        layer(x, y)
+        n0 = ops.launch_count()
+        layer(x, y)
+        steady = ops.launch_count() - n0
+    # steady state: QKV, o1, xproj, o2, ffn1, ffn2 GEMMs + 2 attention + 3 LayerNorm + 2 input casts + 1 output cast
+    # (fp32 in / out around a bf16 layer), and NO cast_group launch
+    assert steady == second and steady <= 14, f"{steady} launches per eval forward"
+    layer.train()
+    out = layer(x.requires_grad_(True), y)[0]
+    out.float().mean().backward()
+    assert all(not w.busy for w in layer._operands.workspaces)
+
+
+@pytest.mark.parametrize("act", [ops.ACT_GELU, ops.ACT_TANH, ops.ACT_QUICKGELU, ops.ACT_RELU])
+def test_activation_kernels(act):
+    ref = {ops.ACT_GELU: torch.nn.functional.gelu, ops.ACT_TANH: torch.tanh, ops.ACT_RELU: torch.relu,
+           ops.ACT_QUICKGELU: lambda t: t * torch.sigmoid(1.702 * t)}[act]
+    x = (3 * torch.randn(64, 1536, device=DEV)).requires_grad_(True)
+    y = Fn.activation(x, act)
+    w = torch.randn_like(y)
+    (y * w).sum().backward()
+    xr = x.detach().clone().requires_grad_(True)
+    yr = ref(xr)
+    (yr * w).sum().backward()
+    assert rel(y, yr) < 1e-5 and rel(x.grad, xr.grad) < 1e-5
+
+
+def test_quick_gelu_gemm_epilogue_and_backward():
+    M, K, F = 650, 768, 3072
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(M, K, generator=g).to(DEV)
+    w0, b0 = (torch.randn(F, K, generator=g) * 0.03).to(DEV), (torch.randn(F, generator=g) * 0.02).to(DEV)
+    w2, b2 = (torch.randn(K, F, generator=g) * 0.03).to(DEV), (torch.randn(K, generator=g) * 0.02).to(DEV)
+    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 2e-2)):
+        ps = [t.clone().requires_grad_(True) for t in (x, w0, b0, w2, b2)]
+        y = Fn.ffn(ps[0].to(dtype), ps[1], ps[2], ps[3], ps[4], residual=ps[0].to(dtype), act=ops.ACT_QUICKGELU, dtype=dtype)
+        probe = torch.randn(M, K, generator=torch.Generator().manual_seed(2)).to(DEV)
+        (y.float() * probe).sum().backward()
+        rs = [t.clone().requires_grad_(True) for t in (x, w0, b0, w2, b2)]
+        h = rs[0] @ rs[1].t() + rs[2]
+        yr = (h * torch.sigmoid(1.702 * h)) @ rs[3].t() + rs[4] + rs[0]
+        (yr * probe).sum().backward()
+        assert rel(y, yr) < tol
+        for a, b in zip(ps, rs):
+            assert rel(a.grad, b.grad) < 2 * tol, (dtype, rel(a.grad, b.grad))
+
+
+def test_bce_and_cross_entropy_kernels_match_torch():
+    g = torch.Generator().manual_seed(3)
+    logits = (2 * torch.randn(64, 498, generator=g)).to(DEV).requires_grad_(True)
+    targets = (torch.rand(64, 498, generator=g) < 0.01).float().to(DEV)
+    loss = Fn.vqa_bce_loss(logits, targets)
+    (2.5 * loss).backward()
+    lr = logits.detach().clone().requires_grad_(True)
+    ref = torch.nn.functional.binary_cross_entropy_with_logits(lr, targets) * 498
+    (2.5 * ref).backward()
+    assert abs(loss.item() - ref.item()) / ref.item() < 1e-5 and rel(logits.grad, lr.grad) < 1e-5
+    V = 30522
+    lg = torch.randn(7, 5, V, generator=g).to(DEV).requires_grad_(True)
+    tg = torch.randint(1, V, (7, 5), generator=g)
+    tg[2, 3:] = 0
+    tg[5, 1:] = 0
+    tg = tg.to(DEV)
+    loss = Fn.cross_entropy(lg, tg, ignore_index=0)
+    loss.backward()
+    lr = lg.detach().clone().requires_grad_(True)
+    ref = nn.CrossEntropyLoss(ignore_index=0)(lr.transpose(1, 2), tg)   # the reference's call, m3ae_decoder.py:365
+    ref.backward()
+    assert abs(loss.item() - ref.item()) / ref.item() < 1e-5 and rel(lg.grad, lr.grad) < 1e-5
