@@ -7,11 +7,19 @@ One "step" = one fine-tune pass of the hot path over one synthetic batch of 64 s
 modality projections -> 6+6 co-attention layers (fwd) -> poolers -> vqa_head -> BCE loss -> backward through all of
 it -> (N>1: NCCL gradient all-reduce) -> AdamW step.  Dropout (p=0.1) is active as in the reference's fine-tune.
 `value` is samples/s with inputs resident in HBM; `e2e` re-measures the same step driven from pinned HOST buffers
-(H2D of the step's inputs + D2H of the loss inside the timed region).  `roofline` is the tcgen05 GEMM kernel
-(dominant kernel): algorithmic FLOPs of every GEMM launch in a step / summed CUDA-event durations, against the
-measured bf16 peak in MEASURED_PEAKS.json.  `cpu_baseline` / `--impl reference` time the oracle port of the
-reference's CPU path (the reference is pure Python+torch and cannot travel to the GPU box; oracle/m3ae_oracle.py is
-pinned to it by golden vectors) on the host cores.
+(H2D of every step's inputs — prefetched on a copy stream while the previous step runs — + D2H of the loss inside the
+timed region).  `roofline` is the tcgen05 GEMM kernel (dominant kernel): algorithmic FLOPs of every GEMM launch in a
+step / summed CUDA-event durations, against the measured bf16 peak in MEASURED_PEAKS.json.
+`cpu_baseline` / `--impl reference` time the REFERENCE'S OWN modules (oracle/_ref: a git-ignored snapshot of
+<reference>/m3ae/modules made by oracle/snapshot_ref.py, imported through oracle/ref_shim.py; kind "reference") on the
+box's host cores — M3AETransformerSS.infer's fusion section + vqa_head + BCE + backward + AdamW on a bounded sample —
+or, when the snapshot is absent, the oracle port (kind "port").  Both legs use ONE definition of the CPU step.
+
+At N = 1 the same JSON line also carries:
+  "decoder"                BASELINE config 3: greedy decode of 16 tokens, batch 128 (roofline vs HBM, e2e, cpu_baseline =
+                           the reference Decoder.search_path at batch 16)
+  "whole_step"             config 2 with the uni-modal encoders included (CLIP ViT-B/16 + RoBERTa-base on the same kernels)
+  "classifier_forward_b8"  config 1: infer + vqa_head at batch 8, next to the reference's CPU fp32 time
 """
 import argparse
 import json
@@ -95,6 +103,158 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
 
 
+# ----------------------------------------------------------------------------- CPU legs: the reference's own code
+class _Tok:
+    cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
+
+
+def _ref_available():
+    from oracle import ref_shim
+    return ref_shim.available()
+
+
+def reference_fusion_stepper(B, dropout_p=0.1, with_optimizer=True):
+    """One fine-tune step of the hot path on the host cores.  Returns (step_fn, kind, description).
+    kind "reference": the reference's own M3AETransformerSS (m3ae_module.py:203-312 fusion section, uni-modal encoder
+    outputs plugged in as constants) + vqa_head + BCE (objectives.py:201) + backward + AdamW(eps 1e-8, betas (0.9, 0.98)),
+    imported from oracle/_ref (or /root/reference) through oracle/ref_shim.py.  kind "port": oracle/m3ae_oracle.py."""
+    from oracle import m3ae_oracle as O
+    inp = O.make_fusion_inputs(1, B=B)
+    if _ref_available():
+        from oracle import ref_shim
+        mm3, Cls = ref_shim.load_m3ae_module()
+        torch.manual_seed(0)
+        model = Cls(ref_shim.m3ae_config(drop_rate=dropout_p)).train()
+        model.load_state_dict(O.make_fusion_state(0), strict=False)
+
+        class Const(torch.nn.Module):
+            def __init__(self, value):
+                super().__init__()
+                self.value = value
+
+            def forward(self, *a, **k):
+                return self.value
+
+        model.language_encoder.embeddings = Const(inp["text_feats"])
+        model.vision_encoder = Const(inp["image_feats"])
+        batch = {"image": [torch.zeros(B, 3, 288, 288)], "text_ids": torch.zeros(B, 32, dtype=torch.long),
+                 "text_labels": torch.full((B, 32), -100), "text_masks": inp["text_masks"]}
+        params = [p for p in model.parameters() if p.requires_grad]
+        opt = torch.optim.AdamW(params, lr=5e-6, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01) if with_optimizer else None
+
+        def step():
+            for p in params:
+                p.grad = None
+            ret = model.infer(batch)
+            logits = model.vqa_head(ret["multi_modal_cls_feats"])
+            loss = torch.nn.functional.binary_cross_entropy_with_logits(logits, inp["targets"]) * inp["targets"].shape[1]
+            loss.backward()
+            if opt is not None:
+                opt.step()
+
+        return step, "reference", "the reference's own M3AETransformerSS fusion section + vqa_head + BCE (oracle/_ref via oracle/ref_shim.py)"
+    sd = {k: v.clone().requires_grad_(True) for k, v in O.make_fusion_state(0).items()}
+    opt = torch.optim.AdamW(list(sd.values()), lr=5e-6, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01) if with_optimizer else None
+
+    def step():
+        for v in sd.values():
+            v.grad = None
+        loss, _, _ = O.finetune_step(inp["text_feats"], inp["image_feats"], inp["text_masks"], inp["targets"], sd,
+                                     dropout_p=dropout_p, training=True)
+        loss.backward()
+        if opt is not None:
+            opt.step()
+
+    return step, "port", "oracle port (oracle/m3ae_oracle.py; no reference snapshot on this box)"
+
+
+def cpu_baseline(sample_b=8, steps=3, threads=None):
+    """The CPU step of `--impl reference` (same definition, same code) timed inside the `ours` run."""
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    step, kind, what = reference_fusion_stepper(sample_b)
+    step()
+    best = 1e9
+    for _ in range(steps):
+        t = time.perf_counter()
+        step()
+        best = min(best, time.perf_counter() - t)
+    return {"value": round(sample_b / best, 3), "unit": "samples/s", "cores": threads, "kind": kind,
+            "sample": f"batch {sample_b} (of 64), fwd+bwd+AdamW fp32, dropout 0.1, best of {steps} after 1 warm-up; {what}"}
+
+
+def cpu_decoder_baseline(B=16, L=16, Lm=359, threads=None):
+    """Reference Decoder(max_len=16).search_path (m3ae_decoder.py:141-182: whole-prefix re-run, 6 layers, no cache) at batch B."""
+    from oracle import m3ae_oracle as O
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    mem = torch.randn(B, Lm, 768, generator=torch.Generator().manual_seed(3))
+    sd = O.make_decoder_state(31)
+    if _ref_available():
+        from oracle import ref_shim
+        ref = ref_shim.load()
+        dec = ref.Decoder(6, 768, 8, 3072, 0.1, L, 30522).eval()
+        dec.load_state_dict(sd, strict=True)
+        kind, what = "reference", "the reference's own Decoder.search_path (oracle/_ref)"
+
+        def run():
+            with torch.no_grad():
+                return dec.search_path(mem, _Tok)
+    else:
+        kind, what = "port", "oracle port of Decoder.search_path, all 6 layers evaluated as the reference does"
+
+        def run():
+            with torch.no_grad():
+                return O.search_path(mem, sd, L, all_layers=True)
+    t = time.perf_counter()
+    run()
+    dt = time.perf_counter() - t
+    return {"value": round(B / dt, 3), "unit": "samples/s", "cores": threads, "kind": kind,
+            "sample": f"batch {B} (of 128), {L} tokens, memory {Lm} tokens, fp32, one run; {what}"}
+
+
+def cpu_config1_baseline(B=8, threads=None):
+    """BASELINE config 1 as written: the reference's real M3AETransformerSS (its CLIP ViT-B/16 class + random-init HF
+    RobertaModel + fusion + vqa_head), infer + vqa_head, eval, CPU fp32, batch 8."""
+    if not _ref_available():
+        return None
+    from oracle import m3ae_oracle as O
+    from oracle import ref_shim
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    mm3, Cls = ref_shim.load_m3ae_module(real_encoders=True)
+    torch.manual_seed(0)
+    model = Cls(ref_shim.m3ae_config()).eval()
+    O.seed_model_parameters(model, 5)
+    ref_shim.wrap_text_layers(model)
+    batch = O.make_model_batch(51, B)
+
+    def run():
+        with torch.no_grad():
+            return model.vqa_head(model.infer(batch)["multi_modal_cls_feats"])
+
+    run()
+    best = 1e9
+    for _ in range(2):
+        t = time.perf_counter()
+        run()
+        best = min(best, time.perf_counter() - t)
+    return {"value": round(B / best, 3), "unit": "samples/s", "cores": threads, "kind": "reference", "ms": round(best * 1e3, 1),
+            "sample": f"batch {B}, infer + vqa_head, eval, fp32, best of 2 after 1 warm-up; the reference's own M3AETransformerSS with its CLIP class + random-init HF RobertaModel"}
+
+
+# ----------------------------------------------------------------------------- GPU legs
+def _event_time(fn, n, sync):
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        fn(i)
+    e1.record()
+    sync()
+    return e0.elapsed_time(e1)
+
+
 def run_ours(args):
     import torch.distributed as dist
 
@@ -122,6 +282,8 @@ def run_ours(args):
     # M3AE_BENCH_FORCE_REDUCER=1: diagnostic — run the N>1 gradient bookkeeping (bucket views, accumulate, zero) on one GPU
     force_reducer = os.environ.get("M3AE_BENCH_FORCE_REDUCER", "0") == "1"
     reducer = GradientAllReducer(params, world) if (world > 1 or force_reducer) else None
+    if reducer is not None:
+        reducer.broadcast_parameters(0)
 
     def step(b):
         if reducer is not None:
@@ -155,6 +317,38 @@ def run_ours(args):
             ms = t.item()
         return ms
 
+    # ---- N > 1: numeric check of the gradient exchange on the GPUs (dropout off): the reducer's averaged gradients of the
+    # per-rank batches must equal the gradient of the concatenated batch computed locally without any exchange.
+    grad_check = None
+    if world > 1:
+        model.eval()
+        gb = 4
+        allb = [synth_batch(gb, dev, 500 + r) for r in range(world)]
+        reducer.zero_grad()
+        loss, _, _ = model.vqa_loss_from_feats(allb[rank]["text"], allb[rank]["image"], allb[rank]["masks"], allb[rank]["targets"])
+        loss.backward()
+        reducer.wait()
+        torch.cuda.synchronize()
+        got = [p.grad.detach().float().clone() for p in params]
+        for p in params:
+            p.grad = None
+        cat = {k: torch.cat([b[k] for b in allb]) for k in allb[0]}
+        loss, _, _ = model.vqa_loss_from_feats(cat["text"], cat["image"], cat["masks"], cat["targets"])
+        loss.backward()
+        torch.cuda.synchronize()
+        num = torch.sqrt(sum(((g - p.grad.float()) ** 2).sum() for g, p in zip(got, params)))
+        den = torch.sqrt(sum((p.grad.float() ** 2).sum() for p in params))
+        err = torch.tensor([(num / den).item()], device=dev)
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        grad_check = {"rel_err_vs_whole_batch": round(err.item(), 6), "per_rank_batch": gb, "gate": 2e-2,
+                      "what": "||avg-reduced grads of per-rank batches - local grads of the concatenated batch|| / ||.||, all parameters, max over ranks, dropout off, bf16"}
+        if not err.item() < 2e-2:
+            raise RuntimeError(f"gradient exchange check failed: {grad_check}")
+        for p in params:
+            p.grad = None
+        reducer.zero_grad()
+        model.train()
+
     # ---- device-resident throughput
     batches = [synth_batch(B, dev, 1000 + rank * 100 + i) for i in range(2)]
     for i in range(max(args.warmup, 3)):
@@ -173,18 +367,42 @@ def run_ours(args):
         host_issue.append((time.perf_counter() - t0) * 1e3)
     torch.cuda.synchronize()
     host_issue_ms = min(host_issue)
-    # ---- end-to-end: pinned host inputs -> H2D -> step -> loss D2H, every step
+    # ---- end-to-end: pinned host inputs -> H2D -> step -> loss D2H, every step.  The H2D of step i+1 is issued on a
+    # copy stream while step i runs (double-buffered device inputs); every step's copy is inside the timed region.
     host = [synth_batch(B, dev, 2000 + rank * 100 + i, pin=True) for i in range(2)]
     h2d_bytes = sum(v.numel() * v.element_size() for v in host[0].values())
     loss_host = torch.zeros((), pin_memory=True)
+    copy_stream = torch.cuda.Stream()
+    dbuf = [{k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in host[0].items()} for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def prefetch(i):
+        s = i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[s])  # the step that last read this slot has finished
+            for k, v in host[i % 2].items():
+                dbuf[s][k].copy_(v, non_blocking=True)
+            ready[s].record(copy_stream)
 
     def e2e_step(i):
-        b = {k: v.to(dev, non_blocking=True) for k, v in host[i % 2].items()}
-        loss = step(b)
+        s = i % 2
+        if i == 0:
+            prefetch(0)
+        prefetch(i + 1)  # next step's inputs travel while this step computes
+        torch.cuda.current_stream().wait_event(ready[s])
+        loss = step(dbuf[s])
+        consumed[s].record()
         loss_host.copy_(loss.detach(), non_blocking=False)  # D2H read of the step's result (synchronises)
 
+    for ev in consumed:
+        ev.record()
     e2e_step(0)
+    torch.cuda.synchronize()
+    for ev in consumed:
+        ev.record()
     ms_e2e = timed(e2e_step, args.steps)
+    torch.cuda.synchronize()
     if sampler:
         sampler.stop_flag = True
         sampler.join(timeout=2)
@@ -237,6 +455,7 @@ def run_ours(args):
         if not (in_sync and moved):
             raise RuntimeError(f"data-parallel replicas diverged or did not train (in_sync={in_sync}, moved={moved}): the gradient exchange is broken")
 
+    line = None
     if rank == 0:
         pk = peaks()
         sps = world * B * args.steps / (ms / 1e3)
@@ -254,9 +473,10 @@ def run_ours(args):
                        "l2": "no explicit flush: per-step working set (>4 GB of activations + 0.7 GB weights) far exceeds the 126 MB L2"},
             "clocks": sampler.summary() if sampler else None,
             "e2e": {"value": round(sps_e2e, 2), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
-                    "ms_per_step": round(ms_e2e / args.steps, 3)},
+                    "ms_per_step": round(ms_e2e / args.steps, 3),
+                    "how": "pinned host inputs, H2D of step i+1 on a copy stream during step i (double-buffered), loss read back every step"},
             "gpu_launches": int(launches), "host_issue_ms_per_step": round(host_issue_ms, 3),
-            "replicas_in_sync": in_sync,
+            "replicas_in_sync": in_sync, "grad_check": grad_check,
             "roofline": {"bound": "tensor", "achieved": round(achieved, 1) if achieved else None, "peak": pk["tflops"], "unit": "TFLOP/s",
                          "frac": round(achieved / pk["tflops"], 4) if achieved else None, "traffic": gemm_traffic()[0],
                          "traffic_source": gemm_traffic()[1],
@@ -265,6 +485,17 @@ def run_ours(args):
             "fusion_stack_tflops": round(stack_tflops, 1),
             "fusion_stack_frac_of_peak": round(stack_tflops / pk["tflops"], 4),
         }
+    # free the fusion model before the other workloads
+    del model, opt, params, batches, host, dbuf, reducer
+    torch.cuda.empty_cache()
+    if rank == 0 and world == 1 and not args.fusion_only:
+        line["decoder"] = bench_decoder(args, dev)
+        torch.cuda.empty_cache()
+        line["whole_step"] = bench_whole_step(args, dev)
+        torch.cuda.empty_cache()
+        line["classifier_forward_b8"] = bench_config1(args, dev)
+        torch.cuda.empty_cache()
+    if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(sample_b=8, steps=3)
         print(json.dumps(line), flush=True)
@@ -272,36 +503,35 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def run_decoder(args):
+def bench_decoder(args, dev):
     """BASELINE config 3: generative decoder head, greedy decode of up to 16 answer tokens, batch 128 (forward only,
     replicas only -> single GPU).  HBM-bound: per step the live layer's weights (18.9 MB bf16), the vocab projection
     (46.9 MB) and the cross K/V cache (B*359*1536*2 B = 141 MB) are streamed once."""
-    import m3ae_b200  # noqa: F401
     from m3ae_b200 import ops
     from m3ae_b200.decoder import Decoder
-    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
-    torch.cuda.set_device(dev)
     B, Lm, L = 128, 359, 16
     torch.manual_seed(0)
     dec = Decoder(6, 768, 8, 3072, 0.1, L, 30522, compute_dtype=torch.bfloat16).to(dev).eval()
-
-    class Tok:
-        cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
-
     g = torch.Generator().manual_seed(3)
     mems = [torch.randn(B, Lm, 768, generator=g).to(dev) for _ in range(2)]
+    steps = max(5, min(args.steps, 20))
     for i in range(max(args.warmup, 3)):
-        dec.search_path(mems[i % 2], Tok)
+        dec.search_path(mems[i % 2], _Tok)
     torch.cuda.synchronize()
     l0, g0 = ops.launch_count(), dec.graph_replayed_launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        ids = dec.search_path(mems[i % 2], Tok)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / args.steps
+    ms = _event_time(lambda i: dec.search_path(mems[i % 2], _Tok), steps, torch.cuda.synchronize) / steps
     launches = (ops.launch_count() - l0) + (dec.graph_replayed_launches - g0)  # eager calls + kernels replayed from the CUDA graph
+    # end to end: memory from pinned host fp32 -> H2D -> greedy program -> ids back on the host
+    hmem = [torch.randn(B, Lm, 768, generator=g).pin_memory() for _ in range(2)]
+    dmem = torch.empty(B, Lm, 768, device=dev)
+    ids_host = torch.empty(B, L, dtype=torch.int64).pin_memory()
+
+    def e2e(i):
+        dmem.copy_(hmem[i % 2], non_blocking=True)
+        ids_host.copy_(dec.search_path(dmem, _Tok), non_blocking=False)
+
+    e2e(0)
+    ms_e2e = _event_time(e2e, steps, torch.cuda.synchronize) / steps
     pk = peaks()
     # algorithmic bytes per greedy step (bf16): live layer weights + vocab projection + cross K/V cache + self K/V cache
     w_bytes = (3 * 768 * 768 + 768 * 768 + 768 * 768 + 768 * 768 + 2 * 768 * 3072 + 30522 * 768) * 2
@@ -309,42 +539,89 @@ def run_decoder(args):
     step_bytes = w_bytes + kv_bytes + B * 8 * 1536 * 2  # + average self cache (8 of 16 positions)
     one_off = B * Lm * 768 * 4 + B * Lm * 768 * 2 * 2 + 1536 * 768 * 2  # memory read (fp32) + cast + cross K/V projection
     achieved = (L * step_bytes + one_off) / (ms * 1e-3) / 1e9
-    line = {"metric": "greedy-decoded samples/sec (M3AE generative decoder head, <=16 tokens)", "value": round(B / (ms * 1e-3), 1),
-            "unit": "samples/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 3),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic (seeded memory [128,359,768], random-init weights)",
-            "config": {"workload": "M3AE generative decoder head greedy decode, 16 tokens, batch 128, memory 359 tokens (KV-cached, live layer only)",
-                       "tokens_per_s": round(B * L / (ms * 1e-3), 1), "us_per_token_step": round(ms * 1e3 / L, 1)},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": None,
-                         "how": "algorithmic bytes per greedy step (weights 65.8 MB + cross K/V 141 MB + self K/V) x 16 + one-off memory projection, / CUDA-event time of search_path"}}
-    print(json.dumps(line), flush=True)
+    out = {"metric": "greedy-decoded samples/sec (M3AE generative decoder head, <=16 tokens)", "value": round(B / (ms * 1e-3), 1),
+           "unit": "samples/s", "n_gpus": 1, "steps": steps, "ms_per_step": round(ms, 3), "dtype": "bf16",
+           "config": {"workload": "M3AE generative decoder head (main_decoder_m3ae) greedy decode, 16 tokens, batch 128, memory 359 tokens (KV-cached, live layer only)",
+                      "tokens_per_s": round(B * L / (ms * 1e-3), 1), "us_per_token_step": round(ms * 1e3 / L, 1)},
+           "gpu_launches": int(launches),
+           "e2e": {"value": round(B / (ms_e2e * 1e-3), 1), "unit": "samples/s", "h2d_bytes_per_step": B * Lm * 768 * 4,
+                   "d2h_bytes_per_step": B * L * 8, "ms_per_step": round(ms_e2e, 3)},
+           "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                        "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": None,
+                        "how": "algorithmic bytes per greedy step (weights 65.8 MB + cross K/V 141 MB + self K/V) x 16 + one-off memory projection, / CUDA-event time of search_path"}}
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_decoder_baseline()
+    del dec, mems
+    return out
 
 
-def cpu_baseline(sample_b=8, steps=3, threads=None):
-    """Oracle port of the reference CPU path (fusion fwd + vqa head + BCE + backward through everything) on the host."""
-    from oracle import m3ae_oracle as O
-    threads = threads or os.cpu_count()
-    torch.set_num_threads(threads)
-    sd = {k: v.clone().requires_grad_(True) for k, v in O.make_fusion_state(0).items()}
-    inp = O.make_fusion_inputs(1, B=sample_b)
+def bench_whole_step(args, dev):
+    """BASELINE config 2 with the uni-modal encoders inside the step: M3AETransformerSS.training_step (CLIP ViT-B/16 +
+    RoBERTa-base + fusion + vqa_head + BCE) -> backward -> AdamW over all trainable parameters, batch 64, bf16, dropout 0.1.
+    Algorithmic work 309.7 GFLOP per sample fwd+bwd."""
+    from m3ae_b200.m3ae_module import M3AETransformerSS
+    from oracle import m3ae_oracle as O  # synthetic batch-dict generator only
+    B = args.batch
+    torch.manual_seed(0)
+    model = M3AETransformerSS({"drop_rate": 0.1}, compute_dtype=torch.bfloat16).to(dev).train()
+    opt = torch.optim.AdamW([p for p in model.parameters()], lr=1e-5, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01, fused=True)
+    batches = [O.make_model_batch(70 + i, B, device=dev) for i in range(2)]
 
-    def one():
-        for v in sd.values():
-            v.grad = None
-        loss, _, _ = O.finetune_step(inp["text_feats"], inp["image_feats"], inp["text_masks"], inp["targets"], sd,
-                                     dropout_p=0.1, training=True)
+    def step(i):
+        opt.zero_grad(set_to_none=True)
+        loss = model.training_step(batches[i % 2], i)
         loss.backward()
+        opt.step()
 
-    one()
-    best = 1e9
-    for _ in range(steps):
-        t = time.perf_counter()
-        one()
-        best = min(best, time.perf_counter() - t)
-    return {"value": round(sample_b / best, 3), "unit": "samples/s", "cores": threads, "kind": "port",
-            "sample": f"batch {sample_b} (of 64), fwd+bwd fp32 with dropout 0.1, no optimizer step, best of {steps} after 1 warm-up; torch CPU ops via oracle/m3ae_oracle.py"}
+    for i in range(3):
+        step(i)
+    steps = max(3, min(args.steps, 10))
+    ms = _event_time(step, steps, torch.cuda.synchronize) / steps
+    pk = peaks()
+    tf = B / (ms * 1e-3) * 309.7e9 / 1e12
+    out = {"metric": "fine-tune samples/sec (whole M3AE: CLIP ViT-B/16 + RoBERTa-base + fusion + vqa_head, fwd+bwd+AdamW)",
+           "value": round(B / (ms * 1e-3), 1), "unit": "samples/s", "ms_per_step": round(ms, 3), "steps": steps, "dtype": "bf16",
+           "config": {"workload": "M3AETransformerSS.training_step on a synthetic batch dict (images 288x288, 32 tokens), batch 64, dropout 0.1, AdamW(fused) over all 322 M parameters"},
+           "model_tflops": round(tf, 1), "frac_of_peak": round(tf / pk["tflops"], 4),
+           "how": "CUDA events around K steps; 309.7 GFLOP per sample fwd+bwd (ViT 54.56 + RoBERTa 5.47 + fusion 42.78 + heads 0.43, x3)"}
+    del model, opt, batches
+    return out
+
+
+def bench_config1(args, dev):
+    """BASELINE config 1: classifier forward (infer + vqa_head), batch 8, 288 px / 32 tokens, eval.  GPU bf16 through the
+    drop-in next to the reference's CPU fp32 time (parity of this exact configuration: tests/test_full_model_gpu.py)."""
+    from m3ae_b200.m3ae_module import M3AETransformerSS
+    from oracle import m3ae_oracle as O
+    torch.manual_seed(0)
+    model = M3AETransformerSS({"drop_rate": 0.0}, compute_dtype=torch.bfloat16)
+    O.seed_model_parameters(model, 5)
+    model = model.to(dev).eval()
+    batch = O.make_model_batch(51, 8, device=dev)
+
+    def run(i):
+        with torch.no_grad():
+            return model.vqa_head(model.infer(batch)["multi_modal_cls_feats"])
+
+    for i in range(3):
+        run(i)
+    ms = _event_time(run, 20, torch.cuda.synchronize) / 20
+    out = {"metric": "classifier forward samples/sec (infer + vqa_head, batch 8)", "value": round(8 / (ms * 1e-3), 1), "unit": "samples/s",
+           "ms_per_forward": round(ms, 3), "dtype": "bf16", "model_tflops": round(8 / (ms * 1e-3) * 103.24e9 / 1e12, 1)}
+    del model
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_config1_baseline()
+    return out
+
+
+def run_decoder(args):
+    import m3ae_b200  # noqa: F401
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    out = bench_decoder(args, dev)
+    out.update({"warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "data": "synthetic (seeded memory [128,359,768], random-init weights)"})
+    print(json.dumps(out), flush=True)
 
 
 def run_reference(args):
@@ -353,35 +630,25 @@ def run_reference(args):
         return
     B = 8
     steps = max(1, min(args.steps, 5))
-    from oracle import m3ae_oracle as O
     threads = os.cpu_count()
     torch.set_num_threads(threads)
-    sd = {k: v.clone().requires_grad_(True) for k, v in O.make_fusion_state(0).items()}
-    opt = torch.optim.AdamW(list(sd.values()), lr=5e-6, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01)
-    inp = O.make_fusion_inputs(1, B=B)
-
-    def one():
-        opt.zero_grad(set_to_none=True)
-        loss, _, _ = O.finetune_step(inp["text_feats"], inp["image_feats"], inp["text_masks"], inp["targets"], sd,
-                                     dropout_p=0.1, training=True)
-        loss.backward()
-        opt.step()
-
-    for _ in range(max(1, min(args.warmup, 2))):
+    one, kind, what = reference_fusion_stepper(B)
+    warm = max(1, min(args.warmup, 2))
+    for _ in range(warm):
         one()
     t = time.perf_counter()
     for _ in range(steps):
         one()
     dt = time.perf_counter() - t
     sps = B * steps / dt
-    sample = f"bounded sample: batch {B} (of 64) x {steps} steps, fp32, dropout 0.1, AdamW step included, {threads} host threads; oracle port (reference is pure Python/torch and absent on this box)"
+    sample = f"bounded sample: batch {B} (of 64) x {steps} steps, fp32, dropout 0.1, AdamW step included, {threads} host threads; {what}"
     print(json.dumps({
         "impl": "reference", "metric": "fine-tune samples/sec (M3AE fusion-stack fine-tune step, fwd+bwd+AdamW)",
-        "value": round(sps, 3), "unit": "samples/s", "n_gpus": args.gpus, "steps": steps, "warmup": max(1, min(args.warmup, 2)),
+        "value": round(sps, 3), "unit": "samples/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": round(dt / steps * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic (seeded uni-modal features 288px/32tok, random-init weights)",
         "config": {"workload": "M3AE VQA-RAD fine-tune step (fwd+bwd), fusion stack 6+6 BertCrossLayer + heads + BCE, 288px / 32 tokens", "per_gpu_batch": B},
-        "cpu_baseline": {"value": round(sps, 3), "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": round(sps, 3), "unit": "samples/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": round(sps, 3), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
@@ -395,18 +662,19 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="per-GPU batch (BASELINE config[1]: 64)")
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fusion-only", action="store_true", help="skip the decoder / whole-step / config-1 objects of the N=1 line")
     ap.add_argument("--watchdog", type=int, default=1500,
                     help="seconds after which a stuck rank dumps every thread's Python stack to stderr and exits 1 (0 = off)")
     ap.add_argument("--workload", default="finetune", choices=["finetune", "decoder"],
-                    help="finetune = BASELINE config[1] (default, the headline); decoder = config[2] greedy decoding")
+                    help="finetune = BASELINE config[1] (default, the headline); decoder = config[2] greedy decoding only")
     args = ap.parse_args()
     if args.watchdog > 0:  # a hung collective or kernel must fail loudly, not hang the caller
         import faulthandler
         faulthandler.dump_traceback_later(args.watchdog, exit=True)
-    if args.workload == "decoder":
-        run_decoder(args)
-    elif args.impl == "reference":
+    if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "decoder":
+        run_decoder(args)
     else:
         run_ours(args)
 
