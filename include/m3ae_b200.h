@@ -92,6 +92,8 @@ typedef struct m3ae_gemm_epilogue_t {
   uint32_t* drop_bits;  /* optional (drop_p > 0, N % 32 == 0, tcgen05 backend): keep bits of the dropout, one uint32 per
                          * (row, 32 columns) at drop_bits[row * (N/32) + col/32], bit j = column col+j kept.  Handed to
                          * m3ae_layernorm_bwd so that backward does not regenerate the Philox stream. */
+  int32_t drop_bits_ready; /* 1: drop_bits already holds this site's keep bits (m3ae_dropout_bits): the epilogue READS them
+                            * instead of evaluating Philox (same bits, by construction); 0: the epilogue writes them */
 } m3ae_gemm_epilogue_t;
 
 typedef struct m3ae_gemm_problem_t {
@@ -146,6 +148,7 @@ typedef struct m3ae_attn_params_t {
   /* optional dropout keep-bit cache [B,H,Lq, 8*ceil(Lk/64)] bytes (bit k%8 of byte k/8 = key k kept): the tensor-core
    * forward writes it, the tensor-core backward reads it instead of re-evaluating Philox.  NULL: bits are recomputed. */
   uint8_t* drop_mask;
+  int32_t drop_mask_ready; /* 1: drop_mask was filled by m3ae_dropout_bits: the tensor-core forward reads it too */
 } m3ae_attn_params_t;
 
 int m3ae_attn_fwd(const m3ae_attn_params_t* p, void* stream);
@@ -211,6 +214,25 @@ int m3ae_cast_group(const m3ae_cast_item_t* items, int32_t n, void* stream);
 /* out[r, :] = a[r, :] + b[:]  (row-broadcast add; modality type embedding, m3ae_module.py:260-263). */
 int m3ae_add_rowvec(const void* a, const float* b, void* out, int64_t M, int32_t N, int32_t in_dtype, int32_t out_dtype,
                     void* stream);
+
+/* Keep bits of up to M3AE_MAX_DROPBITS dropout sites in ONE streaming launch, ahead of the kernels that apply them: the
+ * Philox4x32-7 evaluations (the same counters the kernels would use, so the bits are identical) leave the issue-bound
+ * element-wise phases of the attention kernels and the GEMM epilogues (bert_model.py:334 attention-probability dropout,
+ * :362,:440 hidden dropouts).
+ *   kind 0 (attention): out = drop_mask of m3ae_attn_params_t, rows = B*H*Lq, n = Lk, ld unused
+ *   kind 1 (hidden):    out = drop_bits of m3ae_gemm_epilogue_t, rows = M, n = N (N % 32 == 0), ld = the GEMM's ldo */
+#define M3AE_MAX_DROPBITS 12
+typedef struct m3ae_dropbits_item {
+  void* out;
+  int64_t rows;
+  int64_t ld;
+  int32_t n;
+  int32_t kind;
+  float p;
+  uint64_t seed;
+  uint64_t site; /* drop_stream of the consuming kernel */
+} m3ae_dropbits_item_t;
+int m3ae_dropout_bits(const m3ae_dropbits_item_t* items, int32_t n_items, void* stream);
 
 /* In-place dropout-scale of a gradient: x[i] = keep(i) ? x[i]/(1-p) : 0 with the same Philox stream the
  * forward GEMM epilogue used (element index = row*ld+col). */

@@ -25,7 +25,7 @@ class GemmEpilogue(C.Structure):
         ("residual", C.c_void_p), ("res_dtype", C.c_int32), ("ldr", C.c_int64),
         ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_stream", C.c_uint64),
         ("accumulate", C.c_int32), ("alpha", C.c_float), ("aux_is_grad", C.c_int32),
-        ("drop_bits", C.c_void_p),
+        ("drop_bits", C.c_void_p), ("drop_bits_ready", C.c_int32),
     ]
 
 
@@ -57,8 +57,16 @@ class AttnParams(C.Structure):
         ("dtype", C.c_int32),
         ("dout", C.c_void_p), ("dq", C.c_void_p), ("dk", C.c_void_p), ("dv", C.c_void_p),
         ("lddq", C.c_int64), ("lddk", C.c_int64), ("lddv", C.c_int64),
-        ("delta", C.c_void_p), ("drop_mask", C.c_void_p),
+        ("delta", C.c_void_p), ("drop_mask", C.c_void_p), ("drop_mask_ready", C.c_int32),
     ]
+
+
+class DropBitsItem(C.Structure):
+    _fields_ = [("out", C.c_void_p), ("rows", C.c_int64), ("ld", C.c_int64), ("n", C.c_int32), ("kind", C.c_int32),
+                ("p", C.c_float), ("seed", C.c_uint64), ("site", C.c_uint64)]
+
+
+MAX_DROPBITS = 12
 
 
 # name -> (restype, argtypes); must list every symbol include/m3ae_b200.h declares (tests check this).
@@ -76,6 +84,7 @@ SIGNATURES = {
                                        C.c_void_p]),
     "m3ae_cross_entropy": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                      C.c_int64, C.c_int32, C.c_int64, C.c_void_p]),
+    "m3ae_dropout_bits": (C.c_int, [C.POINTER(DropBitsItem), C.c_int32, C.c_void_p]),
     "m3ae_layernorm_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p]),
     "m3ae_layernorm_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

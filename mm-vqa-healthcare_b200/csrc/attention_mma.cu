@@ -137,7 +137,10 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
     load_tile<BN, NT>(sK, K, P.ldk, k0, P.Lk, tid);
     load_tile<BN, NT>(sV, V, P.ldv, k0, P.Lk, tid);
     for (int i = tid; i < BN; i += NT) sMask[i] = (k0 + i < P.Lk) ? (mask ? mask[k0 + i] : 0.f) : -INFINITY;
-    if (drop) gen_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid, P.drop_mask != nullptr);
+    if (drop) {
+      if (P.drop_mask != nullptr && P.drop_mask_ready) load_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid);  // pre-generated
+      else gen_keep_tile<BM, NJ, NT>(sBits, P, b, h, q0, k0, tid, P.drop_mask != nullptr);
+    }
     __syncthreads();
 
     float s[NJ][4];

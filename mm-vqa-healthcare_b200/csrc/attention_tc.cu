@@ -44,7 +44,7 @@ constexpr int KT = 64;           // backward key tile
 constexpr int BLK = TQ * 128;    // one [128 rows][64 bf16] swizzled block (16 KB)
 constexpr int KBLK = KT * 128;   // one backward K / V tile (8 KB)
 constexpr int FWD_EW = 16;       // forward element-wise warps
-constexpr int BWD_EW = 8;        // backward element-wise warps
+constexpr int BWD_EW = 16;       // backward element-wise warps (4 TMEM lane quadrants x 4 groups of 16 key columns)
 constexpr int NT_FWD = (FWD_EW + 1) * 32;
 constexpr int NT_BWD = (BWD_EW + 1) * 32;
 constexpr int HELD = 6;          // forward: 8-key units of a thread's row share that stay in registers (the rest: TMEM, read twice)
@@ -188,6 +188,13 @@ __device__ __forceinline__ float4 lds128f(uint32_t addr) {
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ uint32_t lds8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+// bits 0 / 1 of b -> 0xFFFF in the low / high half of a bf16x2 lane mask
+__device__ __forceinline__ uint32_t pair_mask(uint32_t b) { return (b & 1u) * 0xFFFFu + (b & 2u) * 0x7FFF8000u; }
 // lane mask of a flag word (bit 15 / bit 31 -> 0xFFFF in the low / high half)
 __device__ __forceinline__ uint32_t flag_lanes(uint32_t f) { return (f >> 15) * 0xFFFFu; }
 
@@ -209,7 +216,8 @@ __device__ __forceinline__ float fwd_unit_max(const uint32_t (&v)[8], bool plain
 // exp2, dropout, bf16 pack and the swizzled 16-byte store of one 8-key unit; returns the unit's (pre-dropout) row sum.
 template <bool DROP>
 __device__ __forceinline__ float fwd_unit_exp(const uint32_t (&v)[8], bool plain, uint32_t mask_addr, float c, float nmx, uint32_t p_addr,
-                                              uint32_t bits_addr, const m3ae_attn_params_t& P, uint64_t row_lin, int u, uint32_t lane_add) {
+                                              uint32_t bits_addr, const m3ae_attn_params_t& P, uint64_t row_lin, int u, uint32_t lane_add,
+                                              bool ready) {
   float pv[8];
   if (plain) {
 #pragma unroll
@@ -223,10 +231,16 @@ __device__ __forceinline__ float fwd_unit_exp(const uint32_t (&v)[8], bool plain
   const float sum = ((pv[0] + pv[1]) + (pv[2] + pv[3])) + ((pv[4] + pv[5]) + (pv[6] + pv[7]));
   uint32_t w0 = pack_bf16x2(pv[0], pv[1]), w1 = pack_bf16x2(pv[2], pv[3]), w2 = pack_bf16x2(pv[4], pv[5]), w3 = pack_bf16x2(pv[6], pv[7]);
   if (DROP) {
-    uint32_t f[4];
-    attn_keep_flags(P.drop_seed, P.drop_stream, row_lin, u, lane_add, f);
-    w0 &= flag_lanes(f[0]); w1 &= flag_lanes(f[1]); w2 &= flag_lanes(f[2]); w3 &= flag_lanes(f[3]);
-    sts8(bits_addr, attn_flags_to_byte(f));
+    if (ready) {
+      // keep bits staged from the pre-generated cache (m3ae_dropout_bits): bit j of the byte = key 8u+j kept
+      const uint32_t b = lds8(bits_addr);
+      w0 &= pair_mask(b); w1 &= pair_mask(b >> 2); w2 &= pair_mask(b >> 4); w3 &= pair_mask(b >> 6);
+    } else {
+      uint32_t f[4];
+      attn_keep_flags(P.drop_seed, P.drop_stream, row_lin, u, lane_add, f);
+      w0 &= flag_lanes(f[0]); w1 &= flag_lanes(f[1]); w2 &= flag_lanes(f[2]); w3 &= flag_lanes(f[3]);
+      sts8(bits_addr, attn_flags_to_byte(f));
+    }
   }
   sts128(p_addr, w0, w1, w2, w3);
   return sum;
@@ -256,6 +270,7 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
   const int h = blockIdx.x, b = blockIdx.y;
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int Lq = P.Lq, Lk = P.Lk, lk_pad = A.lk_pad, n_qt = A.n_qt;
+  int mask_nz = 0;
 
   if (warp == FWD_EW) {
     if (lane == 0) {
@@ -277,10 +292,16 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
     tmem_alloc_n(tmem_ptr_smem, (uint32_t)A.tmem_cols);
   } else {
     const float* mrow = P.mask ? P.mask + (int64_t)b * Lk : nullptr;
-    for (int i = threadIdx.x; i < 384; i += FWD_EW * 32) sMask[i] = i < Lk ? (mrow ? mrow[i] * LOG2E : 0.f) : -INFINITY;
+    for (int i = threadIdx.x; i < 384; i += FWD_EW * 32) {
+      const float mv = (i < Lk && mrow) ? mrow[i] : 0.f;
+      mask_nz |= mv != 0.f;
+      sMask[i] = i < Lk ? mv * LOG2E : -INFINITY;
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  // An additive mask that is all zeros for this batch row (the image stream's all-valid mask, m3ae_module.py:253-256) is
+  // treated as no mask: the element-wise warps then skip two shared-memory loads and an add per 8 keys in both passes.
+  const bool any_mask = __syncthreads_or(mask_nz) != 0;
   tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr_smem, 0);
   const uint32_t tS = tmem_base + 128;
@@ -374,7 +395,7 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const int n8 = lk_pad >> 3;
     const int ub = (n8 * cq) >> 2, nu = ((n8 * (cq + 1)) >> 2) - ub;  // this warp's 8-key units [ub, ub + nu)
-    const bool has_mask = P.mask != nullptr;
+    const bool has_mask = any_mask;
     const float c = A.scale_l2;
     const float keep_scale = drop_keep_scale(P.drop_p);
     const uint32_t thr = drop_thr15(P.drop_p);
@@ -401,6 +422,8 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
     };
 
     const uint32_t lane_add = drop_lane_add(thr);
+    const bool bits_ready = DROP && P.drop_mask != nullptr && P.drop_mask_ready != 0;
+    const int per_row = mask_ld >> 3;  // 8-byte words per row of the keep-bit cache
     const uint32_t a_mask = smem_u32(sMask), a_redm = smem_u32(sRedM) + row * 4, a_reds = smem_u32(sRedS) + row * 4;
     const uint32_t a_prow = smem_u32(sP) + row * 128, a_bits = smem_u32(sBits) + row * mask_ld;
     const uint32_t swz = ((uint32_t)row & 7u) << 4;
@@ -411,6 +434,16 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
       // The first HELD units of the row stay in registers from here on; the rest are read from TMEM twice (max pass,
       // exp pass) and go FIRST in the exp pass, so the S columns are released roughly half-way through the tile.
       uint32_t s[HELD][8];
+      // pre-generated keep bits of this tile: the quadrant's 32 rows x mask_ld bytes are contiguous in the global cache;
+      // issue the (<= 2 per thread) 8-byte loads now, park them in shared memory before the max-exchange barrier below
+      uint2 pre0 = make_uint2(0u, 0u), pre1 = make_uint2(0u, 0u);
+      const int bits_e0 = cq * 32 + lane;
+      const int bits_lim = (Lq - (t * TQ + quad * 32)) * per_row;  // words of rows < Lq (may exceed 32 * per_row)
+      if (bits_ready && active) {
+        const uint2* src = reinterpret_cast<const uint2*>(P.drop_mask + (sbase + t * TQ + quad * 32) * mask_ld);
+        if (bits_e0 < 32 * per_row && bits_e0 < bits_lim) pre0 = __ldg(src + bits_e0);
+        if (bits_e0 + 128 < 32 * per_row && bits_e0 + 128 < bits_lim) pre1 = __ldg(src + bits_e0 + 128);
+      }
       mbar_wait(&bars[F_SF], (uint32_t)(t & 1));
       tcgen05_fence_after();
       if (threadIdx.x == 0) TR(40 + 10 * t);
@@ -438,6 +471,11 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
           mx = fmaxf(mx, fwd_unit_max(v, !has_mask && k0 + 8 <= Lk, a_mask + k0 * 4, c));
         }
         sts32f(a_redm + cq * (TQ * 4), mx);
+        if (bits_ready) {  // every warp of the quadrant finished the previous tile's exp pass (its sum-exchange barrier)
+          uint2* dst = reinterpret_cast<uint2*>(sBits + quad * 32 * mask_ld);
+          if (bits_e0 < 32 * per_row) dst[bits_e0] = pre0;
+          if (bits_e0 + 128 < 32 * per_row) dst[bits_e0 + 128] = pre1;
+        }
         if (threadIdx.x == 0) TR(42 + 10 * t);
         named_bar(1 + quad, 128);
         if (threadIdx.x == 0) TR(43 + 10 * t);
@@ -460,7 +498,7 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
           tmem_ld8(tS + lane_addr + k0, v);
           tmem_ld_wait();
           sum += fwd_unit_exp<DROP>(v, !has_mask && k0 + 8 <= Lk, a_mask + k0 * 4, c, -mx,
-                                    a_prow + (u >> 3) * BLK + ((((uint32_t)u & 7u) << 4) ^ swz), a_bits + u, P, row_lin, u, lane_add);
+                                    a_prow + (u >> 3) * BLK + ((((uint32_t)u & 7u) << 4) ^ swz), a_bits + u, P, row_lin, u, lane_add, bits_ready);
         }
       }
       tcgen05_fence_before();
@@ -473,7 +511,7 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
           if (i < nu) {
             const int u = ub + i, k0 = u * 8;
             sum += fwd_unit_exp<DROP>(s[i], !has_mask && k0 + 8 <= Lk, a_mask + k0 * 4, c, -mx,
-                                      a_prow + (u >> 3) * BLK + ((((uint32_t)u & 7u) << 4) ^ swz), a_bits + u, P, row_lin, u, lane_add);
+                                      a_prow + (u >> 3) * BLK + ((((uint32_t)u & 7u) << 4) ^ swz), a_bits + u, P, row_lin, u, lane_add, bits_ready);
           }
         }
         sts32f(a_reds + cq * (TQ * 4), sum);
@@ -487,14 +525,12 @@ __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_con
         named_bar(1 + quad, 128);
         l = (lds32f(a_reds) + lds32f(a_reds + TQ * 4)) + (lds32f(a_reds + 2 * TQ * 4) + lds32f(a_reds + 3 * TQ * 4));
         if (cq == 0 && qrow < Lq) P.lse[sbase + qrow] = (mx + log2f(l)) * LN2;  // l >= 1: the row maximum contributes exp2(0)
-        if (DROP && P.drop_mask != nullptr) {
+        if (DROP && P.drop_mask != nullptr && !bits_ready) {
           // the quadrant's 32 rows x mask_ld bytes are contiguous in the global keep-bit cache: coalesced 8-byte copies
-          const int per_row = mask_ld >> 3;
           const int r0 = t * TQ + quad * 32;
           const uint2* src = reinterpret_cast<const uint2*>(sBits + quad * 32 * mask_ld);
           uint2* dst = reinterpret_cast<uint2*>(P.drop_mask + (sbase + r0) * mask_ld);
-          for (int e = cq * 32 + lane; e < 32 * per_row; e += 128)
-            if (r0 + e / per_row < Lq) dst[e] = src[e];
+          for (int e = cq * 32 + lane; e < 32 * per_row && e < bits_lim; e += 128) dst[e] = src[e];
         }
       }
       if (threadIdx.x == 0) TR(48 + 10 * t);
@@ -573,6 +609,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int Lq = P.Lq, Lk = P.Lk, lk_pad = A.lk_pad, n_qt = A.n_qt, n_kt = A.n_kt, nkv = A.nkv;
   const int total = n_kt * n_qt;
+  int mask_nz = 0;
 
   if (warp == BWD_EW) {
     if (lane == 0) {
@@ -595,10 +632,14 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     tmem_alloc_n(tmem_ptr_smem, (uint32_t)A.tmem_cols);
   } else {
     const float* mrow = P.mask ? P.mask + (int64_t)b * Lk : nullptr;
-    for (int i = threadIdx.x; i < 384; i += BWD_EW * 32) sMask[i] = i < Lk ? (mrow ? mrow[i] * LOG2E : 0.f) : -INFINITY;
+    for (int i = threadIdx.x; i < 384; i += BWD_EW * 32) {
+      const float mv = (i < Lk && mrow) ? mrow[i] : 0.f;
+      mask_nz |= mv != 0.f;
+      sMask[i] = i < Lk ? mv * LOG2E : -INFINITY;
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  const bool any_mask = __syncthreads_or(mask_nz) != 0;  // all-zero additive mask == no mask (see the forward kernel)
   tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr_smem, 0);
   const uint32_t tDQ = tmem_base, tDK = tmem_base + 192, tDV = tmem_base + 256, tS = tmem_base + 320, tDP = tmem_base + 384;
@@ -716,7 +757,10 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     }
   } else {
     // ===================== element-wise warps =====================
-    const int quad = warp & 3, half = warp >> 2;
+    // 16 warps: quad = TMEM lane quadrant (32 query rows), cg = 16-key column group of the 64-key tile.  (8 warps x 32
+    // columns left 2 warps per scheduler with ~650-instruction dependent chains per iteration: 28 % issue utilisation and
+    // 45 % of the samples on long-scoreboard waits, profiles/r2_ncu_attn_full_baseline.txt.)
+    const int quad = warp & 3, cg = warp >> 2;
     const int row = quad * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const float c = A.scale_l2;
@@ -725,7 +769,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     const uint32_t thr = drop_thr15(P.drop_p);
     const int mask_ld = A.mask_ld;
     const int64_t sbase = ((int64_t)b * P.H + h) * Lq;
-    const bool has_mask = P.mask != nullptr;
+    const bool has_mask = any_mask;
     // per-row constants of the <= 3 query tiles; rows >= Lq: lse = +inf -> P = exp2(-inf) = 0
     float lse2[3], dls[3];
 #pragma unroll
@@ -740,10 +784,10 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     auto store_dkv = [&](int kt) {
       const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;
       const bool kactive = quad * 32 < w;
-      uint32_t rk[32], rv[32];
+      uint32_t rk[16], rv[16];
       if (kactive) {
-        tmem_ld_32x32b_x32(tDK + lane_addr + half * 32, rk);
-        tmem_ld_32x32b_x32(tDV + lane_addr + half * 32, rv);
+        tmem_ld16(tDK + lane_addr + cg * 16, rk);
+        tmem_ld16(tDV + lane_addr + cg * 16, rv);
         tmem_ld_wait();
       }
       tcgen05_fence_before();
@@ -751,8 +795,8 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
       if (lane == 0) mbar_arrive(&bars[B_DE]);
       const int key = kt * KT + row;
       if (kactive && key < Lk) {
-        store_row32((bf16*)P.dk + ((int64_t)b * Lk + key) * P.lddk + h * D + half * 32, rk, 1.0f);
-        store_row32((bf16*)P.dv + ((int64_t)b * Lk + key) * P.lddv + h * D + half * 32, rv, DROP ? keep_scale : 1.0f);
+        store_row16((bf16*)P.dk + ((int64_t)b * Lk + key) * P.lddk + h * D + cg * 16, rk, 1.0f);
+        store_row16((bf16*)P.dv + ((int64_t)b * Lk + key) * P.lddv + h * D + cg * 16, rv, DROP ? keep_scale : 1.0f);
       }
     };
 
@@ -761,38 +805,32 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     int it = 0;
     for (int kt = 0; kt < n_kt; ++kt) {
       const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;
-      const int nsub = (w - half * 32) >= 32 ? 2 : ((w - half * 32) >= 16 ? 1 : 0);  // 16-key sub-blocks of this warp's half
+      const bool cols_live = cg * 16 < w;                    // this warp's 16 key columns exist in the tile (w % 16 == 0)
       const bool plain = !has_mask && (kt * KT + KT <= Lk);  // no additive mask, no padded keys in this tile
 #pragma unroll 1
       for (int qt = 0; qt < n_qt; ++qt, ++it) {
         const int qrow = qt * TQ + row;
-        const bool active = (qt * TQ + quad * 32 < Lq) && nsub > 0;  // warp-uniform
+        const bool active = (qt * TQ + quad * 32 < Lq) && cols_live;  // warp-uniform
         const float l2 = qt == 0 ? lse2[0] : (qt == 1 ? lse2[1] : lse2[2]);
         const float dl = qt == 0 ? dls[0] : (qt == 1 ? dls[1] : dls[2]);
         uint32_t bits = 0xFFFFFFFFu;
         if (DROP && active) {
           const uint64_t row_lin = (uint64_t)(sbase + qrow);
-          const int g0 = kt * 8 + half * 4;  // 8-key group of this warp's first key
+          const int g0 = kt * 8 + cg * 2;  // 8-key group of this warp's first key
           if (P.drop_mask != nullptr) {
-            bits = qrow < Lq ? *reinterpret_cast<const uint32_t*>(P.drop_mask + (int64_t)row_lin * mask_ld + g0) : 0u;
+            bits = qrow < Lq ? (uint32_t)*reinterpret_cast<const uint16_t*>(P.drop_mask + (int64_t)row_lin * mask_ld + g0) : 0u;
           } else {
-            bits = 0;
-#pragma unroll
-            for (int g = 0; g < 4; ++g)
-              if (g < 2 * nsub) bits |= attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0 + g, thr) << (8 * g);
+            bits = attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0, thr) |
+                   (attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0 + 1, thr) << 8);
           }
         }
-        uint32_t rs0[16], rd0[16], rs1[16], rd1[16];
+        uint32_t rs0[16], rd0[16];
         mbar_wait(&bars[B_SF], (uint32_t)(it & 1));
         tcgen05_fence_after();
         if (threadIdx.x == 0) TR(200 + 6 * it);
         if (active) {
-          tmem_ld16(tS + lane_addr + half * 32, rs0);
-          tmem_ld16(tDP + lane_addr + half * 32, rd0);
-          if (nsub == 2) {
-            tmem_ld16(tS + lane_addr + half * 32 + 16, rs1);
-            tmem_ld16(tDP + lane_addr + half * 32 + 16, rd1);
-          }
+          tmem_ld16(tS + lane_addr + cg * 16, rs0);
+          tmem_ld16(tDP + lane_addr + cg * 16, rd0);
           tmem_ld_wait();
         }
         tcgen05_fence_before();
@@ -805,10 +843,8 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
         if (active) {
           // P'' = keep ? P : 0 (dV is scaled by 1/(1-p) on the way out), dS = P * (keep ? dP/(1-p) : 0 - delta) * scale
           const uint32_t pb = a_p + (it & 1) * BLK, db = a_ds + (it & 1) * BLK;
-          const uint32_t mk = a_mask + (kt * KT + half * 32) * 4;
-          bwd_sub<DROP>(rs0, rd0, plain, mk, c, -l2, dl, DROP ? kss : P.scale, bits, pb, db, (uint32_t)(half * 4), swz);
-          if (nsub == 2)
-            bwd_sub<DROP>(rs1, rd1, plain, mk + 64, c, -l2, dl, DROP ? kss : P.scale, bits >> 16, pb, db, (uint32_t)(half * 4 + 2), swz);
+          const uint32_t mk = a_mask + (kt * KT + cg * 16) * 4;
+          bwd_sub<DROP>(rs0, rd0, plain, mk, c, -l2, dl, DROP ? kss : P.scale, bits, pb, db, (uint32_t)(cg * 2), swz);
         }
         if (threadIdx.x == 0) TR(203 + 6 * it);
         fence_proxy_async();
@@ -830,10 +866,10 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
     for (int qt = 0; qt < n_qt; ++qt) {
       const int qrow = qt * TQ + row;
       if (qt * TQ + quad * 32 < Lq) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tDQ + 64 * qt + lane_addr + half * 32, r);
+        uint32_t r[16];
+        tmem_ld16(tDQ + 64 * qt + lane_addr + cg * 16, r);
         tmem_ld_wait();
-        if (qrow < Lq) store_row32((bf16*)P.dq + ((int64_t)b * Lq + qrow) * P.lddq + h * D + half * 32, r, 1.0f);
+        if (qrow < Lq) store_row16((bf16*)P.dq + ((int64_t)b * Lq + qrow) * P.lddq + h * D + cg * 16, r, 1.0f);
       }
     }
   }

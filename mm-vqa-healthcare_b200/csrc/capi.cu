@@ -69,6 +69,7 @@ int activation_fwd(const void*, void*, int64_t, int, int, cudaStream_t);
 int activation_bwd(const void*, const void*, void*, int64_t, int, int, cudaStream_t);
 int bce_with_logits(const float*, const float*, float*, float*, int64_t, float, float, cudaStream_t);
 int cross_entropy(const float*, int64_t, const int64_t*, const float*, float*, float*, int64_t, int64_t, int, int64_t, cudaStream_t);
+int dropout_bits(const m3ae_dropbits_item_t*, int, cudaStream_t);
 int layernorm_fwd(const void*, const float*, const float*, void*, float*, float*, int64_t, int, float, int, cudaStream_t);
 int layernorm_bwd(const void*, const void*, const float*, const float*, const float*, void*, float*, float*, float*, int64_t, int, int, void*, float, uint64_t, uint64_t, const uint32_t*, cudaStream_t);
 int colsum(const void*, float*, int64_t, int, int64_t, int, cudaStream_t);
@@ -159,6 +160,12 @@ int m3ae_cross_entropy(const float* logits, int64_t ld, const int64_t* target, c
   ARCH_GATE();
   M3AE_CHECK(logits && target && row_weight && loss_out, M3AE_ERR_INVALID, "cross_entropy: null pointer");
   return cross_entropy(logits, ld, target, row_weight, loss_out, dlogits, ldd, M, V, ignore_index, (cudaStream_t)stream);
+}
+
+int m3ae_dropout_bits(const m3ae_dropbits_item_t* items, int32_t n_items, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(items != nullptr && n_items >= 1 && n_items <= M3AE_MAX_DROPBITS, M3AE_ERR_INVALID, "dropout_bits: need 1..%d items, got %d", M3AE_MAX_DROPBITS, n_items);
+  return dropout_bits(items, n_items, (cudaStream_t)stream);
 }
 
 int m3ae_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd, int64_t M, int32_t H, float eps, int32_t dtype, void* stream) {

@@ -253,6 +253,7 @@ struct EpiDev {
   int aux_is_grad;         // aux_out := act'(pre-activation); dact multiplies by aux_in as stored
   uint32_t* drop_bits;     // optional keep-bit cache [rows][N/32] (tcgen05 epilogues, 32-column chunks)
   int64_t drop_bits_ld;    // words per row = N / 32 (set by the launcher)
+  int drop_bits_ready;     // 1: read the keep bits from drop_bits instead of evaluating Philox
 };
 
 // Applies the epilogue to `n` consecutive columns [col, col+n) of row `row` whose accumulators are acc[0..n).
@@ -289,13 +290,16 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
   if (e.drop_p > 0.0f) {
     const float inv = drop_keep_scale(e.drop_p);
     uint32_t bits = 0;
+    const bool ready = NV == 32 && e.drop_bits != nullptr && e.drop_bits_ready;
+    const uint32_t cached = ready ? e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] : 0u;
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
-      const bool keep = dropout_keep(e.drop_seed, e.drop_stream, (uint64_t)(row * e.ldo + col + j), e.drop_p);
+      const bool keep = ready ? ((cached >> (j & 31)) & 1u) != 0u
+                              : dropout_keep(e.drop_seed, e.drop_stream, (uint64_t)(row * e.ldo + col + j), e.drop_p);
       acc[j] = keep ? acc[j] * inv : 0.0f;
       if (NV == 32) bits |= (keep ? 1u : 0u) << (j & 31);
     }
-    if (NV == 32 && e.drop_bits != nullptr) e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] = bits;
+    if (NV == 32 && e.drop_bits != nullptr && !ready) e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] = bits;
   }
   if (e.residual) {
 #pragma unroll

@@ -4,6 +4,8 @@
 //                           gradient with respect to the logits in the same pass
 //   cross_entropy           decoder fine-tune loss (m3ae_decoder.py:365-368: CrossEntropyLoss(ignore_index=pad) on the
 //                           transposed logits, * padding_mask, / padding_mask.sum()) and its gradient
+#include <string.h>
+
 #include "common.cuh"
 
 namespace m3ae {
@@ -105,6 +107,43 @@ __global__ void __launch_bounds__(256) cross_entropy_kernel(const float* __restr
   }
 }
 
+struct DropBitsGroup {
+  m3ae_dropbits_item_t it[M3AE_MAX_DROPBITS];
+  int64_t word_begin[M3AE_MAX_DROPBITS + 1];  // prefix sums of output words (uint32) per item
+  int32_t words_per_row[M3AE_MAX_DROPBITS];
+  int n;
+};
+
+// One thread = one uint32 of keep bits = 4 Philox evaluations (independent: good ILP).  Streaming, no shared memory.
+__global__ void __launch_bounds__(256) dropout_bits_kernel(const __grid_constant__ DropBitsGroup G) {
+  const int64_t total = G.word_begin[G.n];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += stride) {
+    int i = 0;
+#pragma unroll
+    for (int k = 1; k < M3AE_MAX_DROPBITS; ++k)
+      if (k < G.n && w >= G.word_begin[k]) i = k;
+    const m3ae_dropbits_item_t& it = G.it[i];
+    const int64_t local = w - G.word_begin[i];
+    const int wpr = G.words_per_row[i];
+    const int64_t row = local / wpr;
+    const int wc = (int)(local - row * wpr);
+    const uint32_t thr = drop_thr15(it.p);
+    uint32_t bits = 0;
+    if (it.kind == 0) {
+      const int units = (it.n + 7) >> 3;  // 8-key units of a row; bytes past the last unit stay 0
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (4 * wc + j < units) bits |= attn_keep_bits8(it.seed, it.site, (uint64_t)row, 4 * wc + j, thr) << (8 * j);
+    } else {
+      const uint64_t e0 = (uint64_t)(row * it.ld + 32 * wc);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bits |= dropout_keep8(it.seed, it.site, e0 + 8 * j, thr) << (8 * j);
+    }
+    reinterpret_cast<uint32_t*>(it.out)[local] = bits;
+  }
+}
+
 unsigned grid_for(int64_t n, int threads) {
   const int64_t cap = (int64_t)sm_count() * 8;
   const int64_t blocks = (n + threads - 1) / threads;
@@ -138,6 +177,31 @@ int bce_with_logits(const float* logits, const float* targets, float* loss_out, 
   M3AE_CHECK(n > 0, M3AE_ERR_INVALID, "bce_with_logits: empty input");
   M3AE_CUDA(cudaMemsetAsync(loss_out, 0, sizeof(float), st));
   bce_logits_kernel<<<grid_for(n, 256), 256, 0, st>>>(logits, targets, loss_out, dlogits, n, scale_loss, scale_grad);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
+int dropout_bits(const m3ae_dropbits_item_t* items, int n, cudaStream_t st) {
+  DropBitsGroup G;
+  memset(&G, 0, sizeof(G));
+  G.n = n;
+  int64_t words = 0;
+  for (int i = 0; i < n; ++i) {
+    const m3ae_dropbits_item_t& it = items[i];
+    M3AE_CHECK(it.out != nullptr && it.rows > 0 && it.n > 0, M3AE_ERR_INVALID, "dropout_bits: empty item %d", i);
+    M3AE_CHECK(it.p > 0.f && it.p < 1.f, M3AE_ERR_INVALID, "dropout_bits: p %f not in (0,1)", it.p);
+    M3AE_CHECK(it.kind == 0 || (it.kind == 1 && it.n % 32 == 0 && it.ld % 8 == 0), M3AE_ERR_INVALID,
+               "dropout_bits: item %d: kind must be 0 (attention) or 1 (hidden, N %% 32 == 0, ld %% 8 == 0)", i);
+    M3AE_CHECK((((uintptr_t)it.out) & 3) == 0, M3AE_ERR_INVALID, "dropout_bits: output of item %d is not 4-byte aligned", i);
+    G.it[i] = it;
+    G.words_per_row[i] = it.kind == 0 ? 2 * ((it.n + 63) / 64) : it.n / 32;  // attention rows: 8 bytes per 64 keys
+    G.word_begin[i] = words;
+    words += it.rows * G.words_per_row[i];
+  }
+  G.word_begin[n] = words;
+  for (int i = n + 1; i <= M3AE_MAX_DROPBITS; ++i) G.word_begin[i] = words;
+  dropout_bits_kernel<<<grid_for(words, 256), 256, 0, st>>>(G);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

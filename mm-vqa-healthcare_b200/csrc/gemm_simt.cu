@@ -13,7 +13,7 @@ void epi_to_dev(const m3ae_gemm_epilogue_t& e, EpiDev* d) {
   d->residual = e.residual; d->res_dtype = e.res_dtype; d->ldr = e.ldr;
   d->drop_p = e.drop_p; d->drop_seed = e.drop_seed; d->drop_stream = e.drop_stream;
   d->accumulate = e.accumulate; d->alpha = e.alpha; d->aux_is_grad = e.aux_is_grad;
-  d->drop_bits = e.drop_bits; d->drop_bits_ld = 0;
+  d->drop_bits = e.drop_bits; d->drop_bits_ld = 0; d->drop_bits_ready = e.drop_bits_ready;
 }
 void count_launch();
 

@@ -339,6 +339,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
           __syncwarp();
         }
+        uint32_t cached_bits[4] = {0u, 0u, 0u, 0u};
+        if (epi.drop_p > 0.f && epi.drop_bits_ready && row < q.M) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            if (c < nchunks) cached_bits[c] = __ldg(epi.drop_bits + row * epi.drop_bits_ld + ((col_base + c * 32) >> 5));
+        }
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
 #pragma unroll 1
@@ -463,17 +469,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           }
           if (epi.drop_p > 0.f) {
             const float inv = drop_keep_scale(epi.drop_p);
-            const uint32_t thr15 = drop_thr15(epi.drop_p);
-            const uint64_t e0 = (uint64_t)(row * epi.ldo + col);  // multiple of 8 (ldo % 8 == 0, col % 32 == 0)
-            uint32_t bits = 0;
+            if (epi.drop_bits_ready) {
+              // keep bits generated ahead of the GEMM (m3ae_dropout_bits): one 4-byte load per thread and chunk, issued
+              // before the accumulator wait (cached_bits), instead of 4 Philox evaluations in the issue-bound epilogue
+              const uint32_t bits = c == 0 ? cached_bits[0] : c == 1 ? cached_bits[1] : c == 2 ? cached_bits[2] : cached_bits[3];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t m8 = dropout_keep8(epi.drop_seed, epi.drop_stream, e0 + 8 * j, thr15);
-              bits |= m8 << (8 * j);
+              for (int j = 0; j < 32; ++j) v[j] = ((bits >> j) & 1u) ? v[j] * inv : 0.f;
+            } else {
+              const uint32_t thr15 = drop_thr15(epi.drop_p);
+              const uint64_t e0 = (uint64_t)(row * epi.ldo + col);  // multiple of 8 (ldo % 8 == 0, col % 32 == 0)
+              uint32_t bits = 0;
 #pragma unroll
-              for (int k = 0; k < 8; ++k) v[8 * j + k] = ((m8 >> k) & 1u) ? v[8 * j + k] * inv : 0.f;
+              for (int j = 0; j < 4; ++j) {
+                const uint32_t m8 = dropout_keep8(epi.drop_seed, epi.drop_stream, e0 + 8 * j, thr15);
+                bits |= m8 << (8 * j);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[8 * j + k] = ((m8 >> k) & 1u) ? v[8 * j + k] * inv : 0.f;
+              }
+              if (epi.drop_bits != nullptr && row < q.M) epi.drop_bits[row * epi.drop_bits_ld + (col >> 5)] = bits;
             }
-            if (epi.drop_bits != nullptr && row < q.M) epi.drop_bits[row * epi.drop_bits_ld + (col >> 5)] = bits;
           }
           if (q.in_is_residual) {
 #pragma unroll

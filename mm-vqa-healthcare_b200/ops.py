@@ -63,7 +63,7 @@ class GemmSpec:
 
     def __init__(self, a, b, out, *, a_major=MAJOR_K, b_major=MAJOR_K, bias=None, act=ACT_NONE, aux_out=None,
                  aux_in=None, dact=ACT_NONE, residual=None, drop_p=0.0, drop_seed=0, drop_stream=0, accumulate=False,
-                 split_k=1, alpha=1.0, aux_is_grad=False, drop_bits=None):
+                 split_k=1, alpha=1.0, aux_is_grad=False, drop_bits=None, drop_bits_ready=False):
         _need_cuda(a, b, out, bias, aux_out, aux_in, residual, drop_bits)
         assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
         assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
@@ -106,6 +106,7 @@ class GemmSpec:
         e.alpha = float(alpha)
         e.aux_is_grad = 1 if aux_is_grad else 0
         e.drop_bits = drop_bits.data_ptr() if drop_bits is not None else None
+        e.drop_bits_ready = 1 if (drop_bits is not None and drop_bits_ready) else 0
         self.problem = p
 
 
@@ -124,7 +125,8 @@ def gemm(a, b, out, backend=GEMM_AUTO, **kw):
 
 
 def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, scale=None, causal=False, drop_p=0.0,
-                drop_seed=0, drop_stream=0, dout=None, dq=None, dk=None, dv=None, delta=None, drop_mask=None):
+                drop_seed=0, drop_stream=0, dout=None, dq=None, dk=None, dv=None, delta=None, drop_mask=None,
+                drop_mask_ready=False):
     _need_cuda(q, k, v, out, lse, mask, probs, dout, dq, dk, dv, delta, drop_mask)
     for t in (q, k, v, out):
         assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
@@ -149,6 +151,7 @@ def attn_params(q, k, v, out, lse, *, B, H, Lq, Lk, dh, mask=None, probs=None, s
     if drop_mask is not None:
         assert drop_mask.dtype == torch.uint8 and drop_mask.is_contiguous() and drop_mask.numel() == B * H * Lq * drop_mask_ld(Lk)
         p.drop_mask = drop_mask.data_ptr()
+        p.drop_mask_ready = 1 if drop_mask_ready else 0
     if dout is not None:
         for t in (dout, dq, dk, dv):
             assert t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
@@ -289,6 +292,30 @@ class CastGroup:
 
     def run(self):
         L.check(self.fn(self.arr, self.n, _stream()), "m3ae_cast_group")
+
+
+class DropoutBits:
+    """A cached grouped launch of m3ae_dropout_bits: keep bits of up to 12 dropout sites (attention caches [B*H*Lq, 8*ceil(Lk/64)]
+    bytes, hidden caches [M, N/32] uint32) generated in one streaming kernel ahead of the kernels that apply them.
+    items: (kind 0 attention | 1 hidden, out tensor, rows, n, ld, p, site); seeds are set per call."""
+
+    def __init__(self, items):
+        assert 1 <= len(items) <= L.MAX_DROPBITS
+        self.keep = [it[1] for it in items]
+        self.n = len(items)
+        self.arr = (L.DropBitsItem * self.n)()
+        for a, (kind, out, rows, n, ld, p, site) in zip(self.arr, items):
+            _need_cuda(out)
+            assert out.is_contiguous()
+            need = rows * (8 * ((n + 63) // 64) if kind == 0 else (n // 32) * 4)
+            assert out.numel() * out.element_size() == need, "keep-bit buffer has the wrong size"
+            a.out, a.rows, a.ld, a.n, a.kind, a.p, a.site = out.data_ptr(), rows, ld, n, kind, float(p), int(site)
+        self.fn = L.load().m3ae_dropout_bits
+
+    def run(self, seeds):
+        for a, s in zip(self.arr, seeds):
+            a.seed = int(s)
+        L.check(self.fn(self.arr, self.n, _stream()), "m3ae_dropout_bits")
 
 
 def add_rowvec(a, b, out):

@@ -88,8 +88,8 @@ def test_whole_model_gradients_b2_match_reference(dtype):
       fp32: per-tensor norm within 2e-4, samples within 2e-3 of the tensor's RMS scale.
       bf16: the WHOLE sampled gradient (all tensors concatenated = what the optimizer sees) within 4e-2 = 2x the forward gate
             (a gradient is a product of two rounded factors; measured 2.4e-2); per-tensor norms within 15 % for every tensor
-            whose reference norm is at least 5 % of the median tensor's, and within 5 % of the median norm in absolute terms
-            for all 627.  The exempted ~70 tensors are attention query / key projections: with random-init weights the
+            whose reference norm is at least 5 % of the median tensor's, and within 5 % of max(own norm, median norm) for all
+            627.  The exempted ~70 tensors are attention query / key projections: with random-init weights the
             attention is near-uniform and the token rows have nearly collapsed onto each other, so the true
             dS = P (dP - rowsum(dO*O)) cancels to ~1e-3 of the typical gradient scale (reference norms 0.01-0.13 against a
             median of 6.4) and the bf16 rounding of O and dO (2^-9) inside that cancellation is larger than the remainder —
@@ -116,7 +116,7 @@ def test_whole_model_gradients_b2_match_reference(dtype):
         gn = p.grad.float().norm().item()
         if dtype == torch.float32 or float(g["norm"]) >= 0.05 * median:
             worst_n = max(worst_n, (name, abs(gn - float(g["norm"])) / float(g["norm"])), key=lambda t: t[1])
-        worst_a = max(worst_a, (name, abs(gn - float(g["norm"])) / median), key=lambda t: t[1])
+        worst_a = max(worst_a, (name, abs(gn - float(g["norm"])) / max(float(g["norm"]), median)), key=lambda t: t[1])
         s = p.grad.float().flatten()[:: max(1, p.numel() // 64)][:64].cpu()
         rms = float(g["norm"]) * (s.numel() / p.numel()) ** 0.5
         worst_s = max(worst_s, (name, ((s - g["samples"]).norm() / max(g["samples"].norm().item(), rms)).item()), key=lambda t: t[1])
@@ -125,7 +125,7 @@ def test_whole_model_gradients_b2_match_reference(dtype):
         n += 1
     total = rel(torch.cat(all_s), torch.cat(all_g))
     print(f"whole-model gradients {dtype}: {n} tensors; concatenated samples rel err {total:.3e}; worst per-tensor norm error "
-          f"{worst_n}; worst norm error in units of the median norm {worst_a}; worst per-tensor sample error {worst_s}")
+          f"{worst_n}; worst norm error in units of max(own, median) norm {worst_a}; worst per-tensor sample error {worst_s}")
     assert n > 600
     if dtype == torch.float32:
         assert worst_n[1] < 2e-4 and worst_s[1] < 2e-3 and total < 2e-4, (worst_n, worst_s, total)

@@ -514,3 +514,61 @@ def test_layernorm_bwd_staging_ring_matches_register_path(M, drop):
         assert torch.equal(a, b)
     for a, b in zip(res[0][1:], res[1][1:]):
         assert rel_err(b, a) < 1e-5
+
+
+@pytest.mark.parametrize("shape", [(325, 325), (32, 325), (325, 32), (32, 32), (70, 325)])
+def test_pregenerated_attention_keep_bits_equal_in_kernel_generation(shape):
+    """m3ae_dropout_bits evaluates the same Philox counters the attention kernels evaluate: the pre-generated cache must be
+    byte-identical to the cache the forward writes, and a forward that READS it (drop_mask_ready) must return the same
+    output and log-sum-exp bit for bit — for the tcgen05 kernel (325x325, 70x325) and the mma.sync tiles (the shapes with a
+    32-token side)."""
+    Lq, Lk = shape
+    B, H, dh, p = 3, 12, 64, 0.1
+    q, k, v = (rnd(B * L, H * dh, dtype=torch.bfloat16, seed=i) for i, L in ((0, Lq), (1, Lk), (2, Lk)))
+    kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, drop_p=p, drop_seed=1234567891011, drop_stream=2)
+    ld = ops.drop_mask_ld(Lk)
+    outs = []
+    written = torch.zeros(B * H * Lq * ld, dtype=torch.uint8, device=DEV)
+    pre = torch.full((B * H * Lq * ld,), 255, dtype=torch.uint8, device=DEV)
+    ops.DropoutBits([(0, pre, B * H * Lq, Lk, 0, p, 2)]).run([1234567891011])
+    for mask, ready in ((written, False), (pre, True)):
+        out = torch.empty(B * Lq, H * dh, dtype=torch.bfloat16, device=DEV)
+        lse = torch.empty(B, H, Lq, device=DEV)
+        ops.attn_fwd(q, k, v, out, lse, drop_mask=mask, drop_mask_ready=ready, **kw)
+        outs.append((out, lse))
+    units = (Lk + 7) // 8
+    assert torch.equal(written.view(-1, ld)[:, :units], pre.view(-1, ld)[:, :units]), "pre-generated bits differ from the kernel's"
+    assert (pre.view(-1, ld)[:, units:] == 0).all()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    # backward reading either cache gives the same gradients
+    dout = rnd(B * Lq, H * dh, dtype=torch.bfloat16, seed=9)
+    grads = []
+    for mask in (written, pre):
+        dq, dk, dv = (torch.empty_like(t) for t in (q, k, v))
+        delta = torch.empty(B, H, Lq, device=DEV)
+        ops.attn_bwd(q, k, v, outs[0][0], outs[0][1], dout=dout, dq=dq, dk=dk, dv=dv, delta=delta, drop_mask=mask, **kw)
+        grads.append((dq, dk, dv))
+    for a, b_ in zip(*grads):
+        assert torch.equal(a, b_)
+
+
+@pytest.mark.parametrize("M", [1000, 20800])
+def test_pregenerated_hidden_keep_bits_equal_epilogue_generation(M):
+    N, K = 768, 128
+    bf = torch.bfloat16
+    a, w, res = rnd(M, K, dtype=bf), rnd(N, K, dtype=bf, seed=1), rnd(M, N, dtype=bf, seed=2)
+    written = torch.zeros(M, N // 32, dtype=torch.int32, device=DEV)
+    pre = torch.full((M, N // 32), -1, dtype=torch.int32, device=DEV)
+    ops.DropoutBits([(1, pre, M, N, N, 0.1, 3)]).run([77])
+    o1, o2 = torch.empty(M, N, dtype=bf, device=DEV), torch.empty(M, N, dtype=bf, device=DEV)
+    ops.gemm(a, w, o1, backend=ops.GEMM_TCGEN05, residual=res, drop_p=0.1, drop_seed=77, drop_stream=3, drop_bits=written)
+    ops.gemm(a, w, o2, backend=ops.GEMM_TCGEN05, residual=res, drop_p=0.1, drop_seed=77, drop_stream=3, drop_bits=pre, drop_bits_ready=True)
+    assert torch.equal(written, pre), "pre-generated hidden keep bits differ from the epilogue's"
+    assert torch.equal(o1, o2)
+    try:
+        ops.set_gemm_epilogue(True)  # generic per-element epilogue reading the cache
+        o3 = torch.empty(M, N, dtype=bf, device=DEV)
+        ops.gemm(a, w, o3, backend=ops.GEMM_TCGEN05, residual=res, drop_p=0.1, drop_seed=77, drop_stream=3, drop_bits=pre, drop_bits_ready=True)
+    finally:
+        ops.set_gemm_epilogue(False)
+    assert rel_err(o3, o1) < 1e-2 and torch.equal(o3 != res, o1 != res)

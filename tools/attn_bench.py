@@ -17,9 +17,18 @@ def run(Lq, Lk, drop=0.0):
     dq = torch.empty_like(q); dkv = torch.empty_like(kv)
     delta = torch.empty(B, H, Lq, device=dev)
     kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, drop_p=drop, drop_seed=1, drop_stream=0)
+    pregen = os.environ.get("PREGEN", "0") == "1" and drop > 0
+    cache = os.environ.get("CACHE", "0") == "1" and drop > 0
+    if pregen or cache:  # production: keep bits generated ahead by m3ae_dropout_bits / cached by the forward, read by the backward
+        kw["drop_mask"] = torch.zeros(B * H * Lq * ops.drop_mask_ld(Lk), dtype=torch.uint8, device=dev)
+    if pregen:
+        gen = ops.DropoutBits([(0, kw["drop_mask"], B * H * Lq, Lk, 0, drop, 0)])
+        gen.run([1])
+        kw["drop_mask_ready"] = True
+        def g(): gen.run([1])
     def f(): ops.attn_fwd(Q, K, V, out, lse, **kw)
     def b(): ops.attn_bwd(Q, K, V, out, lse, dout=dout, dq=dq[:, :768], dk=dkv[:, 768:1536], dv=dkv[:, 1536:], delta=delta, **kw)
-    for name, fn, mult in (("fwd", f, 4), ("bwd", b, 10)):
+    for name, fn, mult in (("fwd", f, 4), ("bwd", b, 10)) + ((("bitgen", g, 0),) if pregen else ()):
         for _ in range(2): fn()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
