@@ -118,10 +118,12 @@ __device__ __forceinline__ void umma_commit_el(uint32_t el, uint64_t* bar) {
   (void)el;
   umma_commit(bar);
 }
-// kind::f16 instruction descriptor: D fp32, A/B bf16, M = 128.
-__device__ __forceinline__ uint32_t idesc(int n, int a_mn, int b_mn) {
+// kind::f16 instruction descriptor: D fp32, A/B bf16, M = 128 (or 64: the accumulator then sits in lanes 0-15 of each
+// 32-lane TMEM sub-partition, row i -> lane (i % 16) + 32 * (i / 16), and a second M = 64 accumulator can share its
+// columns at lane offset 16).
+__device__ __forceinline__ uint32_t idesc(int n, int a_mn, int b_mn, int m = TQ) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) |
-         ((uint32_t)(TQ >> 4) << 24);
+         ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ void tmem_alloc_n(uint32_t* smem_dst, uint32_t ncols) {
@@ -585,10 +587,16 @@ __device__ __forceinline__ void bwd_sub(const uint32_t (&rs)[16], const uint32_t
 }
 
 // ------------------------------------------------------------------------------------------------ backward
-// TMEM columns: dQ tiles at [0, 64*n_qt), dK at 192, dV at 256, S at 320, dP at 384 (each 64 wide).
+// TMEM columns (all 512): dQ tiles at [0, 64*n_qt); dV and dK share [192, 256) as two M = 64 accumulators (dV in lanes
+// 0-15 of each sub-partition, dK in lanes 16-31); S/dP double-buffered: S(b) at 256 + 128 b, dP(b) at 320 + 128 b.
 // smem: Q[n_qt] | dO[n_qt] (resident) | K ring | V ring (64-key tiles) | P x2 | dS x2 | mask | barriers.
-// Iteration it = kt * n_qt + qt (key tiles outer, query tiles inner).
-enum { B_KV0 = 0 /* ..3 */, B_QF0 = 4 /* ..6 */, B_SF = 7, B_SE = 8, B_PF0 = 9, B_PF1 = 10, B_MD0 = 11, B_MD1 = 12, B_DE = 13, B_NBAR = 14 };
+// Iteration it = kt * n_qt + qt (key tiles outer, query tiles inner).  S/dP of iteration it + 2 are issued as soon as the
+// element-wise warps have pulled S/dP of iteration it into registers, so the tensor pipe computes them while iteration it
+// and it + 1 are being processed: the single-buffered version spent half of every iteration in the chain
+// S-drained -> issue -> MMA -> S-full -> tcgen05.ld (4400 cycles per iteration against ~1800 of work on either side,
+// profiles/r2_attn_bwd_timeline.txt).
+enum { B_KV0 = 0 /* ..3 */, B_QF0 = 4 /* ..6 */, B_SF0 = 7, B_SF1 = 8, B_SE0 = 9, B_SE1 = 10, B_PF0 = 11, B_PF1 = 12, B_MD0 = 13, B_MD1 = 14,
+       B_DE = 15, B_NBAR = 16 };
 constexpr int MAX_NKV = 4;
 
 template <bool DROP>
@@ -610,6 +618,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
   const int Lq = P.Lq, Lk = P.Lk, lk_pad = A.lk_pad, n_qt = A.n_qt, n_kt = A.n_kt, nkv = A.nkv;
   const int total = n_kt * n_qt;
   int mask_nz = 0;
+  if (threadIdx.x == 0) TR(100);
 
   if (warp == BWD_EW) {
     if (lane == 0) {
@@ -619,8 +628,10 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
       tma_prefetch_desc(&A.map_do);
       for (int i = 0; i < MAX_NKV; ++i) mbar_init(&bars[B_KV0 + i], 1);
       for (int i = 0; i < 3; ++i) mbar_init(&bars[B_QF0 + i], 1);
-      mbar_init(&bars[B_SF], 1);
-      mbar_init(&bars[B_SE], BWD_EW);
+      mbar_init(&bars[B_SF0], 1);
+      mbar_init(&bars[B_SF1], 1);
+      mbar_init(&bars[B_SE0], BWD_EW);
+      mbar_init(&bars[B_SE1], BWD_EW);
       mbar_init(&bars[B_PF0], BWD_EW);
       mbar_init(&bars[B_PF1], BWD_EW);
       mbar_init(&bars[B_MD0], 1);
@@ -642,7 +653,8 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
   const bool any_mask = __syncthreads_or(mask_nz) != 0;  // all-zero additive mask == no mask (see the forward kernel)
   tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr_smem, 0);
-  const uint32_t tDQ = tmem_base, tDK = tmem_base + 192, tDV = tmem_base + 256, tS = tmem_base + 320, tDP = tmem_base + 384;
+  const uint32_t tDQ = tmem_base, tDV = tmem_base + 192, tDK = tmem_base + 192 + (16u << 16), tS0 = tmem_base + 256;
+  if (threadIdx.x == 0) TR(101);
 
   if (warp == BWD_EW) {
     {
@@ -667,7 +679,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
         tma_load_2d(sdO + qt * BLK, &A.map_do, &bars[B_QF0 + qt], col0, b * Lq + qt * TQ);
       }
       for (int kt = 1; kt < n_kt && kt < nkv; ++kt) load_kv(kt, kt);
-      const uint32_t id_acc = idesc(D, 1, 1);  // dV, dK: A (P'/dS tile) and B (dO/Q tile) both MN-major
+      const uint32_t id_acc = idesc(D, 1, 1, KT);  // dV, dK (M = 64 keys): A (P'/dS tile) and B (dO/Q tile) both MN-major
       const uint32_t id_dq = idesc(D, 0, 1);   // dQ: A = dS K-major, B = K tile MN-major
       // Everything below is kept division-free and derived from kernel parameters and plain loop counters so that the
       // compiler can hold descriptors in uniform registers (a value that passes through a vector register costs an
@@ -680,8 +692,8 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
       const uint32_t qk0 = dlo(uQ, 16), dok0 = dlo(uDO, 16), kk0 = dlo(uK, 16), vk0 = dlo(uV, 16);
       const uint32_t qm0 = dlo(uQ, 8192), dom0 = dlo(uDO, 8192), km0 = dlo(uK, 8192);
       const uint32_t pm0 = dlo(uP, BLK), dsm0 = dlo(uDS, BLK), dsk0 = dlo(uDS, 16);
-      // S, dP of iteration (kt, qt); slot = kt % nkv, use = kt / nkv
-      auto issue_sdp = [&](int kt, int qt, int slot, int use) {
+      // S, dP of iteration (kt, qt) into TMEM buffer sb2; slot = kt % nkv, use = kt / nkv
+      auto issue_sdp = [&](int kt, int qt, int slot, int use, int sb2) {
         const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;  // keys in this tile (multiple of 16)
         const uint32_t id_s = idesc(w, 0, 0);
         if (kt == 0) mbar_wait(&bars[B_QF0 + qt], 0);
@@ -689,6 +701,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
         tcgen05_fence_after();
         const uint32_t q_lo = qk0 + (uint32_t)qt * (BLK >> 4), do_lo = dok0 + (uint32_t)qt * (BLK >> 4);
         const uint32_t k_lo = kk0 + (uint32_t)slot * (KBLK >> 4), v_lo = vk0 + (uint32_t)slot * (KBLK >> 4);
+        const uint32_t tS = tS0 + (uint32_t)sb2 * 128u, tDP = tS + 64u;
         // the two independent accumulation chains are interleaved; one lane issues the whole batch
         if (!elect_one()) return;
         umma_lo<false>(el, tS, q_lo, k_lo, id_s);
@@ -699,21 +712,29 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
         umma_lo<true>(el, tDP, do_lo + 4, v_lo + 4, id_s);
         umma_lo<true>(el, tS, q_lo + 6, k_lo + 6, id_s);
         umma_lo<true>(el, tDP, do_lo + 6, v_lo + 6, id_s);
-        umma_commit_el(el, &bars[B_SF]);
+        umma_commit_el(el, &bars[B_SF0 + sb2]);
       };
-      issue_sdp(0, 0, 0, 0);
-      int it = 0, slot = 0, use = 0;
+      // (a_kt, a_qt): the next S/dP to issue, two iterations ahead of the accumulate MMAs
+      int a_kt = 0, a_qt = 0, a_slot = 0, a_use = 0;
+      auto issue_next = [&](int sb2) {
+        issue_sdp(a_kt, a_qt, a_slot, a_use, sb2);
+        if (++a_qt == n_qt) {
+          a_qt = 0;
+          ++a_kt;
+          if (++a_slot == nkv) { a_slot = 0; ++a_use; }
+        }
+      };
+      issue_next(0);
+      if (total > 1) issue_next(1);
+      int it = 0, slot = 0, prev_slot = 0;
       for (int kt = 0; kt < n_kt; ++kt) {
         const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;
         const int ksteps = w >> 4;               // reduction over the tile's keys (dQ)
-        int nslot = slot + 1, nuse = use;        // ring position of key tile kt + 1
-        if (nslot == nkv) { nslot = 0; nuse = use + 1; }
         for (int qt = 0; qt < n_qt; ++qt, ++it) {
           const int buf = it & 1;
-          if (it + 1 < total) {
-            mbar_wait(&bars[B_SE], (uint32_t)(it & 1));  // S, dP of this iteration are in registers
-            if (qt + 1 < n_qt) issue_sdp(kt, qt + 1, slot, use);
-            else issue_sdp(kt + 1, 0, nslot, nuse);
+          if (it + 2 < total) {
+            mbar_wait(&bars[B_SE0 + buf], (uint32_t)((it >> 1) & 1));  // S, dP of this iteration are in registers
+            issue_next(buf);
             TR(110 + 4 * it);
           }
           mbar_wait(&bars[B_PF0 + buf], (uint32_t)((it >> 1) & 1));
@@ -745,14 +766,15 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
           }
           __syncwarp();
           TR(112 + 4 * it);
-          if (qt == n_qt - 1 && kt + nkv < n_kt) {
-            // this key tile's K/V slot is free once the MMAs above have completed: refill it with tile kt + nkv
-            mbar_wait(&bars[B_MD0 + buf], (uint32_t)((it >> 1) & 1));
-            load_kv(kt + nkv, slot);
+          if (qt == 0 && kt > 0 && kt - 1 + nkv < n_kt) {
+            // the K/V slot of key tile kt - 1 is free once its last accumulate MMAs (iteration it - 1, issued a whole
+            // iteration ago) have completed: refill it with tile kt - 1 + nkv
+            mbar_wait(&bars[B_MD0 + ((it - 1) & 1)], (uint32_t)(((it - 1) >> 1) & 1));
+            load_kv(kt - 1 + nkv, prev_slot);
           }
         }
-        slot = nslot;
-        use = nuse;
+        prev_slot = slot;
+        if (++slot == nkv) slot = 0;
       }
     }
   } else {
@@ -780,28 +802,43 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
       dls[qt] = ok ? P.delta[sbase + qrow] * P.scale : 0.f;
     }
 
-    // dK, dV of key tile kt (complete: its last MMAs were observed) -> global; all EW warps arrive on B_DE
+    // dK, dV of key tile kt (complete: its last MMAs were observed) -> global; all EW warps arrive on B_DE.
+    // M = 64 accumulators: key i of the tile sits in lane (i % 16) of sub-partition i / 16 (dV) and 16 lanes above (dK).
     auto store_dkv = [&](int kt) {
       const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;
-      const bool kactive = quad * 32 < w;
-      uint32_t rk[16], rv[16];
+      const bool kactive = quad * 16 < w;
+      uint32_t r[16];
       if (kactive) {
-        tmem_ld16(tDK + lane_addr + cg * 16, rk);
-        tmem_ld16(tDV + lane_addr + cg * 16, rv);
+        tmem_ld16(tDV + lane_addr + cg * 16, r);
         tmem_ld_wait();
       }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars[B_DE]);
-      const int key = kt * KT + row;
+      const int key = kt * KT + quad * 16 + (lane & 15);
       if (kactive && key < Lk) {
-        store_row16((bf16*)P.dk + ((int64_t)b * Lk + key) * P.lddk + h * D + cg * 16, rk, 1.0f);
-        store_row16((bf16*)P.dv + ((int64_t)b * Lk + key) * P.lddv + h * D + cg * 16, rv, DROP ? keep_scale : 1.0f);
+        const bool is_v = lane < 16;
+        bf16* dst = is_v ? (bf16*)P.dv + ((int64_t)b * Lk + key) * P.lddv : (bf16*)P.dk + ((int64_t)b * Lk + key) * P.lddk;
+        store_row16(dst + h * D + cg * 16, r, (DROP && is_v) ? keep_scale : 1.0f);
       }
     };
 
     const uint32_t a_p = smem_u32(sP) + row * 128, a_ds = smem_u32(sdS) + row * 128, a_mask = smem_u32(sMask);
     const uint32_t swz = (uint32_t)row & 7u;
+    // keep bits of this thread's 16 keys in iteration (kt2, qt2): read one iteration ahead, so that the global-load latency
+    // (~550 cycles per iteration when it sat in front of the S-full wait) is covered by the previous iteration's arithmetic
+    auto keep_bits16 = [&](int kt2, int qt2) -> uint32_t {
+      const int w2 = (lk_pad - kt2 * KT) < KT ? (lk_pad - kt2 * KT) : KT;
+      const int qrow2 = qt2 * TQ + row;
+      if (!DROP || !((qt2 * TQ + quad * 32 < Lq) && cg * 16 < w2)) return 0xFFFFFFFFu;
+      const uint64_t row_lin = (uint64_t)(sbase + qrow2);
+      const int g0 = kt2 * 8 + cg * 2;  // 8-key group of this warp's first key
+      if (P.drop_mask != nullptr)
+        return qrow2 < Lq ? (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(P.drop_mask + (int64_t)row_lin * mask_ld + g0)) : 0u;
+      return attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0, thr) |
+             (attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0 + 1, thr) << 8);
+    };
+    uint32_t bits_next = keep_bits16(0, 0);
     int it = 0;
     for (int kt = 0; kt < n_kt; ++kt) {
       const int w = (lk_pad - kt * KT) < KT ? (lk_pad - kt * KT) : KT;
@@ -809,23 +846,13 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
       const bool plain = !has_mask && (kt * KT + KT <= Lk);  // no additive mask, no padded keys in this tile
 #pragma unroll 1
       for (int qt = 0; qt < n_qt; ++qt, ++it) {
-        const int qrow = qt * TQ + row;
         const bool active = (qt * TQ + quad * 32 < Lq) && cols_live;  // warp-uniform
         const float l2 = qt == 0 ? lse2[0] : (qt == 1 ? lse2[1] : lse2[2]);
         const float dl = qt == 0 ? dls[0] : (qt == 1 ? dls[1] : dls[2]);
-        uint32_t bits = 0xFFFFFFFFu;
-        if (DROP && active) {
-          const uint64_t row_lin = (uint64_t)(sbase + qrow);
-          const int g0 = kt * 8 + cg * 2;  // 8-key group of this warp's first key
-          if (P.drop_mask != nullptr) {
-            bits = qrow < Lq ? (uint32_t)*reinterpret_cast<const uint16_t*>(P.drop_mask + (int64_t)row_lin * mask_ld + g0) : 0u;
-          } else {
-            bits = attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0, thr) |
-                   (attn_keep_bits8(P.drop_seed, P.drop_stream, row_lin, g0 + 1, thr) << 8);
-          }
-        }
+        const uint32_t bits = bits_next;
         uint32_t rs0[16], rd0[16];
-        mbar_wait(&bars[B_SF], (uint32_t)(it & 1));
+        const uint32_t tS = tS0 + (uint32_t)(it & 1) * 128u, tDP = tS + 64u;
+        mbar_wait(&bars[B_SF0 + (it & 1)], (uint32_t)((it >> 1) & 1));
         tcgen05_fence_after();
         if (threadIdx.x == 0) TR(200 + 6 * it);
         if (active) {
@@ -835,7 +862,8 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
         }
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars[B_SE]);
+        if (lane == 0) mbar_arrive(&bars[B_SE0 + (it & 1)]);
+        if (it + 1 < total) bits_next = qt + 1 < n_qt ? keep_bits16(kt, qt + 1) : keep_bits16(kt + 1, 0);
         if (threadIdx.x == 0) TR(201 + 6 * it);
         // the staging buffers of parity it&1 were last read by the accumulate MMAs of iteration it-2
         if (it >= 2) mbar_wait(&bars[B_MD0 + (it & 1)], (uint32_t)(((it - 2) >> 1) & 1));
@@ -875,6 +903,7 @@ __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_con
   }
   tcgen05_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TR(102);
   if (warp == BWD_EW) {
     tcgen05_fence_after();
     tmem_dealloc_n(tmem_base, (uint32_t)A.tmem_cols);

@@ -28,6 +28,6 @@ for _ in range(2): ops.attn_bwd(Q, K, V, out, lse, dout=dout, dq=dq[:, :768], dk
 t = trace()
 nk = ((Lk + 15) // 16 * 16 + 63) // 64
 t0 = t[200]
-print("BWD (relative to first SF seen by EW)")
+print("BWD (relative to first SF seen by EW): kernel entry", t[100] - t0, "prologue done", t[101] - t0, "all warps done", t[102] - t0)
 for it in range(nk * nq):
     print(f" it {it}: ctl sdp(it+1) {t[110+4*it]-t0 if it+1<nk*nq else '-'} PF {t[111+4*it]-t0} mma {t[112+4*it]-t0} | EW: SF {t[200+6*it]-t0} ld+SE {t[201+6*it]-t0} MDwait {t[202+6*it]-t0} compute {t[203+6*it]-t0} PF {t[204+6*it]-t0} dkv {t[205+6*it]-t0 if (it % nq == 0 and it > 0) else '-'}")
