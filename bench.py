@@ -34,6 +34,11 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
+# The ONE JSON line goes to the real stdout; everything else a run prints (the reference's own modules print while they are
+# constructed, m3ae_module.py:133) is sent to stderr so that the driver parses a clean line.
+_STDOUT = sys.stdout
+sys.stdout = sys.stderr
+
 LT, LI, HID, NLAB = 32, 325, 768, 498  # 32 text tokens, 325 image tokens (288 px / 16 + CLS), hidden 768, 498 answers
 FLOPS_FWD_PER_SAMPLE = 42.778e9  # fusion stack forward, algorithmic 2*M*N*K (+attention)
 FLOPS_FWD_BWD_PER_SAMPLE = 128.33e9
@@ -498,7 +503,7 @@ def run_ours(args):
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(sample_b=8, steps=3)
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -621,7 +626,7 @@ def run_decoder(args):
     out = bench_decoder(args, dev)
     out.update({"warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "data": "synthetic (seeded memory [128,359,768], random-init weights)"})
-    print(json.dumps(out), flush=True)
+    print(json.dumps(out), file=_STDOUT, flush=True)
 
 
 def run_reference(args):
@@ -650,7 +655,7 @@ def run_reference(args):
         "config": {"workload": "M3AE VQA-RAD fine-tune step (fwd+bwd), fusion stack 6+6 BertCrossLayer + heads + BCE, 288px / 32 tokens", "per_gpu_batch": B},
         "cpu_baseline": {"value": round(sps, 3), "unit": "samples/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": round(sps, 3), "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }), flush=True)
+    }), file=_STDOUT, flush=True)
 
 
 def main():
