@@ -115,6 +115,54 @@ __device__ __forceinline__ float fast_gelu_both(float x, float& grad) {
   return fmaf(-fabsf(x), h, fmaxf(x, 0.f));
 }
 
+// ---- packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2 on sm_100): two elements per FMA-pipe instruction.  The FMA pipe takes
+// one warp instruction every 2 cycles per scheduler, and the GEMM epilogues are bound by exactly that pipe.
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  asm("{\n.reg .b64 ra, rb, rc, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmov.b64 rc, {%6, %7};\n"
+      "fma.rn.f32x2 rd, ra, rb, rc;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void mul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nmul.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n.reg .b64 ra, rb, rd;\nmov.b64 ra, {%2, %3};\nmov.b64 rb, {%4, %5};\nadd.rn.f32x2 rd, ra, rb;\nmov.b64 {%0, %1}, rd;\n}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+// Two elements of fast_gelu_both at once: x0, x1 are replaced by gelu(x), g0, g1 receive gelu'(x).  Same formulas and
+// constants as the scalar version (13 packed FMA-pipe instructions + 4 MUFU + 6 ALU per PAIR).
+__device__ __forceinline__ void fast_gelu_both2(float& x0, float& x1, float& g0, float& g1) {
+  const float n0 = __uint_as_float(__float_as_uint(x0) | 0x80000000u), n1 = __uint_as_float(__float_as_uint(x1) | 0x80000000u);  // -|x|
+  constexpr float C = -0.47047f * 0.70710678118654752f;
+  float d0, d1;
+  fma2(d0, d1, n0, n1, C, C, 1.0f, 1.0f);  // 1 + p|x|/sqrt(2)
+  const float t0 = rcp_approx(d0), t1 = rcp_approx(d1);
+  float p0, p1;
+  fma2(p0, p1, t0, t1, 0.5f * 0.7478556f, 0.5f * 0.7478556f, 0.5f * -0.0958798f, 0.5f * -0.0958798f);
+  fma2(p0, p1, p0, p1, t0, t1, 0.5f * 0.3480242f, 0.5f * 0.3480242f);
+  float q0, q1;
+  mul2(q0, q1, x0, x1, x0, x1);
+  mul2(q0, q1, q0, q1, -0.72134752044448170f, -0.72134752044448170f);
+  const float e0 = ex2_approx(q0), e1 = ex2_approx(q1);  // exp(-x^2/2)
+  mul2(p0, p1, p0, p1, t0, t1);
+  float h0, h1;
+  mul2(h0, h1, p0, p1, e0, e1);  // 0.5 erfc(|x|/sqrt 2)
+  float c0, c1;
+  fma2(c0, c1, h0, h1, -1.0f, -1.0f, 0.5f, 0.5f);
+  c0 = copysignf(c0, x0);
+  c1 = copysignf(c1, x1);
+  add2(c0, c1, c0, c1, 0.5f, 0.5f);  // Phi(x)
+  float k0, k1;
+  mul2(k0, k1, x0, x1, 0.39894228040143268f, 0.39894228040143268f);
+  fma2(g0, g1, k0, k1, e0, e1, c0, c1);
+  const float r0 = fmaxf(x0, 0.f), r1 = fmaxf(x1, 0.f);
+  fma2(x0, x1, n0, n1, h0, h1, r0, r1);
+}
+
 // QuickGELU of the CLIP visual tower (reference clip_model.py:36-38): x * sigmoid(1.702 x).
 __device__ __forceinline__ float quick_gelu(float x) { return x / (1.0f + __expf(-1.702f * x)); }
 __device__ __forceinline__ float quick_gelu_grad(float x) {
@@ -290,16 +338,19 @@ __device__ __forceinline__ void epilogue_apply(const EpiDev& e, int64_t row, int
   if (e.drop_p > 0.0f) {
     const float inv = drop_keep_scale(e.drop_p);
     uint32_t bits = 0;
-    const bool ready = NV == 32 && e.drop_bits != nullptr && e.drop_bits_ready;
-    const uint32_t cached = ready ? e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] : 0u;
+    // keep-bit cache: one 32-bit word per row and 32 columns; a 16-column caller owns one 16-bit half of a word
+    const bool ready = (NV == 32 || NV == 16) && e.drop_bits != nullptr && e.drop_bits_ready;
+    uint16_t* const half_bits = reinterpret_cast<uint16_t*>(e.drop_bits) + 2 * row * e.drop_bits_ld + (col >> 4);
+    const uint32_t cached = !ready ? 0u : NV == 32 ? e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] : (uint32_t)*half_bits;
 #pragma unroll
     for (int j = 0; j < NV; ++j) if (j < n_valid) {
       const bool keep = ready ? ((cached >> (j & 31)) & 1u) != 0u
                               : dropout_keep(e.drop_seed, e.drop_stream, (uint64_t)(row * e.ldo + col + j), e.drop_p);
       acc[j] = keep ? acc[j] * inv : 0.0f;
-      if (NV == 32) bits |= (keep ? 1u : 0u) << (j & 31);
+      if (NV == 32 || NV == 16) bits |= (keep ? 1u : 0u) << (j & 31);
     }
     if (NV == 32 && e.drop_bits != nullptr && !ready) e.drop_bits[row * (e.drop_bits_ld) + (col >> 5)] = bits;
+    if (NV == 16 && e.drop_bits != nullptr && !ready) *half_bits = (uint16_t)bits;
   }
   if (e.residual) {
 #pragma unroll
@@ -474,6 +525,15 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
         "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+// 32 lanes x 16 consecutive fp32 columns -> 16 registers per thread
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr)
       : "memory");
 }

@@ -29,15 +29,16 @@ constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4..11 epilogue
-constexpr int NUM_EPI_WARPS = 8;
+constexpr int NUM_THREADS = 640;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4..19 epilogue
+constexpr int NUM_EPI_WARPS = 16;
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
-// Epilogue staging: every epilogue warp owns 4 buffers of 32 rows x 32 bf16 (64-byte rows, SWIZZLE_64B):
-// in[0..1] (TMA-loaded residual / pre-activation, double-buffered) and out[0..1] (TMA-stored results).
+// Epilogue staging: every epilogue warp owns 2 buffers of 32 rows x 32 bf16 (64-byte rows, SWIZZLE_64B), one per
+// 32-column chunk of its 64 accumulator columns: the TMA-loaded residual / saved act' tile is overwritten in place by the
+// result, which a TMA store then drains.  The split-K path uses the same 4 KB as one 32x32 fp32 tile.
 constexpr int EPI_BUF_BYTES = 32 * 64;
-constexpr int EPI_WARP_BYTES = 4 * EPI_BUF_BYTES;
+constexpr int EPI_WARP_BYTES = 2 * EPI_BUF_BYTES;
 constexpr int EPI_BYTES = NUM_EPI_WARPS * EPI_WARP_BYTES;
-constexpr int BIAS_BYTES = NUM_EPI_WARPS * 128 * 4;  // every epilogue warp stages the 128 bias values of its column half
+constexpr int BIAS_BYTES = NUM_EPI_WARPS * 64 * 4;  // every epilogue warp stages the 64 bias values of its column group
 // CTAS = 1: one CTA computes a 128x256 tile (tcgen05.mma.cta_group::1).  CTAS = 2: a CTA PAIR (cluster of 2 on one TPC)
 // computes a 256x256 tile with tcgen05.mma.cta_group::2 — each CTA stages its own 128 rows of A and HALF of B
 // (128 of the 256 columns), so the operand bytes an SM reads from shared memory per MMA drop from 12 KB to 8 KB
@@ -262,12 +263,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     }
   } else if (warp >= 4) {
     // ===================== epilogue warps =====================
+    // 16 warps: quad = TMEM lane quadrant (32 accumulator rows), cgrp = 64-column group of the 256-column accumulator.
+    // (Round 1 ran 8 warps x 128 columns at 168 registers: two warps per scheduler could not cover their own dependency
+    // latency and the scalar erfc polynomial alone filled the FMA pipe for longer than a K = 768 tile's MMAs take —
+    // tensor pipe 31-41 % active on the epilogue-heavy stages, profiles/r1_ncu_gemm_full_v19_final.txt.)
     const int e = warp - 4;
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    const int half = e >> 2;    // which 128-column half of the accumulator
+    const int cgrp = e >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t iph0 = 0, iph1 = 0;  // phases of this warp's two in-buffer barriers
+    uint8_t* const wbuf = epi_smem + e * EPI_WARP_BYTES;
+    uint64_t* const ibar = in_bar + 2 * e;
+    float* const sbias = bias_smem + e * 64;
     auto release_acc = [&](int a) {  // this warp is done reading accumulator `a`
       if (CTAS == 2 && rank != 0) mbar_arrive_cluster(&tmem_empty[a], 0);
       else mbar_arrive(&tmem_empty[a]);
@@ -277,35 +285,37 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       const TcProblem& q = P.p[u.p];
       const EpiDev& epi = q.epi;
       const int tile_row0 = u.m_blk * TILE_M + rank * BM;  // first output row of this CTA's 128-lane accumulator
+      const int row0 = tile_row0 + quad * 32;
+      const int col_base = u.n_blk * BN + cgrp * 64;
+      const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + cgrp * 64);
       if (q.epi_fast == 2) {
-        // ---- fp32 accumulate (out += alpha * acc): 32x32 fp32 tiles staged in swizzled smem, added into global memory
-        //      by TMA reductions.  One bulk reduction replaces 1024 scattered RED.ADD.F32 (lane = row: 32 lines/instr).
-        uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
-        const int row0 = tile_row0 + quad * 32;
-        const int col_base = u.n_blk * BN + half * 128;
-        const int nchunks = (row0 < q.M) ? min(4, (q.N - col_base + 31) / 32) : 0;
+        // ---- fp32 accumulate (out += alpha * acc): one 32x32 fp32 tile staged in swizzled smem (the warp's whole 4 KB),
+        //      added into global memory by a TMA reduction.  One bulk reduction replaces 1024 scattered RED.ADD.F32.
+        const int nchunks = (row0 < q.M) ? min(2, (q.N - col_base + 31) / 32) : 0;
         const float alpha = epi.alpha;
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
 #pragma unroll 1
         for (int c = 0; c < nchunks; ++c) {
-          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 128 + c * 32);
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(taddr, r);
+          uint32_t r0[16], r1[16];
+          tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 32), r0);
+          tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 32 + 16), r1);
           tmem_ld_wait();
-          uint8_t* buf = wbuf + (c & 1) * (2 * EPI_BUF_BYTES);
-          if (lane == 0) tma_store_wait_read<1>();
+          if (lane == 0) tma_store_wait_read<0>();  // the previous reduction has finished reading the tile
           __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {  // SWIZZLE_128B: 16-byte chunk ^= row % 8
-            const float4 w = make_float4(__uint_as_float(r[4 * j]) * alpha, __uint_as_float(r[4 * j + 1]) * alpha,
-                                         __uint_as_float(r[4 * j + 2]) * alpha, __uint_as_float(r[4 * j + 3]) * alpha);
-            *reinterpret_cast<float4*>(buf + lane * 128 + (((uint32_t)j ^ (uint32_t)(lane & 7)) << 4)) = w;
+          for (int j = 0; j < 4; ++j) {  // SWIZZLE_128B: 16-byte chunk ^= row % 8
+            const float4 w0 = make_float4(__uint_as_float(r0[4 * j]) * alpha, __uint_as_float(r0[4 * j + 1]) * alpha,
+                                          __uint_as_float(r0[4 * j + 2]) * alpha, __uint_as_float(r0[4 * j + 3]) * alpha);
+            const float4 w1 = make_float4(__uint_as_float(r1[4 * j]) * alpha, __uint_as_float(r1[4 * j + 1]) * alpha,
+                                          __uint_as_float(r1[4 * j + 2]) * alpha, __uint_as_float(r1[4 * j + 3]) * alpha);
+            *reinterpret_cast<float4*>(wbuf + lane * 128 + (((uint32_t)j ^ (uint32_t)(lane & 7)) << 4)) = w0;
+            *reinterpret_cast<float4*>(wbuf + lane * 128 + (((uint32_t)(j + 4) ^ (uint32_t)(lane & 7)) << 4)) = w1;
           }
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
-            tma_reduce_add_2d(&q.map_out, buf, col_base + c * 32, row0);
+            tma_reduce_add_2d(&q.map_out, wbuf, col_base + c * 32, row0);
             tma_store_commit();
           }
         }
@@ -313,36 +323,42 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         __syncwarp();
         if (lane == 0) {
           release_acc(acc);
-          tma_store_wait_read<0>();  // the next unit may be a bf16 problem whose TMA loads land in these bytes
+          tma_store_wait_read<0>();  // the next unit may be a bf16 problem that writes these bytes after a wait_read<1>
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         continue;
       }
       if (q.epi_fast) {
-        // ---- TMA-staged bf16 epilogue: coalesced in/out through swizzled smem sub-tiles of 32 rows x 32 columns
-        uint8_t* wbuf = epi_smem + e * EPI_WARP_BYTES;
-        uint64_t* ibar = in_bar + 2 * e;
-        const int row0 = tile_row0 + quad * 32;
-        const int col_base = u.n_blk * BN + half * 128;
-        const int nchunks = min(4, (q.N - col_base + 31) / 32);  // <= 0: this warp's half lies outside N
+        // ---- TMA-staged bf16 epilogue: coalesced in/out through swizzled smem sub-tiles of 32 rows x 32 columns.
+        // Chunk c (32 columns) stages its input (residual / saved act') AND its output in buf[c]: a thread reads and
+        // writes only its own row, so the result overwrites the input in place.  With a second (aux) output every chunk
+        // uses buf[0] for in/out and buf[1] for the aux tile.
+        const int nchunks = min(2, (q.N - col_base + 31) / 32);  // <= 0: this warp's columns lie outside N
         const int64_t row = (int64_t)row0 + lane;
         const uint32_t sw = (uint32_t)((lane >> 1) & 3);           // SWIZZLE_64B: 16-byte chunk ^= (row/2)%4
         const bool aux = epi.aux_out != nullptr;
-        if (q.has_in && lane == 0 && nchunks > 0) {
+        const bool aux_grad = aux && epi.aux_is_grad;
+        if (q.has_in && nchunks > 0 && lane == 0) {
+          tma_store_wait_read<0>();  // the previous unit's stores have finished reading both buffers
           mbar_expect_tx(&ibar[0], EPI_BUF_BYTES);
           tma_load_2d(wbuf, &q.map_in, &ibar[0], col_base, row0);
+          if (!aux && nchunks > 1) {
+            mbar_expect_tx(&ibar[1], EPI_BUF_BYTES);
+            tma_load_2d(wbuf + EPI_BUF_BYTES, &q.map_in, &ibar[1], col_base + 32, row0);
+          }
         }
-        float* sbias = bias_smem + e * 128;
         if (epi.bias) {  // issued before the accumulator wait: the global-load latency hides behind the tile's MMAs
-          const int c4 = col_base + 4 * lane;
-          const float4 b4 = (c4 < q.N) ? __ldg(reinterpret_cast<const float4*>(epi.bias + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-          *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
+          if (lane < 16) {
+            const int c4 = col_base + 4 * lane;
+            const float4 b4 = (c4 < q.N) ? __ldg(reinterpret_cast<const float4*>(epi.bias + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
+          }
           __syncwarp();
         }
-        uint32_t cached_bits[4] = {0u, 0u, 0u, 0u};
+        uint32_t cached_bits[2] = {0u, 0u};
         if (epi.drop_p > 0.f && epi.drop_bits_ready && row < q.M) {
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < 2; ++c)
             if (c < nchunks) cached_bits[c] = __ldg(epi.drop_bits + row * epi.drop_bits_ld + ((col_base + c * 32) >> 5));
         }
         mbar_wait(&tmem_full[acc], acc_phase);
@@ -350,160 +366,149 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
 #pragma unroll 1
         for (int c = 0; c < nchunks; ++c) {
           const int col = col_base + c * 32;
-          if (q.has_in && lane == 0 && c + 1 < nchunks) {
-            mbar_expect_tx(&ibar[(c + 1) & 1], EPI_BUF_BYTES);
-            tma_load_2d(wbuf + ((c + 1) & 1) * EPI_BUF_BYTES, &q.map_in, &ibar[(c + 1) & 1], col + 32, row0);
-          }
-          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 128 + c * 32);
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(taddr, r);
-          tmem_ld_wait();
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (epi.bias) {
-            const float4* b4 = reinterpret_cast<const float4*>(sbias + c * 32);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 t4 = b4[j];
-              v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
+          const int bi = aux ? 0 : c;
+          uint8_t* const iobuf = wbuf + bi * EPI_BUF_BYTES;
+          uint8_t* const abuf = wbuf + EPI_BUF_BYTES;
+          if (lane == 0) {
+            if (aux) {
+              if (c > 0 || !q.has_in) tma_store_wait_read<0>();
+              if (q.has_in && c > 0) {  // (input + two outputs: no prefetch, the in/out buffer is shared by both chunks)
+                mbar_expect_tx(&ibar[0], EPI_BUF_BYTES);
+                tma_load_2d(wbuf, &q.map_in, &ibar[0], col, row0);
+              }
+            } else if (!q.has_in) {
+              tma_store_wait_read<1>();  // the store that last read buf[c] (this chunk of the previous unit) is done
             }
           }
-          uint8_t* obuf = wbuf + (2 + (aux ? 0 : (c & 1))) * EPI_BUF_BYTES;
-          uint8_t* abuf = wbuf + 3 * EPI_BUF_BYTES;
-          // previous TMA stores must have finished READING the staging buffers we are about to overwrite
-          if (lane == 0) { if (aux) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
           __syncwarp();
-          const bool aux_grad = aux && epi.aux_is_grad;
-          if (aux && !aux_grad) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 w;
-              w.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]); w.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
-              w.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]); w.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
-              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
-            }
-          }
-          if (aux_grad && epi.act == M3AE_ACT_GELU) {
-            // aux := gelu'(v): the cdf/pdf terms are shared with the activation itself (one extra FMA per element)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float d[8];
-#pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                v[8 * j + k] = fast_gelu_both(v[8 * j + k], d[k]);
-              }
-              uint4 w;
-              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
-              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
-              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
-            }
-          } else if (aux_grad && epi.act == M3AE_ACT_QUICKGELU) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float d[8];
-#pragma unroll
-              for (int k = 0; k < 8; ++k) v[8 * j + k] = fast_quick_gelu_both(v[8 * j + k], d[k]);
-              uint4 w;
-              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
-              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
-              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
-            }
-          } else if (aux_grad) {
-            const bool relu = epi.act == M3AE_ACT_RELU;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float d[8];
-#pragma unroll
-              for (int k = 0; k < 8; ++k) {
-                d[k] = (!relu || v[8 * j + k] > 0.f) ? 1.f : 0.f;
-                if (relu) v[8 * j + k] = fmaxf(v[8 * j + k], 0.f);
-              }
-              uint4 w;
-              w.x = pack_bf16x2(d[0], d[1]); w.y = pack_bf16x2(d[2], d[3]);
-              w.z = pack_bf16x2(d[4], d[5]); w.w = pack_bf16x2(d[6], d[7]);
-              *reinterpret_cast<uint4*>(abuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
-            }
-          } else if (epi.act == M3AE_ACT_GELU) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fast_gelu(v[j]);
-          } else if (epi.act == M3AE_ACT_RELU) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-          } else if (epi.act == M3AE_ACT_QUICKGELU) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fast_quick_gelu(v[j]);
-          } else if (epi.act == M3AE_ACT_TANH) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
-          }
-          float in[32];
           if (q.has_in) {
-            if (c & 1) { mbar_wait(&ibar[1], iph1); iph1 ^= 1; } else { mbar_wait(&ibar[0], iph0); iph0 ^= 1; }
-            const uint8_t* ib = wbuf + (c & 1) * EPI_BUF_BYTES;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint4 w = *reinterpret_cast<const uint4*>(ib + lane * 64 + (((uint32_t)j ^ sw) << 4));
-              float2 f;
-              f = unpack_bf16x2(w.x); in[8 * j + 0] = f.x; in[8 * j + 1] = f.y;
-              f = unpack_bf16x2(w.y); in[8 * j + 2] = f.x; in[8 * j + 3] = f.y;
-              f = unpack_bf16x2(w.z); in[8 * j + 4] = f.x; in[8 * j + 5] = f.y;
-              f = unpack_bf16x2(w.w); in[8 * j + 6] = f.x; in[8 * j + 7] = f.y;
-            }
-            __syncwarp();  // all lanes done with in[c&1] before lane 0 re-arms it two chunks later
+            if (bi) { mbar_wait(&ibar[1], iph1); iph1 ^= 1; } else { mbar_wait(&ibar[0], iph0); iph0 ^= 1; }
           }
-          if (epi.dact != M3AE_ACT_NONE) {
-            if (epi.aux_is_grad) {
+          uint32_t keep_word = 0;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= in[j];
-            } else if (epi.dact == M3AE_ACT_GELU) {
+          for (int hh = 0; hh < 2; ++hh) {
+            uint32_t r[16];
+            tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 32 + hh * 16), r);
+            tmem_ld_wait();
+            float v[16];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= fast_gelu_grad(in[j]);
-            } else if (epi.dact != M3AE_ACT_RELU) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= act_exact_grad(epi.dact, in[j]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = in[j] > 0.f ? v[j] : 0.f;
-            }
-          }
-          if (epi.drop_p > 0.f) {
-            const float inv = drop_keep_scale(epi.drop_p);
-            if (epi.drop_bits_ready) {
-              // keep bits generated ahead of the GEMM (m3ae_dropout_bits): one 4-byte load per thread and chunk, issued
-              // before the accumulator wait (cached_bits), instead of 4 Philox evaluations in the issue-bound epilogue
-              const uint32_t bits = c == 0 ? cached_bits[0] : c == 1 ? cached_bits[1] : c == 2 ? cached_bits[2] : cached_bits[3];
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = ((bits >> j) & 1u) ? v[j] * inv : 0.f;
-            } else {
-              const uint32_t thr15 = drop_thr15(epi.drop_p);
-              const uint64_t e0 = (uint64_t)(row * epi.ldo + col);  // multiple of 8 (ldo % 8 == 0, col % 32 == 0)
-              uint32_t bits = 0;
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+            if (epi.bias) {
+              const float4* b4 = reinterpret_cast<const float4*>(sbias + c * 32 + hh * 16);
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const uint32_t m8 = dropout_keep8(epi.drop_seed, epi.drop_stream, e0 + 8 * j, thr15);
-                bits |= m8 << (8 * j);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) v[8 * j + k] = ((m8 >> k) & 1u) ? v[8 * j + k] * inv : 0.f;
+                const float4 t4 = b4[j];
+                v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
               }
-              if (epi.drop_bits != nullptr && row < q.M) epi.drop_bits[row * epi.drop_bits_ld + (col >> 5)] = bits;
             }
-          }
-          if (q.in_is_residual) {
+            const uint32_t o0 = (((uint32_t)(2 * hh) ^ sw) << 4), o1 = (((uint32_t)(2 * hh + 1) ^ sw) << 4);
+            auto put8 = [&](uint8_t* buf, uint32_t off, const float* f) {
+              uint4 w;
+              w.x = pack_bf16x2(f[0], f[1]); w.y = pack_bf16x2(f[2], f[3]);
+              w.z = pack_bf16x2(f[4], f[5]); w.w = pack_bf16x2(f[6], f[7]);
+              *reinterpret_cast<uint4*>(buf + lane * 64 + off) = w;
+            };
+            if (aux && !aux_grad) {
+              put8(abuf, o0, v);
+              put8(abuf, o1, v + 8);
+            }
+            if (aux_grad && epi.act == M3AE_ACT_GELU) {
+              // aux := gelu'(v): the cdf/pdf terms are shared with the activation itself; two elements per FFMA2
+              float d[16];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += in[j];
-          }
+              for (int j = 0; j < 16; j += 2) fast_gelu_both2(v[j], v[j + 1], d[j], d[j + 1]);
+              put8(abuf, o0, d);
+              put8(abuf, o1, d + 8);
+            } else if (aux_grad && epi.act == M3AE_ACT_QUICKGELU) {
+              float d[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 w;
-            w.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]); w.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
-            w.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]); w.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
-            *reinterpret_cast<uint4*>(obuf + lane * 64 + (((uint32_t)j ^ sw) << 4)) = w;
+              for (int j = 0; j < 16; ++j) v[j] = fast_quick_gelu_both(v[j], d[j]);
+              put8(abuf, o0, d);
+              put8(abuf, o1, d + 8);
+            } else if (aux_grad) {
+              const bool relu = epi.act == M3AE_ACT_RELU;
+              float d[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                d[j] = (!relu || v[j] > 0.f) ? 1.f : 0.f;
+                if (relu) v[j] = fmaxf(v[j], 0.f);
+              }
+              put8(abuf, o0, d);
+              put8(abuf, o1, d + 8);
+            } else if (epi.act == M3AE_ACT_GELU) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 2) {
+                float d0, d1;  // (unused: the compiler drops the gradient half)
+                fast_gelu_both2(v[j], v[j + 1], d0, d1);
+              }
+            } else if (epi.act == M3AE_ACT_RELU) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+            } else if (epi.act == M3AE_ACT_QUICKGELU) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = fast_quick_gelu(v[j]);
+            } else if (epi.act == M3AE_ACT_TANH) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = tanhf(v[j]);
+            }
+            float in[16];
+            if (q.has_in) {
+              const uint4 wa = *reinterpret_cast<const uint4*>(iobuf + lane * 64 + o0);
+              const uint4 wb = *reinterpret_cast<const uint4*>(iobuf + lane * 64 + o1);
+              float2 f;
+              f = unpack_bf16x2(wa.x); in[0] = f.x; in[1] = f.y;
+              f = unpack_bf16x2(wa.y); in[2] = f.x; in[3] = f.y;
+              f = unpack_bf16x2(wa.z); in[4] = f.x; in[5] = f.y;
+              f = unpack_bf16x2(wa.w); in[6] = f.x; in[7] = f.y;
+              f = unpack_bf16x2(wb.x); in[8] = f.x; in[9] = f.y;
+              f = unpack_bf16x2(wb.y); in[10] = f.x; in[11] = f.y;
+              f = unpack_bf16x2(wb.z); in[12] = f.x; in[13] = f.y;
+              f = unpack_bf16x2(wb.w); in[14] = f.x; in[15] = f.y;
+            }
+            if (epi.dact != M3AE_ACT_NONE) {
+              if (epi.aux_is_grad) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] *= in[j];
+              } else if (epi.dact == M3AE_ACT_GELU) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] *= fast_gelu_grad(in[j]);
+              } else if (epi.dact != M3AE_ACT_RELU) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] *= act_exact_grad(epi.dact, in[j]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = in[j] > 0.f ? v[j] : 0.f;
+              }
+            }
+            if (epi.drop_p > 0.f) {
+              const float inv = drop_keep_scale(epi.drop_p);
+              uint32_t bits16;
+              if (epi.drop_bits_ready) {
+                // keep bits generated ahead of the GEMM (m3ae_dropout_bits), loaded before the accumulator wait
+                bits16 = ((c == 0 ? cached_bits[0] : cached_bits[1]) >> (16 * hh)) & 0xFFFFu;
+              } else {
+                const uint32_t thr15 = drop_thr15(epi.drop_p);
+                const uint64_t e0 = (uint64_t)(row * epi.ldo + col + 16 * hh);  // multiple of 8 (ldo % 8 == 0)
+                bits16 = dropout_keep8(epi.drop_seed, epi.drop_stream, e0, thr15) |
+                         (dropout_keep8(epi.drop_seed, epi.drop_stream, e0 + 8, thr15) << 8);
+                keep_word |= bits16 << (16 * hh);
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = ((bits16 >> j) & 1u) ? v[j] * inv : 0.f;
+            }
+            if (q.in_is_residual) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += in[j];
+            }
+            put8(iobuf, o0, v);
+            put8(iobuf, o1, v + 8);
           }
+          if (epi.drop_p > 0.f && !epi.drop_bits_ready && epi.drop_bits != nullptr && row < q.M)
+            epi.drop_bits[row * epi.drop_bits_ld + (col >> 5)] = keep_word;
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&q.map_out, obuf, col, row0);
+            tma_store_2d(&q.map_out, iobuf, col, row0);
             if (aux) tma_store_2d(&q.map_aux, abuf, col, row0);
             tma_store_commit();
           }
@@ -514,35 +519,35 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         continue;
       }
+      // ---- generic per-element epilogue (odd N, fp32 / atomically accumulated outputs): 16 columns at a time
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
-      const int64_t row = (int64_t)tile_row0 + quad * 32 + lane;
+      const int64_t row = (int64_t)row0 + lane;
       const bool row_ok = row < q.M;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
-        const int col = u.n_blk * BN + half * 128 + c * 32;
+        const int col = col_base + c * 16;
         if (col >= q.N) break;  // warp-uniform
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 128 + c * 32);
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr, r);
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 16), r);
         tmem_ld_wait();
         if (row_ok) {
-          float v[32];
+          float v[16];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          const int n_valid = min(32, q.N - col);
-          epilogue_apply<32>(epi, row, col, n_valid, v);
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          const int n_valid = min(16, q.N - col);
+          epilogue_apply<16>(epi, row, col, n_valid, v);
           const size_t o = (size_t)(row * epi.ldo + col);
           if (epi.accumulate) {
             float* out = (float*)epi.out + o;
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
+            for (int j = 0; j < 16; ++j)
               if (j < n_valid) atomicAdd(out + j, v[j]);
           } else if (epi.out_dtype == M3AE_BF16) {
             bf16* out = (bf16*)epi.out + o;
-            if (n_valid == 32 && (((uintptr_t)out) & 15) == 0) {
+            if (n_valid == 16 && (((uintptr_t)out) & 15) == 0) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < 2; ++j) {
                 uint4 w;
                 w.x = pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
                 w.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
@@ -552,17 +557,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
               }
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < 16; ++j)
                 if (j < n_valid) out[j] = __float2bfloat16_rn(v[j]);
             }
           } else {
             float* out = (float*)epi.out + o;
-            if (n_valid == 32 && (((uintptr_t)out) & 15) == 0) {
+            if (n_valid == 16 && (((uintptr_t)out) & 15) == 0) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) ((float4*)out)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              for (int j = 0; j < 4; ++j) ((float4*)out)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < 16; ++j)
                 if (j < n_valid) out[j] = v[j];
             }
           }
