@@ -266,8 +266,10 @@ int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* tabl
 int m3ae_set_attention_backend(int32_t backend);
 /* Test hook: 1 = force the generic per-element GEMM epilogue (cross-checks the TMA-staged one), 0 = auto. */
 int m3ae_set_gemm_epilogue(int32_t generic);
-/* tcgen05 GEMM tile mode: 0 = auto (CTA pairs, tcgen05.mma.cta_group::2 on 256x256 tiles, unless every problem of the
- * launch has M <= 128), 1 = always one CTA per 128x256 tile, 2 = always CTA pairs.  Results are identical. */
+/* tcgen05 GEMM tile mode: 0 = auto (clusters of two CTA pairs — tcgen05.mma.cta_group::2 on 256x256 tiles, the operand
+ * tile the two pairs share fetched once and TMA-multicast — unless every problem of the launch has M <= 128),
+ * 1 = always one CTA per 128x256 tile, 2 = one CTA pair per cluster (no multicast), 3 = always two pairs per cluster.
+ * Results are identical.  Process-global test / benchmarking hook: not synchronised with concurrent launches. */
 int m3ae_set_gemm_cta_pair(int32_t mode);
 /* Test hook: 1 = m3ae_layernorm_bwd loads rows through registers only (cross-checks the cp.async.bulk staging ring), 0 = auto. */
 int m3ae_set_layernorm_bwd_staging(int32_t registers_only);

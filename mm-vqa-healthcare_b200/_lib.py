@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libm3ae_b200.so")
+# M3AE_B200_LIB: developer hook for same-box A/B timing of two builds of the library (tools/ab/); unset in every test and bench record
+LIB_PATH = os.environ.get("M3AE_B200_LIB") or os.path.join(_HERE, "libm3ae_b200.so")
 
 F32, BF16 = 0, 1
 ACT_NONE, ACT_GELU, ACT_RELU, ACT_QUICKGELU, ACT_TANH = 0, 1, 2, 3, 4

@@ -131,7 +131,7 @@ int m3ae_set_gemm_epilogue(int32_t generic) { force_generic_epilogue = generic !
 /* Test hook: 1 = LayerNorm backward loads rows through registers only (cross-checks the bulk-copy ring), 0 = auto. */
 int m3ae_set_layernorm_bwd_staging(int32_t registers_only) { ln_bwd_force_registers = registers_only != 0; return M3AE_OK; }
 int m3ae_set_gemm_cta_pair(int32_t mode) {
-  M3AE_CHECK(mode >= 0 && mode <= 2, M3AE_ERR_INVALID, "m3ae_set_gemm_cta_pair: mode %d not in {0 auto, 1 single CTA, 2 CTA pair}", mode);
+  M3AE_CHECK(mode >= 0 && mode <= 3, M3AE_ERR_INVALID, "m3ae_set_gemm_cta_pair: mode %d not in {0 auto, 1 single CTA, 2 CTA pair, 3 two pairs with operand multicast}", mode);
   gemm_cta_pair_mode = mode;
   return M3AE_OK;
 }

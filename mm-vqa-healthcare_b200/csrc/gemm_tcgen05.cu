@@ -29,7 +29,13 @@ constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 640;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4..19 epilogue
+// Warp roles: 0..15 epilogue, 16 TMA producer, 17 MMA issuer, 18 TMEM allocator, 19 idle.  The control warps carry the
+// HIGHEST warp ids on purpose: a scheduler picks the eligible warp with the highest id first, and epilogue warps polling an
+// mbarrier are always eligible — with the producer and the MMA issuer at ids 0 and 1 the spinning epilogue warps of their
+// schedulers kept taking the issue slot (MMA issuer found its operands ready in 95 % of its waits, yet the tensor pipe
+// was only 60 % active: profiles/r2_ncu_gemm_full_16w.txt).
+constexpr int NUM_THREADS = 640;
+constexpr int WARP_TMA = 16, WARP_MMA = 17, WARP_ALLOC = 18;
 constexpr int NUM_EPI_WARPS = 16;
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 // Epilogue staging: every epilogue warp owns 2 buffers of 32 rows x 32 bf16 (64-byte rows, SWIZZLE_64B), one per
@@ -38,20 +44,35 @@ constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 constexpr int EPI_BUF_BYTES = 32 * 64;
 constexpr int EPI_WARP_BYTES = 2 * EPI_BUF_BYTES;
 constexpr int EPI_BYTES = NUM_EPI_WARPS * EPI_WARP_BYTES;
-constexpr int BIAS_BYTES = NUM_EPI_WARPS * 64 * 4;  // every epilogue warp stages the 64 bias values of its column group
+constexpr int BIAS_BYTES = 2 * 4 * 64 * 4;  // per accumulator parity and 64-column group: the tile's bias values (the four
+                                           // warps of a column group write the same values)
 // CTAS = 1: one CTA computes a 128x256 tile (tcgen05.mma.cta_group::1).  CTAS = 2: a CTA PAIR (cluster of 2 on one TPC)
 // computes a 256x256 tile with tcgen05.mma.cta_group::2 — each CTA stages its own 128 rows of A and HALF of B
 // (128 of the 256 columns), so the operand bytes an SM reads from shared memory per MMA drop from 12 KB to 8 KB
 // (96 -> 64 B/clk against the 128 B/clk an SM can deliver) and a stage shrinks from 48 KB to 32 KB (4 stages instead of 3).
-template <int CTAS>
+// CL = 4 (opt-in, m3ae_set_gemm_cta_pair(3)): a cluster of TWO CTA pairs.  Both pairs work on neighbouring tiles that share
+// one operand (the B tile when the pairs are stacked along M, the A tile when they sit side by side along N); every CTA
+// fetches HALF of its share of that operand and TMA-multicasts it to the CTA of the same rank in the other pair: 96 KB
+// of L2 reads per 16.8 MFLOP instead of 64 KB per 8.4 MFLOP (ncu: 774 MB of TMA loads for 37 MB of operands on the
+// FFN-up GEMM, 8.4 TB/s).  Measured: no gain — see the launcher.
+template <int CL>
 struct Cfg {
+  static constexpr int CTAS = CL >= 2 ? 2 : 1;   // CTAs per output tile (cta_group)
+  static constexpr int NPAIR = CL / CTAS;        // tiles a cluster works on at a time
   static constexpr int TILE_M = BM * CTAS;
   static constexpr int B_ROWS = BN / CTAS;  // B rows (output columns) staged per CTA
   static constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int STAGES = CTAS == 1 ? 3 : 4;
+#ifndef M3AE_GEMM_STAGES
+#define M3AE_GEMM_STAGES 5
+#endif
+  // Operand bytes in flight per SM = (STAGES - 1) x 32 KB; at 64 B/clk per SM (tensor pipe saturated) and ~1500-2000
+  // cycles of loaded L2 latency, Little's law asks for 96-128 KB.  Measured 3 / 4 / 5 stages (profiles/r2_gemm_stages_ab.txt):
+  // K = 3072 forward 1011 / 1123 / 1175 TFLOP/s, split-K wgrad 1164 / 1333 / 1377; the K = 768 shapes do not move.
+  static constexpr int STAGES = CTAS == 1 ? 3 : M3AE_GEMM_STAGES;
   static constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + 1024 /*align slack*/ + NUM_BARS * 8 + 16;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + NUM_BARS * 8 + 16;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 constexpr int MAX_GROUP = 4;
 
@@ -61,6 +82,9 @@ struct alignas(64) TcProblem {
   CUtensorMap map_out;   // fast epilogue only: bf16 [M,N], box 32x32, SWIZZLE_64B
   CUtensorMap map_aux;   // aux_out (same geometry as out)
   CUtensorMap map_in;    // residual or aux_in
+  int share;             // CL = 4 only: 1 = the cluster's pairs are stacked along M and share (multicast) the B tile,
+                         //              2 = side by side along N, sharing the A tile.  tiles_m / tiles_n then count
+                         //              two-tile super tiles along that dimension.
   int epi_fast;          // 1: TMA-staged bf16 epilogue; 2: fp32 accumulate through TMA reduce-add tiles (split-K wgrad);
                          // 0: generic per-element epilogue
   int in_is_residual;    // fast path: which operand map_in describes (0 = none/aux_in)
@@ -113,20 +137,29 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& P, int unit) {
   return u;
 }
 
-template <int CTAS>
+template <int CL>
 __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ TcParams P) {
-  using C = Cfg<CTAS>;
+  using C = Cfg<CL>;
+  constexpr int CTAS = C::CTAS;
   constexpr int STAGES = C::STAGES;
   constexpr int STAGE_BYTES = C::STAGE_BYTES;
   constexpr int NUM_BARS = C::NUM_BARS;
   constexpr int TILE_M = C::TILE_M;
-  extern __shared__ uint8_t smem_raw[];
-  // the dynamic shared window starts at the same offset in both CTAs of a pair, so this rounding is identical in both
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  // SWIZZLE_128B operand tiles need 1024-byte alignment.  The kernel has no static shared memory, so the dynamic window
+  // starts on a 1 KB boundary (checked below: every byte of the 227 KB is spoken for, there is no slack to round up into).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0u) {
+    if (threadIdx.x == 0) printf("m3ae: gemm_tcgen05_kernel: dynamic shared memory is not 1 KB aligned (0x%x)\n", smem_u32(smem_raw));
+    __trap();
+  }
   // CTA pair: rank 0 (leader) issues the MMAs for both; work is distributed per pair
-  const int rank = CTAS == 2 ? (int)cluster_ctarank() : 0;
-  const int worker = CTAS == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int n_workers = CTAS == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int crank = CL >= 2 ? (int)cluster_ctarank() : 0;
+  const int rank = crank & 1;         // rank inside the CTA pair
+  const int pair = crank >> 1;        // which pair of the cluster (CL = 4)
+  const uint16_t pair_mask = (uint16_t)(3u << (2 * pair));  // the two CTAs of this pair
+  const int worker = (int)blockIdx.x / CL;
+  const int n_workers = (int)gridDim.x / CL;
   uint8_t* epi_smem = smem + STAGES * STAGE_BYTES;
   float* bias_smem = (float*)(epi_smem + EPI_BYTES);
   uint64_t* bars = (uint64_t*)(epi_smem + EPI_BYTES + BIAS_BYTES);
@@ -140,7 +173,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform by construction: say so
   const int lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == WARP_TMA && lane == 0) {
     for (int i = 0; i < P.n_problems; ++i) {
       tma_prefetch_desc(&P.p[i].map_a);
       tma_prefetch_desc(&P.p[i].map_b);
@@ -152,10 +185,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       }
     }
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == WARP_MMA && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], C::NPAIR);  // a slot is free once the MMAs of EVERY pair that received data in it are done
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
@@ -164,12 +197,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     for (int s = 0; s < 2 * NUM_EPI_WARPS; ++s) mbar_init(&in_bar[s], 1);
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == WARP_ALLOC) {
     if (CTAS == 2) tmem_alloc_pair<TMEM_COLS>(tmem_ptr_smem);
     else tmem_alloc<TMEM_COLS>(tmem_ptr_smem);
   }
   tcgen05_fence_before();
-  if (CTAS == 2) cluster_sync_all();  // the peer's barriers must be initialised before anything remote arrives on them
+  if (CL >= 2) cluster_sync_all();  // the other CTAs' barriers must be initialised before anything remote arrives on them
   else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
@@ -178,15 +211,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   // asynchronous operations.  Issuing from inside an `if (lane == 0)` region makes the compiler feed every TMA / MMA
   // operand into uniform registers through an ELECT + R2UR.BROADCAST waterfall loop in front of EACH instruction
   // (~130 cycles per tcgen05.mma: as long as the 128-cycle MMA itself, so the issue thread paced the tensor pipe).
-  if (warp == 0) {
+  if (warp == WARP_TMA) {
     // ===================== TMA producer =====================
     int stage = 0;
     uint32_t phase = 0;
     for (int unit = worker; unit < P.total_units; unit += n_workers) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
-      const int a_row0 = u.m_blk * TILE_M + rank * BM;         // this CTA's 128 rows of A
-      const int b_row0 = u.n_blk * BN + rank * C::B_ROWS;      // this CTA's share of B (all 256 columns when alone)
+      const int share = CL == 4 ? q.share : 0;
+      const int m_blk = share == 1 ? 2 * u.m_blk + pair : u.m_blk;
+      const int n_blk = share == 2 ? 2 * u.n_blk + pair : u.n_blk;
+      const int a_row0 = m_blk * TILE_M + rank * BM;         // this CTA's 128 rows of A
+      const int b_row0 = n_blk * BN + rank * C::B_ROWS;      // this CTA's share of B (all 256 columns when alone)
+      const uint16_t mc_mask = (uint16_t)(5u << rank);       // the CTAs of this rank in both pairs
       for (int kb = u.kb0; kb < u.kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
@@ -196,14 +233,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             if (CTAS == 2) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1);
             else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
           };
+          // the shared operand: this CTA fetches 64 of its 128 rows (one of the two 8 KB swizzle blocks) and multicasts
+          // them into the same place of the same-rank CTA of the other pair
+          auto load_mc = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+            tma_load_2d_pair_mc(dst, m, &full_bar[stage], c0, c1, mc_mask);
+          };
           if (rank == 0) mbar_expect_tx(&full_bar[stage], STAGE_BYTES * CTAS);  // bytes of both CTAs land on the leader's barrier
-          if (q.a_major == M3AE_MAJOR_K) {
+          if (share == 2) {
+            if (q.a_major == M3AE_MAJOR_K) load_mc(sa + pair * (64 * 128), &q.map_a, kb * BK, a_row0 + pair * 64);
+            else load_mc(sa + pair * (BK * 128), &q.map_a, a_row0 + pair * 64, kb * BK);
+          } else if (q.a_major == M3AE_MAJOR_K) {
             load(sa, &q.map_a, kb * BK, a_row0);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) load(sa + j * (BK * 128), &q.map_a, a_row0 + j * 64, kb * BK);
           }
-          if (q.b_major == M3AE_MAJOR_K) {
+          if (share == 1) {
+            if (q.b_major == M3AE_MAJOR_K) load_mc(sb + pair * (64 * 128), &q.map_b, kb * BK, b_row0 + pair * 64);
+            else load_mc(sb + pair * (BK * 128), &q.map_b, b_row0 + pair * 64, kb * BK);
+          } else if (q.b_major == M3AE_MAJOR_K) {
             load(sb, &q.map_b, kb * BK, b_row0);
           } else {
 #pragma unroll
@@ -214,7 +262,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && rank == 0) {
+  } else if (warp == WARP_MMA && rank == 0) {
     // ===================== MMA issuer (one elected lane per k-block; the leader CTA of a pair) =====================
     int stage = 0;
     uint32_t phase = 0;
@@ -249,8 +297,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             else umma_f16(tmem_d, da, db, idesc, (kb > u.kb0 || k > 0) ? 1u : 0u);
           }
           if (CTAS == 2) {
-            umma_commit_pair(&empty_bar[stage]);  // frees the smem slot in BOTH CTAs once these MMAs have read it
-            if (kb + 1 == u.kb1) umma_commit_pair(&tmem_full[acc]);
+            // frees the smem slot once these MMAs have read it: in both CTAs of the pair, and (CL = 4) in the other pair
+            // too, whose producers multicast into this pair's slots
+            umma_commit_mc(&empty_bar[stage], CL == 4 ? (uint16_t)0xF : pair_mask);
+            if (kb + 1 == u.kb1) umma_commit_mc(&tmem_full[acc], pair_mask);
           } else {
             umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
             if (kb + 1 == u.kb1) umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
@@ -261,13 +311,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp >= 4) {
+  } else if (warp < NUM_EPI_WARPS) {
     // ===================== epilogue warps =====================
     // 16 warps: quad = TMEM lane quadrant (32 accumulator rows), cgrp = 64-column group of the 256-column accumulator.
     // (Round 1 ran 8 warps x 128 columns at 168 registers: two warps per scheduler could not cover their own dependency
     // latency and the scalar erfc polynomial alone filled the FMA pipe for longer than a K = 768 tile's MMAs take —
     // tensor pipe 31-41 % active on the epilogue-heavy stages, profiles/r1_ncu_gemm_full_v19_final.txt.)
-    const int e = warp - 4;
+    const int e = warp;
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const int cgrp = e >> 2;
     int acc = 0;
@@ -275,18 +325,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     uint32_t iph0 = 0, iph1 = 0;  // phases of this warp's two in-buffer barriers
     uint8_t* const wbuf = epi_smem + e * EPI_WARP_BYTES;
     uint64_t* const ibar = in_bar + 2 * e;
-    float* const sbias = bias_smem + e * 64;
+    float* const sbias_grp = bias_smem + cgrp * 64;  // + acc * 256: this tile's bias values
     auto release_acc = [&](int a) {  // this warp is done reading accumulator `a`
-      if (CTAS == 2 && rank != 0) mbar_arrive_cluster(&tmem_empty[a], 0);
+      if (CTAS == 2 && rank != 0) mbar_arrive_cluster(&tmem_empty[a], (uint32_t)(2 * pair));
       else mbar_arrive(&tmem_empty[a]);
     };
     for (int unit = worker; unit < P.total_units; unit += n_workers) {
       const Unit u = decode_unit(P, unit);
       const TcProblem& q = P.p[u.p];
       const EpiDev& epi = q.epi;
-      const int tile_row0 = u.m_blk * TILE_M + rank * BM;  // first output row of this CTA's 128-lane accumulator
+      const int share = CL == 4 ? q.share : 0;
+      const int m_blk = share == 1 ? 2 * u.m_blk + pair : u.m_blk;
+      const int n_blk = share == 2 ? 2 * u.n_blk + pair : u.n_blk;
+      const int tile_row0 = m_blk * TILE_M + rank * BM;  // first output row of this CTA's 128-lane accumulator
       const int row0 = tile_row0 + quad * 32;
-      const int col_base = u.n_blk * BN + cgrp * 64;
+      const int col_base = n_blk * BN + cgrp * 64;
       const uint32_t tacc = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + cgrp * 64);
       if (q.epi_fast == 2) {
         // ---- fp32 accumulate (out += alpha * acc): one 32x32 fp32 tile staged in swizzled smem (the warp's whole 4 KB),
@@ -347,14 +400,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             tma_load_2d(wbuf + EPI_BUF_BYTES, &q.map_in, &ibar[1], col_base + 32, row0);
           }
         }
-        if (epi.bias) {  // issued before the accumulator wait: the global-load latency hides behind the tile's MMAs
-          if (lane < 16) {
-            const int c4 = col_base + 4 * lane;
-            const float4 b4 = (c4 < q.N) ? __ldg(reinterpret_cast<const float4*>(epi.bias + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
-          }
-          __syncwarp();
+        // bias: loaded before the accumulator wait (the global-load latency hides behind the tile's MMAs), published to
+        // shared memory after it — by then every warp has finished the tile that last used this parity's slot
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (epi.bias && lane < 16) {
+          const int c4 = col_base + 4 * lane;
+          if (c4 < q.N) b4 = __ldg(reinterpret_cast<const float4*>(epi.bias + c4));
         }
+        float* const sbias = sbias_grp + acc * 256;
         uint32_t cached_bits[2] = {0u, 0u};
         if (epi.drop_p > 0.f && epi.drop_bits_ready && row < q.M) {
 #pragma unroll
@@ -363,6 +416,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         }
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
+        if (epi.bias) {
+          if (lane < 16) *reinterpret_cast<float4*>(sbias + 4 * lane) = b4;
+          __syncwarp();
+        }
 #pragma unroll 1
         for (int c = 0; c < nchunks; ++c) {
           const int col = col_base + c * 32;
@@ -582,9 +639,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   }
 
   tcgen05_fence_before();
-  if (CTAS == 2) cluster_sync_all();  // neither CTA may leave while its partner still multicasts onto its barriers / reads its smem
+  if (CL >= 2) cluster_sync_all();  // no CTA may leave while another still multicasts onto its barriers / into its smem
   else __syncthreads();
-  if (warp == 2) {
+  if (warp == WARP_ALLOC) {
     tcgen05_fence_after();
     if (CTAS == 2) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
     else tmem_dealloc<TMEM_COLS>(tmem_base);
@@ -687,31 +744,58 @@ bool force_generic_epilogue = false;  // test hook (m3ae_set_gemm_epilogue): run
 int gemm_cta_pair_mode = 0;           // m3ae_set_gemm_cta_pair: 0 auto, 1 always single CTA, 2 always CTA pair
 
 namespace {
-template <int CTAS>
+// Clusters of CL CTAs that can be resident at once (the kernel is persistent: a cluster that has to wait for another one to
+// retire would serialise the launch).  Queried once per cluster size.
+template <int CL>
+int max_clusters() {
+  static std::once_flag once;
+  static int n = 0;
+  std::call_once(once, [] {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(sm_count() / CL * CL));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = Cfg<CL>::SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int v = 0;
+    if (cudaOccupancyMaxActiveClusters(&v, gemm_tcgen05_kernel<CL>, &cfg) == cudaSuccess && v > 0) n = v;
+    else { (void)cudaGetLastError(); n = sm_count() / CL; }
+    if (n > sm_count() / CL) n = sm_count() / CL;
+  });
+  return n;
+}
+
+template <int CL>
 int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CTAS>::SMEM_BYTES);
+    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CL>::SMEM_BYTES);
   });
-  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CTAS>::SMEM_BYTES,
+  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CL>::SMEM_BYTES,
              cudaGetErrorString(attr_err));
-  const int workers_max = sm_count() / CTAS;
+  const int workers_max = CL == 1 ? sm_count() : max_clusters<CL>();
   const int workers = units < workers_max ? units : workers_max;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)(workers * CTAS));
+  cfg.gridDim = dim3((unsigned)(workers * CL));
   cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = Cfg<CTAS>::SMEM_BYTES;
+  cfg.dynamicSmemBytes = Cfg<CL>::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CTAS>, P));
+  M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CL>, P));
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -724,7 +808,12 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
   // there the second CTA would only multiply zero rows and halve the number of SMs streaming the weights).
   int max_m = 0;
   for (int i = 0; i < n; ++i) max_m = probs[i].M > max_m ? probs[i].M : max_m;
-  const int ctas = gemm_cta_pair_mode == 1 ? 1 : gemm_cta_pair_mode == 2 ? 2 : (max_m > BM ? 2 : 1);
+  // mode 0 (auto): CTA pairs; 1: single CTA; 2: one pair per cluster; 3: clusters of two pairs with operand multicast.
+  // Mode 3 is correct (bit-identical, tests/test_kernels_gpu.py) but measured SLOWER on this part: 4-CTA clusters leave
+  // TPCs idle in GPCs with an odd TPC count and the two pairs advance in lock step (profiles/r2_gemm_stages_ab.txt:
+  // QKV forward 72.9 vs 67.7 us, one-wave split-K wgrads 112 vs 71 us) — the kernel is latency-, not L2-bandwidth-bound.
+  const int cl = gemm_cta_pair_mode == 1 ? 1 : gemm_cta_pair_mode == 3 ? 4 : gemm_cta_pair_mode == 2 ? 2 : (max_m > BM ? 2 : 1);
+  const int ctas = cl >= 2 ? 2 : 1;
   const int tile_m = BM * ctas;
   const int b_rows = BN / ctas;
   TcParams P;
@@ -739,11 +828,19 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     M3AE_CHECK(g.split_k == 1 || (g.epi.accumulate && g.epi.out_dtype == M3AE_F32), M3AE_ERR_INVALID,
                "split_k > 1 requires accumulate=1 and an fp32 output");
     M3AE_CHECK(!g.epi.accumulate || g.epi.out_dtype == M3AE_F32, M3AE_ERR_INVALID, "accumulate requires an fp32 output");
+    // CL = 4: which operand the two pairs of a cluster share.  Stack the pairs along the dimension with an even number of
+    // tiles (the odd tile of an odd count is computed against zero-filled operands and clipped away); ties go to M.
+    const int tm1 = (g.M + tile_m - 1) / tile_m, tn1 = (g.N + BN - 1) / BN;
+    q.share = 0;
+    if (cl == 4) {
+      const double waste_m = (double)(tm1 & 1) / (double)(tm1 + (tm1 & 1)), waste_n = (double)(tn1 & 1) / (double)(tn1 + (tn1 & 1));
+      q.share = waste_m <= waste_n ? 1 : 2;
+    }
     int rc;
-    if (g.a_major == M3AE_MAJOR_K) rc = encode_map(&q.map_a, g.a, g.M, g.K, g.lda, BM);
+    if (g.a_major == M3AE_MAJOR_K) rc = encode_map(&q.map_a, g.a, g.M, g.K, g.lda, q.share == 2 ? BM / 2 : BM);
     else rc = encode_map(&q.map_a, g.a, g.K, g.M, g.lda, BK);
     if (rc) return rc;
-    if (g.b_major == M3AE_MAJOR_K) rc = encode_map(&q.map_b, g.b, g.N, g.K, g.ldb, b_rows);
+    if (g.b_major == M3AE_MAJOR_K) rc = encode_map(&q.map_b, g.b, g.N, g.K, g.ldb, q.share == 1 ? b_rows / 2 : b_rows);
     else rc = encode_map(&q.map_b, g.b, g.K, g.N, g.ldb, BK);
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
@@ -773,8 +870,8 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     }
     q.M = g.M; q.N = g.N; q.K = g.K;
     q.a_major = g.a_major; q.b_major = g.b_major;
-    q.tiles_m = (g.M + tile_m - 1) / tile_m;
-    q.tiles_n = (g.N + BN - 1) / BN;
+    q.tiles_m = q.share == 1 ? (tm1 + 1) / 2 : tm1;
+    q.tiles_n = q.share == 2 ? (tn1 + 1) / 2 : tn1;
     q.kblocks = (g.K + BK - 1) / BK;
     int split = g.split_k < q.kblocks ? g.split_k : q.kblocks;
     q.kb_per_split = (q.kblocks + split - 1) / split;
@@ -791,7 +888,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     q.unit_end = units;
   }
   P.total_units = units;
-  return ctas == 2 ? launch_tc<2>(P, units, stream) : launch_tc<1>(P, units, stream);
+  return cl == 4 ? launch_tc<4>(P, units, stream) : cl == 2 ? launch_tc<2>(P, units, stream) : launch_tc<1>(P, units, stream);
 }
 
 }  // namespace m3ae

@@ -51,7 +51,8 @@ def set_layernorm_bwd_staging(registers_only):
 
 
 def set_gemm_cta_pair(mode):
-    """0 auto, 1 one CTA per 128x256 tile, 2 CTA pairs (tcgen05.mma.cta_group::2, 256x256 tiles)."""
+    """0 auto, 1 one CTA per 128x256 tile, 2 CTA pairs (tcgen05.mma.cta_group::2, 256x256 tiles), 3 clusters of two pairs
+    that share one operand by TMA multicast (what auto picks for M > 128)."""
     L.check(L.load().m3ae_set_gemm_cta_pair(int(mode)), "m3ae_set_gemm_cta_pair")
 
 

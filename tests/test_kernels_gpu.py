@@ -411,7 +411,9 @@ def test_gemm_cta_pair_matches_single_cta_tiles():
     MN = ops.MAJOR_MN
     bf = torch.bfloat16
     cases = []
-    for (M, N, K) in [(300, 498, 768), (2600, 2304, 768), (257, 768, 3072), (20800 // 8, 3072, 768)]:
+    # (2600, 2304): 11 x 9 pair tiles (both odd: the odd tile runs against zero-filled operands); (257, 768): 2 x 3;
+    # (1300, 512): 6 x 2; (520, 3072): 3 x 12 -> the cluster's pairs sit side by side along N and share the A tile
+    for (M, N, K) in [(300, 498, 768), (2600, 2304, 768), (257, 768, 3072), (20800 // 8, 3072, 768), (1300, 512, 768), (520, 3072, 768)]:
         a, b = rnd(M, K, dtype=bf, scale=0.5), rnd(N, K, dtype=bf, scale=0.5, seed=1)
         res, pre = rnd(M, N, dtype=bf, seed=2), rnd(M, N, dtype=bf, seed=3)
         bias = rnd(N, seed=4)
@@ -435,17 +437,18 @@ def test_gemm_cta_pair_matches_single_cta_tiles():
     try:
         for name, mk in cases:
             outs = {}
-            for mode in (1, 2):
+            for mode in (1, 2, 3):
                 ops.set_gemm_cta_pair(mode)
                 specs = mk()
                 ops.gemm_group(specs, backend=ops.GEMM_TCGEN05)
                 torch.cuda.synchronize()
                 outs[mode] = [t for s in specs for t in (s.keep[2], s.keep[4]) if t is not None]
-            for o1, o2 in zip(outs[1], outs[2]):
-                if "splitK" in name:
-                    assert rel_err(o2, o1) < 1e-5, name
-                else:
-                    assert torch.equal(o1, o2), f"{name}: CTA-pair result differs from single-CTA result"
+            for mode in (2, 3):  # 3 = clusters of two pairs sharing one operand by TMA multicast (auto mode for M > 128)
+                for o1, o2 in zip(outs[1], outs[mode]):
+                    if "splitK" in name:
+                        assert rel_err(o2, o1) < 1e-5, (name, mode)
+                    else:
+                        assert torch.equal(o1, o2), f"{name}: mode {mode} result differs from the single-CTA result"
     finally:
         ops.set_gemm_cta_pair(0)
 

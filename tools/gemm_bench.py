@@ -15,7 +15,7 @@ def t(*s, dtype=bf):
     return (torch.randn(*s, device=dev) * 0.05).to(dtype)
 
 ONLY = os.environ.get("ONLY", "")
-ops.set_gemm_cta_pair(int(os.environ.get("PAIR", "0")))  # 0 auto (CTA pairs), 1 single-CTA tiles, 2 pairs
+ops.set_gemm_cta_pair(int(os.environ.get("PAIR", "0")))  # 0 auto (two-pair clusters with multicast), 1 single-CTA tiles, 2 pairs, 3 two-pair clusters
 print(f"# m3ae_set_gemm_cta_pair({os.environ.get('PAIR', '0')})")
 REPS = int(os.environ.get("REPS", "20"))
 
