@@ -94,6 +94,11 @@ typedef struct m3ae_gemm_epilogue_t {
                          * m3ae_layernorm_bwd so that backward does not regenerate the Philox stream. */
   int32_t drop_bits_ready; /* 1: drop_bits already holds this site's keep bits (m3ae_dropout_bits): the epilogue READS them
                             * instead of evaluating Philox (same bits, by construction); 0: the epilogue writes them */
+  float* amax_val;      /* optional (tcgen05 backend, fp32 out or out == NULL): per-row maximum of every 64-column group of the */
+  int32_t* amax_idx;    /* result and its column, amax_val[g * M + row] / amax_idx[g * M + row], g = col / 64, first maximum
+                         * wins.  m3ae_argmax_partials reduces them to the row argmax, so the decoder's vocabulary
+                         * projection (m3ae_decoder.py:136,151-153) never writes its [B, 30522] logits.  With amax_val set,
+                         * out may be NULL (nothing but the partials is written). */
 } m3ae_gemm_epilogue_t;
 
 typedef struct m3ae_gemm_problem_t {
@@ -260,6 +265,9 @@ int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M
 int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M,
                        int32_t D, int32_t out_dtype, void* stream);
 
+/* Row argmax from the per-64-column partials of m3ae_gemm (epi.amax_val / amax_idx): ids[row] (int64) = column of the first
+ * maximum over groups [0, n_groups).  Replaces argmax(log_softmax(final_linear(x))) of m3ae_decoder.py:151-153. */
+int m3ae_argmax_partials(const float* amax_val, const int32_t* amax_idx, int32_t n_groups, int32_t M, int64_t* ids, void* stream);
 /* Test hook: 0 = auto (tcgen05/TMEM attention for bf16 where the shape is covered, else mma.sync tiles),
  * 1 = tcgen05 for every covered shape (auto skips the ones where mma.sync is faster), 2 = force the generic fp32-math
  * attention kernels, 3 (M3AE_ATTN_MMA_SYNC) = skip tcgen05, use the mma.sync tiles. */
@@ -271,6 +279,9 @@ int m3ae_set_gemm_epilogue(int32_t generic);
  * 1 = always one CTA per 128x256 tile, 2 = one CTA pair per cluster (no multicast), 3 = always two pairs per cluster.
  * Results are identical.  Process-global test / benchmarking hook: not synchronised with concurrent launches. */
 int m3ae_set_gemm_cta_pair(int32_t mode);
+/* Single-CTA launches (every problem M <= 128): 0 = auto (128x64 tiles when 128x256 tiles would occupy less than a third of
+ * the SMs), 1 = always 128x256, 2 = always 128x64.  Results are identical.  Process-global test hook. */
+int m3ae_set_gemm_skinny(int32_t mode);
 /* Test hook: 1 = m3ae_layernorm_bwd loads rows through registers only (cross-checks the cp.async.bulk staging ring), 0 = auto. */
 int m3ae_set_layernorm_bwd_staging(int32_t registers_only);
 

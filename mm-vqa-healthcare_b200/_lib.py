@@ -27,6 +27,7 @@ class GemmEpilogue(C.Structure):
         ("drop_p", C.c_float), ("drop_seed", C.c_uint64), ("drop_stream", C.c_uint64),
         ("accumulate", C.c_int32), ("alpha", C.c_float), ("aux_is_grad", C.c_int32),
         ("drop_bits", C.c_void_p), ("drop_bits_ready", C.c_int32),
+        ("amax_val", C.c_void_p), ("amax_idx", C.c_void_p),
     ]
 
 
@@ -106,6 +107,8 @@ SIGNATURES = {
                                      C.c_int32, C.c_void_p]),
     "m3ae_set_attention_backend": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
+    "m3ae_argmax_partials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "m3ae_set_gemm_skinny": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_cta_pair": (C.c_int, [C.c_int32]),
     "m3ae_set_layernorm_bwd_staging": (C.c_int, [C.c_int32]),
 }

@@ -83,6 +83,8 @@ int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, vo
 
 extern bool force_generic_epilogue;
 extern int gemm_cta_pair_mode;
+extern int gemm_skinny_mode;
+int argmax_partials(const float*, const int32_t*, int, int, int64_t*, cudaStream_t);
 extern bool ln_bwd_force_registers;
 static int g_attn_backend = M3AE_GEMM_AUTO;
 
@@ -108,7 +110,11 @@ int m3ae_gemm(const m3ae_gemm_problem_t* problems, int32_t n, int32_t in_dtype, 
   M3AE_CHECK(in_dtype == M3AE_F32 || in_dtype == M3AE_BF16, M3AE_ERR_INVALID, "m3ae_gemm: bad input dtype %d", in_dtype);
   for (int i = 0; i < n; ++i) {
     const m3ae_gemm_problem_t& g = problems[i];
-    M3AE_CHECK(g.a && g.b && g.epi.out, M3AE_ERR_INVALID, "m3ae_gemm: null operand in problem %d", i);
+    M3AE_CHECK(g.a && g.b && (g.epi.out || g.epi.amax_val), M3AE_ERR_INVALID, "m3ae_gemm: null operand in problem %d", i);
+    M3AE_CHECK((g.epi.amax_val == nullptr) == (g.epi.amax_idx == nullptr), M3AE_ERR_INVALID, "m3ae_gemm: amax_val and amax_idx come together");
+    M3AE_CHECK(g.epi.amax_val == nullptr || (in_dtype == M3AE_BF16 && backend != M3AE_GEMM_SIMT && g.split_k <= 1 && !g.epi.accumulate &&
+                                              (g.epi.out == nullptr || g.epi.out_dtype == M3AE_F32)),
+               M3AE_ERR_UNSUPPORTED, "m3ae_gemm: the row-argmax partials need the tcgen05 backend, no split-K and an fp32 (or no) output");
     M3AE_CHECK(g.epi.drop_p >= 0.f && g.epi.drop_p < 1.f, M3AE_ERR_INVALID, "m3ae_gemm: dropout %f not in [0,1)", g.epi.drop_p);
     M3AE_CHECK(g.epi.dact == M3AE_ACT_NONE || g.epi.aux_in != nullptr, M3AE_ERR_INVALID, "m3ae_gemm: dact needs aux_in");
     M3AE_CHECK(g.epi.drop_bits == nullptr || (g.epi.drop_p > 0.f && g.N % 32 == 0 && in_dtype == M3AE_BF16 && backend != M3AE_GEMM_SIMT),
@@ -213,6 +219,16 @@ int m3ae_decode_attn(const void* q, int64_t ldq, const void* kcache, const void*
   ARCH_GATE();
   M3AE_CHECK(q && kcache && vcache && out, M3AE_ERR_INVALID, "decode_attn: null pointer");
   return decode_attn(q, ldq, kcache, vcache, ldk, ldv, bsk, bsv, out, ldo, B, H, len, dh, scale, dtype, (cudaStream_t)stream);
+}
+int m3ae_argmax_partials(const float* amax_val, const int32_t* amax_idx, int32_t n_groups, int32_t M, int64_t* ids, void* stream) {
+  ARCH_GATE();
+  M3AE_CHECK(amax_val && amax_idx && ids && n_groups > 0 && M > 0, M3AE_ERR_INVALID, "argmax_partials: null pointer or empty input");
+  return argmax_partials(amax_val, amax_idx, n_groups, M, ids, (cudaStream_t)stream);
+}
+int m3ae_set_gemm_skinny(int32_t mode) {
+  M3AE_CHECK(mode >= 0 && mode <= 2, M3AE_ERR_INVALID, "m3ae_set_gemm_skinny: mode %d not in {0 auto, 1 never, 2 always}", mode);
+  gemm_skinny_mode = mode;
+  return M3AE_OK;
 }
 int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M, int32_t N, int32_t dtype, void* stream) {
   ARCH_GATE();

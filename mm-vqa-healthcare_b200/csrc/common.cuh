@@ -302,6 +302,9 @@ struct EpiDev {
   uint32_t* drop_bits;     // optional keep-bit cache [rows][N/32] (tcgen05 epilogues, 32-column chunks)
   int64_t drop_bits_ld;    // words per row = N / 32 (set by the launcher)
   int drop_bits_ready;     // 1: read the keep bits from drop_bits instead of evaluating Philox
+  float* amax_val;         // per-(64-column group, row) maximum / its column (tcgen05 generic epilogue), or null
+  int32_t* amax_idx;
+  int32_t amax_ld;         // = M (set by the launcher)
 };
 
 // Applies the epilogue to `n` consecutive columns [col, col+n) of row `row` whose accumulators are acc[0..n).

@@ -14,6 +14,7 @@ void epi_to_dev(const m3ae_gemm_epilogue_t& e, EpiDev* d) {
   d->drop_p = e.drop_p; d->drop_seed = e.drop_seed; d->drop_stream = e.drop_stream;
   d->accumulate = e.accumulate; d->alpha = e.alpha; d->aux_is_grad = e.aux_is_grad;
   d->drop_bits = e.drop_bits; d->drop_bits_ld = 0; d->drop_bits_ready = e.drop_bits_ready;
+  d->amax_val = e.amax_val; d->amax_idx = e.amax_idx; d->amax_ld = 0;
 }
 void count_launch();
 

@@ -25,7 +25,8 @@ namespace m3ae {
 namespace {
 
 constexpr int BM = 128;
-constexpr int BN = 256;
+constexpr int BN_WIDE = 256;    // output columns per tile
+constexpr int BN_SKINNY = 64;   // ... of the skinny variant (launches whose problems all have M <= 128 and few wide tiles)
 constexpr int BK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
@@ -55,8 +56,12 @@ constexpr int BIAS_BYTES = 2 * 4 * 64 * 4;  // per accumulator parity and 64-col
 // fetches HALF of its share of that operand and TMA-multicasts it to the CTA of the same rank in the other pair: 96 KB
 // of L2 reads per 16.8 MFLOP instead of 64 KB per 8.4 MFLOP (ncu: 774 MB of TMA loads for 37 MB of operands on the
 // FFN-up GEMM, 8.4 TB/s).  Measured: no gain — see the launcher.
-template <int CL>
+// BNV = 64 (single CTA only): 128x64 tiles.  The decoder's per-token GEMMs have M = batch <= 128 and N = 768..3072: with
+// 256-column tiles 3-12 CTAs of 148 stream the whole weight matrix through one k-loop each (14-35 us per GEMM against 1-7 us
+// of HBM time, profiles/r1_launches_decoder_v18_summary.txt); 64-column tiles put 12-48 CTAs on it with a 6-stage ring.
+template <int CL, int BNV = BN_WIDE>
 struct Cfg {
+  static constexpr int BN = BNV;
   static constexpr int CTAS = CL >= 2 ? 2 : 1;   // CTAs per output tile (cta_group)
   static constexpr int NPAIR = CL / CTAS;        // tiles a cluster works on at a time
   static constexpr int TILE_M = BM * CTAS;
@@ -69,7 +74,7 @@ struct Cfg {
   // Operand bytes in flight per SM = (STAGES - 1) x 32 KB; at 64 B/clk per SM (tensor pipe saturated) and ~1500-2000
   // cycles of loaded L2 latency, Little's law asks for 96-128 KB.  Measured 3 / 4 / 5 stages (profiles/r2_gemm_stages_ab.txt):
   // K = 3072 forward 1011 / 1123 / 1175 TFLOP/s, split-K wgrad 1164 / 1333 / 1377; the K = 768 shapes do not move.
-  static constexpr int STAGES = CTAS == 1 ? 3 : M3AE_GEMM_STAGES;
+  static constexpr int STAGES = CTAS == 1 ? (BNV == BN_SKINNY ? 6 : 3) : M3AE_GEMM_STAGES;
   static constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * NUM_EPI_WARPS;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + NUM_BARS * 8 + 16;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
@@ -137,10 +142,11 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& P, int unit) {
   return u;
 }
 
-template <int CL>
+template <int CL, int BNV>
 __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ TcParams P) {
-  using C = Cfg<CL>;
+  using C = Cfg<CL, BNV>;
   constexpr int CTAS = C::CTAS;
+  constexpr int BN = C::BN;
   constexpr int STAGES = C::STAGES;
   constexpr int STAGE_BYTES = C::STAGE_BYTES;
   constexpr int NUM_BARS = C::NUM_BARS;
@@ -320,6 +326,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
     const int e = warp;
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const int cgrp = e >> 2;
+    const bool cg_live = cgrp * 64 < BN;  // skinny tiles: only the first column group exists (the others just keep the barrier protocol)
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t iph0 = 0, iph1 = 0;  // phases of this warp's two in-buffer barriers
@@ -344,7 +351,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       if (q.epi_fast == 2) {
         // ---- fp32 accumulate (out += alpha * acc): one 32x32 fp32 tile staged in swizzled smem (the warp's whole 4 KB),
         //      added into global memory by a TMA reduction.  One bulk reduction replaces 1024 scattered RED.ADD.F32.
-        const int nchunks = (row0 < q.M) ? min(2, (q.N - col_base + 31) / 32) : 0;
+        const int nchunks = (row0 < q.M && cg_live) ? min(2, (q.N - col_base + 31) / 32) : 0;
         const float alpha = epi.alpha;
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
@@ -386,7 +393,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
         // Chunk c (32 columns) stages its input (residual / saved act') AND its output in buf[c]: a thread reads and
         // writes only its own row, so the result overwrites the input in place.  With a second (aux) output every chunk
         // uses buf[0] for in/out and buf[1] for the aux tile.
-        const int nchunks = min(2, (q.N - col_base + 31) / 32);  // <= 0: this warp's columns lie outside N
+        const int nchunks = cg_live ? min(2, (q.N - col_base + 31) / 32) : 0;  // <= 0: this warp's columns lie outside N
         const int64_t row = (int64_t)row0 + lane;
         const uint32_t sw = (uint32_t)((lane >> 1) & 3);           // SWIZZLE_64B: 16-byte chunk ^= (row/2)%4
         const bool aux = epi.aux_out != nullptr;
@@ -581,10 +588,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       tcgen05_fence_after();
       const int64_t row = (int64_t)row0 + lane;
       const bool row_ok = row < q.M;
+      float best = -INFINITY;  // row maximum of this warp's 64 columns and its column (epi.amax_val)
+      int best_col = col_base < q.N ? col_base : 0;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         const int col = col_base + c * 16;
-        if (col >= q.N) break;  // warp-uniform
+        if (col >= q.N || !cg_live) break;  // warp-uniform
         uint32_t r[16];
         tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 16), r);
         tmem_ld_wait();
@@ -594,6 +603,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
           for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
           const int n_valid = min(16, q.N - col);
           epilogue_apply<16>(epi, row, col, n_valid, v);
+          if (epi.amax_val != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j < n_valid && v[j] > best) { best = v[j]; best_col = col + j; }  // ascending columns, strict >: first maximum
+            if (epi.out == nullptr) continue;
+          }
           const size_t o = (size_t)(row * epi.ldo + col);
           if (epi.accumulate) {
             float* out = (float*)epi.out + o;
@@ -629,6 +644,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
             }
           }
         }
+      }
+      if (epi.amax_val != nullptr && row_ok && cg_live && col_base < q.N) {
+        const int64_t g = (int64_t)(col_base >> 6) * epi.amax_ld + row;
+        epi.amax_val[g] = best;
+        epi.amax_idx[g] = best_col;
       }
       tcgen05_fence_before();
       __syncwarp();
@@ -723,6 +743,7 @@ bool tma_ok(const void* p, int64_t ld) { return p != nullptr && (((uintptr_t)p) 
 // bf16 input operand (residual or aux_in), optional bf16 aux_out.  Everything else uses the generic per-element path.
 bool epilogue_is_fast(const m3ae_gemm_problem_t& g) {
   const m3ae_gemm_epilogue_t& e = g.epi;
+  if (e.amax_val != nullptr || e.out == nullptr) return false;
   if (e.out_dtype != M3AE_BF16 || e.accumulate || e.alpha != 1.0f || (g.N % 32) != 0) return false;
   if (!tma_ok(e.out, e.ldo)) return false;
   if (e.aux_out && !tma_ok(e.aux_out, e.ldo)) return false;
@@ -742,11 +763,12 @@ void count_launch();
 
 bool force_generic_epilogue = false;  // test hook (m3ae_set_gemm_epilogue): run the per-element epilogue everywhere
 int gemm_cta_pair_mode = 0;           // m3ae_set_gemm_cta_pair: 0 auto, 1 always single CTA, 2 always CTA pair
+int gemm_skinny_mode = 0;             // m3ae_set_gemm_skinny: 0 auto, 1 never, 2 always (single-CTA launches only)
 
 namespace {
 // Clusters of CL CTAs that can be resident at once (the kernel is persistent: a cluster that has to wait for another one to
 // retire would serialise the launch).  Queried once per cluster size.
-template <int CL>
+template <int CL, int BNV>
 int max_clusters() {
   static std::once_flag once;
   static int n = 0;
@@ -755,7 +777,7 @@ int max_clusters() {
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3((unsigned)(sm_count() / CL * CL));
     cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = Cfg<CL>::SMEM_BYTES;
+    cfg.dynamicSmemBytes = Cfg<CL, BNV>::SMEM_BYTES;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CL;
@@ -764,29 +786,29 @@ int max_clusters() {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     int v = 0;
-    if (cudaOccupancyMaxActiveClusters(&v, gemm_tcgen05_kernel<CL>, &cfg) == cudaSuccess && v > 0) n = v;
+    if (cudaOccupancyMaxActiveClusters(&v, gemm_tcgen05_kernel<CL, BNV>, &cfg) == cudaSuccess && v > 0) n = v;
     else { (void)cudaGetLastError(); n = sm_count() / CL; }
     if (n > sm_count() / CL) n = sm_count() / CL;
   });
   return n;
 }
 
-template <int CL>
+template <int CL, int BNV>
 int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CL>::SMEM_BYTES);
+    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CL, BNV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CL, BNV>::SMEM_BYTES);
   });
-  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CL>::SMEM_BYTES,
+  M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CL, BNV>::SMEM_BYTES,
              cudaGetErrorString(attr_err));
-  const int workers_max = CL == 1 ? sm_count() : max_clusters<CL>();
+  const int workers_max = CL == 1 ? sm_count() : max_clusters<CL, BNV>();
   const int workers = units < workers_max ? units : workers_max;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)(workers * CL));
   cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = Cfg<CL>::SMEM_BYTES;
+  cfg.dynamicSmemBytes = Cfg<CL, BNV>::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -795,7 +817,7 @@ int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CL>, P));
+  M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CL, BNV>, P));
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -815,6 +837,10 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
   const int cl = gemm_cta_pair_mode == 1 ? 1 : gemm_cta_pair_mode == 3 ? 4 : gemm_cta_pair_mode == 2 ? 2 : (max_m > BM ? 2 : 1);
   const int ctas = cl >= 2 ? 2 : 1;
   const int tile_m = BM * ctas;
+  // skinny tiles when one CTA per tile is used anyway and 256-column tiles would occupy less than a third of the SMs
+  int wide_tiles = 0;
+  for (int i = 0; i < n; ++i) wide_tiles += ((probs[i].M + BM - 1) / BM) * ((probs[i].N + BN_WIDE - 1) / BN_WIDE) * (probs[i].split_k > 1 ? probs[i].split_k : 1);
+  const int BN = (cl == 1 && gemm_skinny_mode != 1 && (gemm_skinny_mode == 2 || wide_tiles * 3 < sm_count())) ? BN_SKINNY : BN_WIDE;
   const int b_rows = BN / ctas;
   TcParams P;
   memset(&P, 0, sizeof(P));
@@ -845,6 +871,7 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     if (rc) return rc;
     epi_to_dev(g.epi, &q.epi);
     q.epi.drop_bits_ld = g.N / 32;
+    q.epi.amax_ld = g.M;
     q.epi_fast = (!force_generic_epilogue && epilogue_is_fast(g)) ? 1 : 0;
     if (!force_generic_epilogue && epilogue_is_reduce(g)) q.epi_fast = 2;
     q.has_in = 0;
@@ -888,7 +915,9 @@ int gemm_tcgen05_launch(const m3ae_gemm_problem_t* probs, int n, cudaStream_t st
     q.unit_end = units;
   }
   P.total_units = units;
-  return cl == 4 ? launch_tc<4>(P, units, stream) : cl == 2 ? launch_tc<2>(P, units, stream) : launch_tc<1>(P, units, stream);
+  if (cl == 4) return launch_tc<4, BN_WIDE>(P, units, stream);
+  if (cl == 2) return launch_tc<2, BN_WIDE>(P, units, stream);
+  return BN == BN_SKINNY ? launch_tc<1, BN_SKINNY>(P, units, stream) : launch_tc<1, BN_WIDE>(P, units, stream);
 }
 
 }  // namespace m3ae

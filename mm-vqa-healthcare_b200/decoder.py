@@ -297,7 +297,15 @@ class Decoder(nn.Module):
         k_self, v_self = buf(B, L, D), buf(B, L, D)
         x, xn, q, a, x1, x1n, q2, c, x3, x3n, h, u, x5, x6 = (buf(B, D) for _ in range(14))
         h, u = buf(B, w_f0.shape[0]), buf(B, w_f0.shape[0])
-        logits = buf(B, V, dtype=torch.float32)
+        # the vocabulary projection never writes its [B, V] logits: its epilogue records, per row and 64-column group, the
+        # maximum and its column; argmax_partials picks the row argmax (log_softmax is monotone, m3ae_decoder.py:151-153)
+        # (bf16 tensor-core path; the fp32 strict-parity path keeps logits + argmax_rows)
+        fused_argmax = dt == torch.bfloat16
+        n_grp = (V + 63) // 64
+        if fused_argmax:
+            amax_v, amax_i = buf(n_grp, B, dtype=torch.float32), buf(n_grp, B, dtype=torch.int32)
+        else:
+            logits = buf(B, V, dtype=torch.float32)
         m1, r1 = buf(B, dtype=torch.float32), buf(B, dtype=torch.float32)
         seq = torch.full((L + 1, B), pad, dtype=torch.int64, device=dev)  # time-major: seq[t] is contiguous
         seq[0] = tokenizer.cls_token_id
@@ -305,9 +313,9 @@ class Decoder(nn.Module):
         bq2 = b_in2[:D].contiguous()
         pe = self.positional_encoding.pe[0].contiguous()
         table = self.target_embedding.weight.detach()
+        pos_all = torch.arange(L, dtype=torch.int32, device=dev).repeat_interleave(B).view(L, B)
         for t in range(L):
-            pos = torch.full((B,), t, dtype=torch.int32, device=dev)
-            ops.decoder_embed(seq[t], pos, table, pe, x)  # 2*E[id] + pe[t]
+            ops.decoder_embed(seq[t], pos_all[t], table, pe, x)  # 2*E[id] + pe[t]
             ops.layernorm_fwd(x, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps, xn, m1, r1)
             # q for this token; k, v written straight into the cache rows [b, t, :]
             ops.gemm_group([ops.GemmSpec(xn, w_in1[:D], q, bias=bq),
@@ -323,8 +331,12 @@ class Decoder(nn.Module):
             ops.gemm(x3n, w_f0, h, bias=layer.ffn[0].bias, act=ops.ACT_RELU)
             ops.gemm(h, w_f2, x5, bias=layer.ffn[2].bias, residual=x3)
             ops.layernorm_fwd(x5, layer.layernorm3.weight, layer.layernorm3.bias, layer.layernorm3.eps, x6, m1, r1)
-            ops.gemm(x6, w_vocab, logits, bias=self.final_linear.bias)
-            ops.argmax_rows(logits, seq[t + 1])  # log_softmax is monotone (:151-153)
+            if fused_argmax:
+                ops.gemm_group([ops.GemmSpec(x6, w_vocab, None, bias=self.final_linear.bias, amax=(amax_v, amax_i))])
+                ops.argmax_partials(amax_v, amax_i, seq[t + 1])
+            else:
+                ops.gemm(x6, w_vocab, logits, bias=self.final_linear.bias)
+                ops.argmax_rows(logits, seq[t + 1])
             if early_exit_every and (t + 1) % early_exit_every == 0:
                 nxt = seq[1:t + 2]
                 done = nxt == sep

@@ -64,16 +64,22 @@ class GemmSpec:
 
     def __init__(self, a, b, out, *, a_major=MAJOR_K, b_major=MAJOR_K, bias=None, act=ACT_NONE, aux_out=None,
                  aux_in=None, dact=ACT_NONE, residual=None, drop_p=0.0, drop_seed=0, drop_stream=0, accumulate=False,
-                 split_k=1, alpha=1.0, aux_is_grad=False, drop_bits=None, drop_bits_ready=False):
+                 split_k=1, alpha=1.0, aux_is_grad=False, drop_bits=None, drop_bits_ready=False, amax=None):
+        """amax = (vals fp32 [ceil(N/64), M], idx int32 [ceil(N/64), M]): the epilogue also records, per row and 64-column
+        group, the maximum of the result and its column (reduced by argmax_partials); `out` may then be None."""
         _need_cuda(a, b, out, bias, aux_out, aux_in, residual, drop_bits)
-        assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
-        assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+        assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
         assert a.dtype == b.dtype
+        if out is None:
+            if amax is None:
+                raise ValueError("GEMM needs an output tensor (or amax partials)")
+        else:
+            assert out.dim() == 2 and out.stride(1) == 1
         M, K = (a.shape if a_major == MAJOR_K else (a.shape[1], a.shape[0]))
         N, Kb = (b.shape if b_major == MAJOR_K else (b.shape[1], b.shape[0]))
         if K != Kb:
             raise ValueError(f"GEMM contraction mismatch: A gives K={K}, B gives K={Kb}")
-        if tuple(out.shape) != (M, N):
+        if out is not None and tuple(out.shape) != (M, N):
             raise ValueError(f"GEMM output shape {tuple(out.shape)} != ({M},{N})")
         if bias is not None:
             assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
@@ -85,7 +91,7 @@ class GemmSpec:
         self.in_dtype = a.dtype
         if drop_bits is not None:  # keep bits of the epilogue dropout, [M, N/32] uint32 words (read by layernorm_bwd)
             assert N % 32 == 0 and drop_bits.is_contiguous() and drop_bits.numel() * drop_bits.element_size() == M * (N // 32) * 4
-        self.keep = (a, b, out, bias, aux_out, aux_in, residual, drop_bits)  # keep tensors alive until launch returns
+        self.keep = (a, b, out, bias, aux_out, aux_in, residual, drop_bits, amax)  # keep tensors alive until launch returns
         p = L.GemmProblem()
         p.a, p.b = a.data_ptr(), b.data_ptr()
         p.lda, p.ldb = a.stride(0), b.stride(0)
@@ -93,7 +99,17 @@ class GemmSpec:
         p.M, p.N, p.K = M, N, K
         p.split_k = split_k
         e = p.epi
-        e.out, e.out_dtype, e.ldo = out.data_ptr(), _code(out.dtype), out.stride(0)
+        if out is not None:
+            e.out, e.out_dtype, e.ldo = out.data_ptr(), _code(out.dtype), out.stride(0)
+        else:
+            e.out, e.out_dtype, e.ldo = None, F32, N
+        if amax is not None:
+            av, ai = amax
+            _need_cuda(av, ai)
+            G = (N + 63) // 64
+            assert av.dtype == torch.float32 and ai.dtype == torch.int32 and av.is_contiguous() and ai.is_contiguous()
+            assert tuple(av.shape) == (G, M) and tuple(ai.shape) == (G, M)
+            e.amax_val, e.amax_idx = av.data_ptr(), ai.data_ptr()
         e.bias = bias.data_ptr() if bias is not None else None
         e.act = act
         e.aux_out = aux_out.data_ptr() if aux_out is not None else None
@@ -346,6 +362,21 @@ def decode_attn(q, kcache, vcache, out, *, H, length, dh, scale=None):
                                       float(scale if scale is not None else dh ** -0.5), _code(q.dtype), _stream()),
             "m3ae_decode_attn")
     return out
+
+
+def argmax_partials(vals, idx, out=None):
+    """Row argmax (int64 [M]) from the per-64-column partials a GEMM epilogue wrote (GemmSpec(amax=...)); first maximum wins."""
+    _need_cuda(vals, idx)
+    G, M = vals.shape
+    out = torch.empty(M, dtype=torch.int64, device=vals.device) if out is None else out
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == M
+    L.check(L.load().m3ae_argmax_partials(_ptr(vals), _ptr(idx), G, M, _ptr(out), _stream()), "m3ae_argmax_partials")
+    return out
+
+
+def set_gemm_skinny(mode):
+    """Test hook for single-CTA GEMM launches (every problem M <= 128): 0 auto, 1 always 128x256 tiles, 2 always 128x64 tiles."""
+    L.check(L.load().m3ae_set_gemm_skinny(int(mode)), "m3ae_set_gemm_skinny")
 
 
 def argmax_rows(logits, out=None):

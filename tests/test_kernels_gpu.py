@@ -575,3 +575,62 @@ def test_pregenerated_hidden_keep_bits_equal_epilogue_generation(M):
     finally:
         ops.set_gemm_epilogue(False)
     assert rel_err(o3, o1) < 1e-2 and torch.equal(o3 != res, o1 != res)
+
+
+def test_gemm_skinny_tiles_match_wide_tiles():
+    """Single-CTA launches (M <= 128: the decoder's per-token GEMMs): 128x64 tiles accumulate every output over K in the same
+    order as 128x256 tiles -> bit-identical results, for the epilogues the decoder step uses."""
+    bf = torch.bfloat16
+    try:
+        for (M, N, K) in [(128, 768, 768), (128, 3072, 768), (100, 768, 3072), (128, 2304, 768), (7, 200, 768)]:
+            a, b = rnd(M, K, dtype=bf, scale=0.5), rnd(N, K, dtype=bf, scale=0.5, seed=1)
+            bias, res = rnd(N, seed=4), rnd(M, N, dtype=bf, seed=2)
+            outs = {}
+            for mode in (1, 2):
+                ops.set_gemm_skinny(mode)
+                o1, o2, o3 = (torch.empty(M, N, dtype=bf, device=DEV) for _ in range(3))
+                o4 = torch.empty(M, N, device=DEV)
+                ops.gemm_group([ops.GemmSpec(a, b, o1, bias=bias)], backend=ops.GEMM_TCGEN05)
+                ops.gemm_group([ops.GemmSpec(a, b, o2, bias=bias, act=ops.ACT_RELU)], backend=ops.GEMM_TCGEN05)
+                ops.gemm_group([ops.GemmSpec(a, b, o3, bias=bias, residual=res)], backend=ops.GEMM_TCGEN05)
+                ops.gemm_group([ops.GemmSpec(a, b, o4, bias=bias)], backend=ops.GEMM_TCGEN05)
+                torch.cuda.synchronize()
+                outs[mode] = (o1, o2, o3, o4)
+            for x, y in zip(outs[1], outs[2]):
+                assert torch.equal(x, y), (M, N, K)
+            ref = a.float() @ b.float().t() + bias
+            assert rel_err(outs[2][3], ref) < 2e-3
+    finally:
+        ops.set_gemm_skinny(0)
+
+
+@pytest.mark.parametrize("skinny", [1, 2])
+def test_gemm_row_argmax_epilogue(skinny):
+    """Vocabulary projection without logits (m3ae_decoder.py:136,151-153): the epilogue's per-64-column (max, column) partials,
+    reduced by argmax_partials, equal torch.argmax of the fp32 logits the same GEMM writes — ties included (first wins)."""
+    bf = torch.bfloat16
+    M, N, K = 128, 30522, 768
+    a, b = rnd(M, K, dtype=bf, scale=0.5), rnd(N, K, dtype=bf, scale=0.5, seed=1)
+    b[20000] = b[77]        # duplicated vocabulary rows: exact ties between far-apart columns ...
+    b[78] = b[77]           # ... and inside one 64-column group
+    a[3] = b[77] * 4        # row 3's maximum is (very likely) on the tied columns
+    bias = rnd(N, seed=4) * 0.01
+    bias[20000] = bias[77]
+    bias[78] = bias[77]
+    G = (N + 63) // 64
+    try:
+        ops.set_gemm_skinny(skinny)
+        logits = torch.empty(M, N, device=DEV)
+        av, ai = torch.empty(G, M, device=DEV), torch.empty(G, M, dtype=torch.int32, device=DEV)
+        ops.gemm_group([ops.GemmSpec(a, b, logits, bias=bias, amax=(av, ai))], backend=ops.GEMM_TCGEN05)
+        ids = ops.argmax_partials(av, ai)
+        av2, ai2 = torch.zeros_like(av), torch.zeros_like(ai)
+        ops.gemm_group([ops.GemmSpec(a, b, None, bias=bias, amax=(av2, ai2))], backend=ops.GEMM_TCGEN05)  # no logits at all
+        ids2 = ops.argmax_partials(av2, ai2)
+        torch.cuda.synchronize()
+    finally:
+        ops.set_gemm_skinny(0)
+    want = logits.argmax(dim=1)
+    assert torch.equal(ids, want) and torch.equal(ids2, want)
+    assert int(want[3]) == 77, "tie case not exercised"
+    assert torch.equal(ops.argmax_rows(logits), want)
