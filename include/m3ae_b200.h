@@ -282,6 +282,10 @@ int m3ae_set_gemm_cta_pair(int32_t mode);
 /* Single-CTA launches (every problem M <= 128): 0 = auto (128x64 tiles when 128x256 tiles would occupy less than a third of
  * the SMs), 1 = always 128x256, 2 = always 128x64.  Results are identical.  Process-global test hook. */
 int m3ae_set_gemm_skinny(int32_t mode);
+/* Programmatic dependent launch (every kernel of the library: cudaLaunchAttributeProgrammaticStreamSerialization +
+ * griddepcontrol.wait before the first global access): 1 = on, 0 = off (default; M3AE_PDL=1 in the environment turns it
+ * on).  Results are identical; measured neutral on the fine-tune step and harmful inside CUDA graphs.  Process-global. */
+int m3ae_set_pdl(int32_t on);
 /* Test hook: 1 = m3ae_layernorm_bwd loads rows through registers only (cross-checks the cp.async.bulk staging ring), 0 = auto. */
 int m3ae_set_layernorm_bwd_staging(int32_t registers_only);
 

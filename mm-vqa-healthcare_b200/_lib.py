@@ -109,6 +109,7 @@ SIGNATURES = {
     "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
     "m3ae_argmax_partials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "m3ae_set_gemm_skinny": (C.c_int, [C.c_int32]),
+    "m3ae_set_pdl": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_cta_pair": (C.c_int, [C.c_int32]),
     "m3ae_set_layernorm_bwd_staging": (C.c_int, [C.c_int32]),
 }

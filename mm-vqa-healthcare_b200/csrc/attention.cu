@@ -22,6 +22,7 @@ constexpr int KC = 32;  // keys per chunk == warp width
 
 template <typename T, int DH, int ROWS_PER_WARP>
 __global__ void __launch_bounds__(128) attn_fwd_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int WARPS = 4;
   constexpr int ROWS = WARPS * ROWS_PER_WARP;
   constexpr int ND = DH / 32;
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const m3ae_attn_params_t 
 // probs[b,h,i,j] = dropout(exp(scale*q_i.k_j + mask_j - lse_i))  -- only for output_attentions=True
 template <typename T, int DH>
 __global__ void __launch_bounds__(128) attn_probs_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int b = blockIdx.z, h = blockIdx.y;
   const int qi = blockIdx.x * 4 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -131,6 +133,7 @@ __global__ void __launch_bounds__(128) attn_probs_kernel(const m3ae_attn_params_
 // delta[b,h,i] = sum_d dO[i,d] * O[i,d]
 template <typename T, int DH>
 __global__ void __launch_bounds__(128) attn_delta_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int b = blockIdx.z, h = blockIdx.y;
   const int qi = blockIdx.x * 4 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -147,6 +150,7 @@ __global__ void __launch_bounds__(128) attn_delta_kernel(const m3ae_attn_params_
 // bf16, dh = 64, heads packed side by side in a row (the fusion stack's ctx layout): one warp per token row, 16-byte loads,
 // 8 lanes share a head.  Streams O and dO once at full sector efficiency (the generic kernel above issues 2-byte loads).
 __global__ void __launch_bounds__(256) attn_delta_rows_bf16_64_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int lane = threadIdx.x & 31;
   const int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);  // token row b*Lq + qi
   if (r >= (int64_t)P.B * P.Lq) return;
@@ -176,6 +180,7 @@ __global__ void __launch_bounds__(256) attn_delta_rows_bf16_64_kernel(const m3ae
 // dQ_i = scale * sum_j dS_ij K_j,  dS_ij = P_ij (dP_ij - delta_i),  dP_ij = keep_ij/(1-p) * dO_i.V_j
 template <typename T, int DH>
 __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int RPW = 4, ROWS = 16, ND = DH / 32;
   __shared__ float sK[KC][DH + 1];
   __shared__ float sV[KC][DH + 1];
@@ -256,6 +261,7 @@ __global__ void __launch_bounds__(128) attn_bwd_dq_kernel(const m3ae_attn_params
 // dV_j = sum_i P'_ij dO_i,  dK_j = scale * sum_i dS_ij Q_i  (one lane <-> one query inside a 32-query chunk)
 template <typename T, int DH>
 __global__ void __launch_bounds__(128) attn_bwd_dkv_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int RPW = 4, ROWS = 16, ND = DH / 32;
   __shared__ float sQ[KC][DH + 1];
   __shared__ float sdO[KC][DH + 1];
@@ -356,6 +362,7 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
                                                          const T* __restrict__ vc, int64_t ldk, int64_t ldv, int64_t bsk,
                                                          int64_t bsv, T* __restrict__ out, int64_t ldo, int H, int len,
                                                          float scale) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int ND = DH / 32;
   __shared__ float sm[4], sl[4], so[4][DH];
   const int b = blockIdx.x / H, h = blockIdx.x % H;
@@ -416,6 +423,7 @@ __global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __res
                                                               const bf16* __restrict__ vc, int64_t ldk, int64_t ldv, int64_t bsk,
                                                               int64_t bsv, bf16* __restrict__ out, int64_t ldo, int H, int len,
                                                               float scale) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int NCH = DH / 8;        // 16-byte chunks per row (12 for dh 96, 8 for dh 64)
   constexpr int CPL = NCH / 4;       // chunks per lane in the score phase (4 lanes per key)
   constexpr int NG = 128 / NCH;      // key residues in the P V phase (10 / 16)
@@ -533,6 +541,7 @@ __global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __res
 
 template <typename T>
 __global__ void __launch_bounds__(256) argmax_rows_kernel(const T* __restrict__ x, int64_t ld, int64_t* __restrict__ out, int N) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   __shared__ float sv[8];
   __shared__ int si[8];
   const T* row = x + (size_t)blockIdx.x * ld;
@@ -560,6 +569,7 @@ __global__ void __launch_bounds__(256) argmax_rows_kernel(const T* __restrict__ 
 template <typename TO>
 __global__ void decoder_embed_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ pos,
                                      const float* __restrict__ table, const float* __restrict__ pe, TO* __restrict__ out, int D) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   // target_embed += positional_encoding(target_embed)  ==> 2*E[id] + pe[pos]   (m3ae_decoder.py:125-127, :36)
   const int64_t r = blockIdx.x;
   const float* e = table + (size_t)ids[r] * D;
@@ -573,8 +583,8 @@ __global__ void decoder_embed_kernel(const int64_t* __restrict__ ids, const int3
 template <typename T>
 void launch_probs(const m3ae_attn_params_t* p, cudaStream_t st) {
   dim3 g2((p->Lq + 3) / 4, p->H, p->B);
-  if (p->dh == 64) attn_probs_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
-  else attn_probs_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
+  if (p->dh == 64) M3AE_LAUNCH((attn_probs_kernel<T, 64>), g2, 128, 0, st, *p);
+  else M3AE_LAUNCH((attn_probs_kernel<T, 96>), g2, 128, 0, st, *p);
   count_launch();
 }
 
@@ -582,10 +592,10 @@ template <typename T>
 int launch_generic_fwd(const m3ae_attn_params_t* p, cudaStream_t st) {
   if (p->dh == 64) {
     dim3 grid((p->Lq + 31) / 32, p->H, p->B);
-    attn_fwd_kernel<T, 64, 8><<<grid, 128, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_fwd_kernel<T, 64, 8>), grid, 128, 0, st, *p);
   } else {
     dim3 grid((p->Lq + 15) / 16, p->H, p->B);
-    attn_fwd_kernel<T, 96, 4><<<grid, 128, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_fwd_kernel<T, 96, 4>), grid, 128, 0, st, *p);
   }
   count_launch();
   if (p->probs) launch_probs<T>(p, st);
@@ -598,13 +608,13 @@ int launch_generic_bwd(const m3ae_attn_params_t* p, cudaStream_t st) {
   dim3 g1((p->Lq + 15) / 16, p->H, p->B);
   dim3 g2((p->Lk + 15) / 16, p->H, p->B);
   if (p->dh == 64) {
-    attn_delta_kernel<T, 64><<<g0, 128, 0, st>>>(*p);
-    attn_bwd_dq_kernel<T, 64><<<g1, 128, 0, st>>>(*p);
-    attn_bwd_dkv_kernel<T, 64><<<g2, 128, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_delta_kernel<T, 64>), g0, 128, 0, st, *p);
+    M3AE_LAUNCH((attn_bwd_dq_kernel<T, 64>), g1, 128, 0, st, *p);
+    M3AE_LAUNCH((attn_bwd_dkv_kernel<T, 64>), g2, 128, 0, st, *p);
   } else {
-    attn_delta_kernel<T, 96><<<g0, 128, 0, st>>>(*p);
-    attn_bwd_dq_kernel<T, 96><<<g1, 128, 0, st>>>(*p);
-    attn_bwd_dkv_kernel<T, 96><<<g2, 128, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_delta_kernel<T, 96>), g0, 128, 0, st, *p);
+    M3AE_LAUNCH((attn_bwd_dq_kernel<T, 96>), g1, 128, 0, st, *p);
+    M3AE_LAUNCH((attn_bwd_dkv_kernel<T, 96>), g2, 128, 0, st, *p);
   }
   count_launch(); count_launch(); count_launch();
   return M3AE_OK;
@@ -626,10 +636,10 @@ int validate(const m3ae_attn_params_t* p, bool bwd) {
 void launch_delta_bf16_64(const m3ae_attn_params_t* p, cudaStream_t st) {
   if ((p->ldo % 8) == 0 && (((uintptr_t)p->out | (uintptr_t)p->dout) & 15) == 0) {
     const int64_t rows = (int64_t)p->B * p->Lq;
-    attn_delta_rows_bf16_64_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_delta_rows_bf16_64_kernel), (unsigned)((rows + 7) / 8), 256, 0, st, *p);
   } else {
     dim3 g0((p->Lq + 3) / 4, p->H, p->B);
-    attn_delta_kernel<bf16, 64><<<g0, 128, 0, st>>>(*p);
+    M3AE_LAUNCH((attn_delta_kernel<bf16, 64>), g0, 128, 0, st, *p);
   }
   count_launch();
 }
@@ -686,13 +696,13 @@ int decode_attn(const void* q, int64_t ldq, const void* kc, const void* vc, int6
   // bf16 with 16-byte aligned rows and a cache that fits the score buffer: the bandwidth kernel
   if (dtype == M3AE_BF16 && len <= DEC_MAX_LEN && ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && bsk % 8 == 0 && bsv % 8 == 0 &&
       ((((uintptr_t)q) | ((uintptr_t)kc) | ((uintptr_t)vc)) & 15) == 0) {
-    if (dh == 64) decode_attn_bf16_kernel<64><<<B * H, 128, 0, st>>>((const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
-    else decode_attn_bf16_kernel<96><<<B * H, 128, 0, st>>>((const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
+    if (dh == 64) M3AE_LAUNCH((decode_attn_bf16_kernel<64>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
+    else M3AE_LAUNCH((decode_attn_bf16_kernel<96>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
     count_launch();
     M3AE_CUDA(cudaGetLastError());
     return M3AE_OK;
   }
-#define DA(T, DH) decode_attn_kernel<T, DH><<<B * H, 128, 0, st>>>((const T*)q, ldq, (const T*)kc, (const T*)vc, ldk, ldv, bsk, bsv, (T*)out, ldo, H, len, scale)
+#define DA(T, DH) M3AE_LAUNCH((decode_attn_kernel<T, DH>), B * H, 128, 0, st, (const T*)q, ldq, (const T*)kc, (const T*)vc, ldk, ldv, bsk, bsv, (T*)out, ldo, H, len, scale)
   if (dtype == M3AE_BF16) { if (dh == 64) DA(bf16, 64); else DA(bf16, 96); }
   else { if (dh == 64) DA(float, 64); else DA(float, 96); }
 #undef DA
@@ -706,6 +716,7 @@ int decode_attn(const void* q, int64_t ldq, const void* kc, const void* vc, int6
 // 4 blocks, 20 us per token step); larger value wins, then the smaller column.
 __global__ void __launch_bounds__(256) argmax_partials_kernel(const float* __restrict__ val, const int32_t* __restrict__ idx, int G, int M,
                                                              int64_t* __restrict__ out) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   __shared__ float sv[8];
   __shared__ int si[8];
   const int row = blockIdx.x;
@@ -731,7 +742,7 @@ __global__ void __launch_bounds__(256) argmax_partials_kernel(const float* __res
   }
 }
 int argmax_partials(const float* val, const int32_t* idx, int G, int M, int64_t* out, cudaStream_t st) {
-  argmax_partials_kernel<<<(unsigned)M, 256, 0, st>>>(val, idx, G, M, out);
+  M3AE_LAUNCH((argmax_partials_kernel), (unsigned)M, 256, 0, st, val, idx, G, M, out);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -739,8 +750,8 @@ int argmax_partials(const float* val, const int32_t* idx, int G, int M, int64_t*
 
 int argmax_rows(const void* x, int64_t ld, int64_t* out, int64_t M, int N, int dtype, cudaStream_t st) {
   M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "argmax_rows: empty input");
-  if (dtype == M3AE_BF16) argmax_rows_kernel<bf16><<<(unsigned)M, 256, 0, st>>>((const bf16*)x, ld, out, N);
-  else argmax_rows_kernel<float><<<(unsigned)M, 256, 0, st>>>((const float*)x, ld, out, N);
+  if (dtype == M3AE_BF16) M3AE_LAUNCH((argmax_rows_kernel<bf16>), (unsigned)M, 256, 0, st, (const bf16*)x, ld, out, N);
+  else M3AE_LAUNCH((argmax_rows_kernel<float>), (unsigned)M, 256, 0, st, (const float*)x, ld, out, N);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -749,8 +760,8 @@ int argmax_rows(const void* x, int64_t ld, int64_t* out, int64_t M, int N, int d
 int decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M, int D,
                   int out_dtype, cudaStream_t st) {
   M3AE_CHECK(M > 0 && D > 0, M3AE_ERR_INVALID, "decoder_embed: empty input");
-  if (out_dtype == M3AE_BF16) decoder_embed_kernel<bf16><<<(unsigned)M, 256, 0, st>>>(ids, pos, table, pe, (bf16*)out, D);
-  else decoder_embed_kernel<float><<<(unsigned)M, 256, 0, st>>>(ids, pos, table, pe, (float*)out, D);
+  if (out_dtype == M3AE_BF16) M3AE_LAUNCH((decoder_embed_kernel<bf16>), (unsigned)M, 256, 0, st, ids, pos, table, pe, (bf16*)out, D);
+  else M3AE_LAUNCH((decoder_embed_kernel<float>), (unsigned)M, 256, 0, st, ids, pos, table, pe, (float*)out, D);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

@@ -106,6 +106,7 @@ __device__ __forceinline__ void load_keep_tile(uint64_t* sBits, const m3ae_attn_
 // ------------------------------------------------------------------------------------------------ forward
 template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sQ[BM][LDS];
   __shared__ __align__(16) bf16 sK[BN][LDS];
@@ -241,6 +242,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_fwd_mma_kernel(const m3ae_at
 // ------------------------------------------------------------------------------------------------ backward: dQ
 template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sQ[BM][LDS];   // Q, then dQ staging
   __shared__ __align__(16) bf16 sdO[BM][LDS];
@@ -358,6 +360,7 @@ __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dq_mma_kernel(const m3ae
 // Works on the transposed problem: rows = keys (16 per warp), columns = queries (64 per smem tile).
 template <int NWARPS, int BN>
 __global__ void __launch_bounds__(NWARPS * 32) attn_bwd_dkv_mma_kernel(const m3ae_attn_params_t P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int BM = NWARPS * 16, NT = NWARPS * 32, NJ = BN / 8, NK2 = BN / 16;
   __shared__ __align__(16) bf16 sK[BM][LDS];   // K, then dK staging
   __shared__ __align__(16) bf16 sV[BM][LDS];   // V, then dV staging
@@ -518,15 +521,15 @@ inline int pick_tile(int L) { return L <= 32 ? 32 : ((L + 47) / 48 * 48 <= (L + 
   do {                                                                                                 \
     const int bm = pick_tile(ROWS_L), bn = pick_tile(COLS_L);                                          \
     dim3 grid((ROW_COUNT + bm - 1) / bm, p->H, p->B);                                                  \
-    if (bm == 32 && bn == 32) KERNEL<2, 32><<<grid, 64, 0, st>>>(*p);                                  \
-    else if (bm == 32 && bn == 48) KERNEL<2, 48><<<grid, 64, 0, st>>>(*p);                             \
-    else if (bm == 32) KERNEL<2, 64><<<grid, 64, 0, st>>>(*p);                                         \
-    else if (bm == 48 && bn == 32) KERNEL<3, 32><<<grid, 96, 0, st>>>(*p);                             \
-    else if (bm == 48 && bn == 48) KERNEL<3, 48><<<grid, 96, 0, st>>>(*p);                             \
-    else if (bm == 48) KERNEL<3, 64><<<grid, 96, 0, st>>>(*p);                                         \
-    else if (bn == 32) KERNEL<4, 32><<<grid, 128, 0, st>>>(*p);                                        \
-    else if (bn == 48) KERNEL<4, 48><<<grid, 128, 0, st>>>(*p);                                        \
-    else KERNEL<4, 64><<<grid, 128, 0, st>>>(*p);                                                      \
+    if (bm == 32 && bn == 32) M3AE_LAUNCH((KERNEL<2, 32>), grid, 64, 0, st, *p);                                  \
+    else if (bm == 32 && bn == 48) M3AE_LAUNCH((KERNEL<2, 48>), grid, 64, 0, st, *p);                             \
+    else if (bm == 32) M3AE_LAUNCH((KERNEL<2, 64>), grid, 64, 0, st, *p);                                         \
+    else if (bm == 48 && bn == 32) M3AE_LAUNCH((KERNEL<3, 32>), grid, 96, 0, st, *p);                             \
+    else if (bm == 48 && bn == 48) M3AE_LAUNCH((KERNEL<3, 48>), grid, 96, 0, st, *p);                             \
+    else if (bm == 48) M3AE_LAUNCH((KERNEL<3, 64>), grid, 96, 0, st, *p);                                         \
+    else if (bn == 32) M3AE_LAUNCH((KERNEL<4, 32>), grid, 128, 0, st, *p);                                        \
+    else if (bn == 48) M3AE_LAUNCH((KERNEL<4, 48>), grid, 128, 0, st, *p);                                        \
+    else M3AE_LAUNCH((KERNEL<4, 64>), grid, 128, 0, st, *p);                                                      \
     count_launch();                                                                                    \
   } while (0)
 

@@ -256,6 +256,7 @@ enum { F_KV = 0, F_QF0 = 1, F_QF1 = 2, F_SF = 3, F_SE = 4, F_PF = 5, F_OF = 6, F
 
 template <bool DROP>
 __global__ void __launch_bounds__(NT_FWD, 1) attn_fwd_tc_kernel(const __grid_constant__ TcAttn A) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const m3ae_attn_params_t& P = A.p;
@@ -601,6 +602,7 @@ constexpr int MAX_NKV = 4;
 
 template <bool DROP>
 __global__ void __launch_bounds__(NT_BWD, 1) attn_bwd_tc_kernel(const __grid_constant__ TcAttn A) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const m3ae_attn_params_t& P = A.p;
@@ -1044,8 +1046,8 @@ int attn_fwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st) {
   int rc = setup(p, false, &A, &smem);
   if (rc) return rc;
   dim3 grid(p->H, p->B);
-  if (p->drop_p > 0.f) attn_fwd_tc_kernel<true><<<grid, NT_FWD, smem, st>>>(A);
-  else attn_fwd_tc_kernel<false><<<grid, NT_FWD, smem, st>>>(A);
+  if (p->drop_p > 0.f) M3AE_LAUNCH((attn_fwd_tc_kernel<true>), grid, NT_FWD, smem, st, A);
+  else M3AE_LAUNCH((attn_fwd_tc_kernel<false>), grid, NT_FWD, smem, st, A);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -1067,8 +1069,8 @@ int attn_bwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st) {
   if (rc) return rc;
   launch_delta_bf16_64(p, st);
   dim3 grid(p->H, p->B);
-  if (p->drop_p > 0.f) attn_bwd_tc_kernel<true><<<grid, NT_BWD, smem, st>>>(A);
-  else attn_bwd_tc_kernel<false><<<grid, NT_BWD, smem, st>>>(A);
+  if (p->drop_p > 0.f) M3AE_LAUNCH((attn_bwd_tc_kernel<true>), grid, NT_BWD, smem, st, A);
+  else M3AE_LAUNCH((attn_bwd_tc_kernel<false>), grid, NT_BWD, smem, st, A);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

@@ -84,6 +84,14 @@ int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, vo
 extern bool force_generic_epilogue;
 extern int gemm_cta_pair_mode;
 extern int gemm_skinny_mode;
+static int g_pdl_mode = -1;  // -1: not decided yet (M3AE_PDL environment variable), 0 off, 1 on
+bool pdl_on() {
+  if (g_pdl_mode < 0) {
+    const char* e = getenv("M3AE_PDL");
+    g_pdl_mode = (e != nullptr && e[0] == '1') ? 1 : 0;  // opt-in: measured neutral on the fusion step, harmful inside CUDA graphs
+  }
+  return g_pdl_mode == 1;
+}
 int argmax_partials(const float*, const int32_t*, int, int, int64_t*, cudaStream_t);
 extern bool ln_bwd_force_registers;
 static int g_attn_backend = M3AE_GEMM_AUTO;
@@ -224,6 +232,10 @@ int m3ae_argmax_partials(const float* amax_val, const int32_t* amax_idx, int32_t
   ARCH_GATE();
   M3AE_CHECK(amax_val && amax_idx && ids && n_groups > 0 && M > 0, M3AE_ERR_INVALID, "argmax_partials: null pointer or empty input");
   return argmax_partials(amax_val, amax_idx, n_groups, M, ids, (cudaStream_t)stream);
+}
+int m3ae_set_pdl(int32_t on) {
+  g_pdl_mode = on ? 1 : 0;
+  return M3AE_OK;
 }
 int m3ae_set_gemm_skinny(int32_t mode) {
   M3AE_CHECK(mode >= 0 && mode <= 2, M3AE_ERR_INVALID, "m3ae_set_gemm_skinny: mode %d not in {0 auto, 1 never, 2 always}", mode);

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #include "../../include/m3ae_b200.h"
 
@@ -34,6 +35,40 @@ void set_last_error(const char* fmt, ...);
 
 int check_device_sm100();  // 0 when the current device is sm_100, else error code (and sets last error)
 int sm_count();
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// Opt-in (m3ae_set_pdl(1) or M3AE_PDL=1).  Every kernel of this library can be launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization and starts with pdl_sync(): griddepcontrol.launch_dependents lets the
+// NEXT kernel of the stream be scheduled as soon as SMs free up (its CTAs then sit in griddepcontrol.wait),
+// griddepcontrol.wait blocks until the PREVIOUS kernel has completed and its writes are visible.  Every kernel waits
+// before it exits, so completion is transitive; kernels of other libraries (PyTorch) in between are ordinary
+// stream-ordered launches.  Without the attribute griddepcontrol.* are no-ops.
+// Measured on B200 (profiles/r2_pdl_ab.txt): the ~660 launches of a fine-tune step gain nothing (14.83 / 14.71 ms off vs
+// 14.83 / 14.61 ms on: back-to-back launches of one stream already overlap their launch latency), and inside the decoder's
+// CUDA graph programmatic edges are slower (157 -> 182 us per token step).  Hence off by default.
+bool pdl_on();
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+  pdl_launch_dependents();
+  pdl_wait();
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_on() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define M3AE_LAUNCH(kernel, grid, block, smem, st, ...) (void)::m3ae::launch_k(kernel, dim3(grid), dim3(block), (size_t)(smem), st, ##__VA_ARGS__)
 
 // ---------------------------------------------------------------- dtype helpers
 typedef __nv_bfloat16 bf16;

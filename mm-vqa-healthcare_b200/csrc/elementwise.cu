@@ -15,6 +15,7 @@ namespace {
 
 template <typename T>
 __global__ void act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t n, int act) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     y[i] = from_f32<T>(act_exact(act, to_f32<T>(x[i])));
@@ -23,6 +24,7 @@ __global__ void act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64
 // dx = dy * act'(x), x = the forward pre-activation
 template <typename T>
 __global__ void act_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t n, int act) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     dx[i] = from_f32<T>(to_f32<T>(dy[i]) * act_exact_grad(act, to_f32<T>(x[i])));
@@ -33,6 +35,7 @@ __global__ void act_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x
 __global__ void __launch_bounds__(256) bce_logits_kernel(const float* __restrict__ x, const float* __restrict__ t,
                                                           float* __restrict__ loss_out, float* __restrict__ dx, int64_t n,
                                                           float scale_loss, float scale_grad) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   float acc = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -62,6 +65,7 @@ __global__ void __launch_bounds__(256) bce_logits_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) cross_entropy_kernel(const float* __restrict__ x, int64_t ld, const int64_t* __restrict__ target,
                                                              const float* __restrict__ row_weight, float* __restrict__ loss_out,
                                                              float* __restrict__ dx, int64_t ldd, int V, int64_t ignore_index) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t row = blockIdx.x;
   const float* xr = x + row * ld;
   const int64_t tg = target[row];
@@ -116,6 +120,7 @@ struct DropBitsGroup {
 
 // One thread = one uint32 of keep bits = 4 Philox evaluations (independent: good ILP).  Streaming, no shared memory.
 __global__ void __launch_bounds__(256) dropout_bits_kernel(const __grid_constant__ DropBitsGroup G) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t total = G.word_begin[G.n];
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += stride) {
@@ -155,8 +160,8 @@ unsigned grid_for(int64_t n, int threads) {
 int activation_fwd(const void* x, void* y, int64_t n, int act, int dtype, cudaStream_t st) {
   M3AE_CHECK(n > 0, M3AE_ERR_INVALID, "activation_fwd: empty input");
   M3AE_CHECK(act >= M3AE_ACT_NONE && act <= M3AE_ACT_TANH, M3AE_ERR_INVALID, "activation_fwd: unknown activation %d", act);
-  if (dtype == M3AE_BF16) act_fwd_kernel<bf16><<<grid_for(n, 256), 256, 0, st>>>((const bf16*)x, (bf16*)y, n, act);
-  else act_fwd_kernel<float><<<grid_for(n, 256), 256, 0, st>>>((const float*)x, (float*)y, n, act);
+  if (dtype == M3AE_BF16) M3AE_LAUNCH((act_fwd_kernel<bf16>), grid_for(n, 256), 256, 0, st, (const bf16*)x, (bf16*)y, n, act);
+  else M3AE_LAUNCH((act_fwd_kernel<float>), grid_for(n, 256), 256, 0, st, (const float*)x, (float*)y, n, act);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -165,8 +170,8 @@ int activation_fwd(const void* x, void* y, int64_t n, int act, int dtype, cudaSt
 int activation_bwd(const void* dy, const void* x, void* dx, int64_t n, int act, int dtype, cudaStream_t st) {
   M3AE_CHECK(n > 0, M3AE_ERR_INVALID, "activation_bwd: empty input");
   M3AE_CHECK(act >= M3AE_ACT_NONE && act <= M3AE_ACT_TANH, M3AE_ERR_INVALID, "activation_bwd: unknown activation %d", act);
-  if (dtype == M3AE_BF16) act_bwd_kernel<bf16><<<grid_for(n, 256), 256, 0, st>>>((const bf16*)dy, (const bf16*)x, (bf16*)dx, n, act);
-  else act_bwd_kernel<float><<<grid_for(n, 256), 256, 0, st>>>((const float*)dy, (const float*)x, (float*)dx, n, act);
+  if (dtype == M3AE_BF16) M3AE_LAUNCH((act_bwd_kernel<bf16>), grid_for(n, 256), 256, 0, st, (const bf16*)dy, (const bf16*)x, (bf16*)dx, n, act);
+  else M3AE_LAUNCH((act_bwd_kernel<float>), grid_for(n, 256), 256, 0, st, (const float*)dy, (const float*)x, (float*)dx, n, act);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -176,7 +181,7 @@ int bce_with_logits(const float* logits, const float* targets, float* loss_out, 
                     float scale_grad, cudaStream_t st) {
   M3AE_CHECK(n > 0, M3AE_ERR_INVALID, "bce_with_logits: empty input");
   M3AE_CUDA(cudaMemsetAsync(loss_out, 0, sizeof(float), st));
-  bce_logits_kernel<<<grid_for(n, 256), 256, 0, st>>>(logits, targets, loss_out, dlogits, n, scale_loss, scale_grad);
+  M3AE_LAUNCH((bce_logits_kernel), grid_for(n, 256), 256, 0, st, logits, targets, loss_out, dlogits, n, scale_loss, scale_grad);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -201,7 +206,7 @@ int dropout_bits(const m3ae_dropbits_item_t* items, int n, cudaStream_t st) {
   }
   G.word_begin[n] = words;
   for (int i = n + 1; i <= M3AE_MAX_DROPBITS; ++i) G.word_begin[i] = words;
-  dropout_bits_kernel<<<grid_for(words, 256), 256, 0, st>>>(G);
+  M3AE_LAUNCH((dropout_bits_kernel), grid_for(words, 256), 256, 0, st, G);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -211,7 +216,7 @@ int cross_entropy(const float* logits, int64_t ld, const int64_t* target, const 
                   int64_t ldd, int64_t M, int V, int64_t ignore_index, cudaStream_t st) {
   M3AE_CHECK(M > 0 && V > 0, M3AE_ERR_INVALID, "cross_entropy: empty input");
   M3AE_CUDA(cudaMemsetAsync(loss_out, 0, sizeof(float), st));
-  cross_entropy_kernel<<<(unsigned)M, 256, 0, st>>>(logits, ld, target, row_weight, loss_out, dlogits, ldd, V, ignore_index);
+  M3AE_LAUNCH((cross_entropy_kernel), (unsigned)M, 256, 0, st, logits, ld, target, row_weight, loss_out, dlogits, ldd, V, ignore_index);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

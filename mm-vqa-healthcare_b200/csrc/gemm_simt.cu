@@ -31,6 +31,7 @@ struct SimtProblem {
 
 template <typename TIn>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const SimtProblem P) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   __shared__ float As[TK][TM + 4];
   __shared__ float Bs[TK][TN + 4];
   const TIn* __restrict__ A = (const TIn*)P.a;
@@ -112,8 +113,8 @@ int gemm_simt_launch(const m3ae_gemm_problem_t* probs, int n, int in_dtype, cuda
     P.M = g.M; P.N = g.N; P.K = g.K; P.split_k = g.split_k;
     epi_to_dev(g.epi, &P.epi);
     dim3 grid((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, g.split_k);
-    if (in_dtype == M3AE_BF16) gemm_simt_kernel<bf16><<<grid, 256, 0, stream>>>(P);
-    else gemm_simt_kernel<float><<<grid, 256, 0, stream>>>(P);
+    if (in_dtype == M3AE_BF16) M3AE_LAUNCH((gemm_simt_kernel<bf16>), grid, 256, 0, stream, P);
+    else M3AE_LAUNCH((gemm_simt_kernel<float>), grid, 256, 0, stream, P);
     count_launch();
     M3AE_CUDA(cudaGetLastError());
   }

@@ -212,6 +212,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
   else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's
+  // tail; nothing below may touch global memory before that kernel has completed
+  pdl_sync();
 
   // Producer and MMA warps run their control flow with ALL lanes (convergent) and elect one lane per batch of
   // asynchronous operations.  Issuing from inside an `if (lane == 0)` region makes the compiler feed every TMA / MMA
@@ -810,13 +813,15 @@ int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = Cfg<CL, BNV>::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_on() ? 2 : 1;
   M3AE_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<CL, BNV>, P));
   count_launch();
   M3AE_CUDA(cudaGetLastError());

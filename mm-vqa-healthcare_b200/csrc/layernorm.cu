@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const T* __restri
                                                               const float* __restrict__ beta, T* __restrict__ y,
                                                               float* __restrict__ mean_out, float* __restrict__ rstd_out,
                                                               int64_t M, int H, float eps) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int VN = Vec<T>::N;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
@@ -126,6 +127,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
                                                               float* __restrict__ dcolsum, int64_t M, int H,
                                                               T* __restrict__ dx_drop, float drop_p, uint64_t drop_seed,
                                                               uint64_t drop_stream, const uint8_t* __restrict__ drop_bits) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   constexpr int VN = Vec<T>::N;
   extern __shared__ __align__(128) float red[];  // [LN_WARPS][H] floats | RING: [LN_WARPS][LN_RING][2][H] T | [LN_WARPS][LN_RING] barriers
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -294,6 +296,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32, LN_BWD_CTAS_PER_SM) ln_bwd_kern
 
 template <typename T>
 __global__ void colsum_kernel(const T* __restrict__ x, float* __restrict__ out, int64_t M, int N, int64_t ld, int rows_per_cta) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   // block = (32 columns) x (8 row lanes); each CTA covers rows [blockIdx.y*rows_per_cta, ...)
   __shared__ float red[8][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
@@ -316,6 +319,7 @@ __global__ void colsum_kernel(const T* __restrict__ x, float* __restrict__ out, 
 // (512 B), 4 rows in flight per thread.  Bias gradients of the fused QKV / KV / Q / FFN-up projections.
 __global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const bf16* __restrict__ x, float* __restrict__ out, int64_t M, int N,
                                                               int64_t ld, int rows_per_cta) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   __shared__ float red[8][32][9];
   const int c = (blockIdx.x * 32 + threadIdx.x) * 8;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
@@ -367,11 +371,13 @@ __global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const bf16* __rest
 
 template <typename TS, typename TD>
 __global__ void cast_kernel(const TS* __restrict__ src, TD* __restrict__ dst, int64_t n) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = from_f32<TD>(to_f32<TS>(src[i]));
 }
 // 8 fp32 -> 8 bf16 per thread-iteration (n % 8 == 0, aligned)
 __global__ void cast_f32_bf16_vec_kernel(const float4* __restrict__ src, uint4* __restrict__ dst, int64_t n8) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
     const float4 a = src[2 * i], b = src[2 * i + 1];
@@ -390,6 +396,7 @@ struct CastGroup {
   int8_t sd[M3AE_MAX_CAST_GROUP], dd[M3AE_MAX_CAST_GROUP];
 };
 __global__ void cast_group_kernel(const __grid_constant__ CastGroup G) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int it = blockIdx.y;
   const int64_t n = G.n[it];
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -428,6 +435,7 @@ __global__ void cast_group_kernel(const __grid_constant__ CastGroup G) {
 
 template <typename TI, typename TO>
 __global__ void add_rowvec_kernel(const TI* __restrict__ a, const float* __restrict__ b, TO* __restrict__ out, int64_t M, int N) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t total = M * N;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
@@ -437,6 +445,7 @@ __global__ void add_rowvec_kernel(const TI* __restrict__ a, const float* __restr
 template <typename T>
 __global__ void dropout_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int N, int64_t ld, float p,
                                      uint64_t seed, uint64_t stream_id) {
+  pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
   const int64_t total = M * N;
   const float inv = drop_keep_scale(p);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -453,7 +462,7 @@ int layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
                   float eps, int dtype, cudaStream_t st) {
   M3AE_CHECK(M > 0, M3AE_ERR_INVALID, "layernorm: empty input");
   const unsigned grid = (unsigned)((M + LN_WARPS - 1) / LN_WARPS);
-#define LN_FWD(T, HV) ln_fwd_kernel<T, HV><<<grid, LN_WARPS * 32, 0, st>>>((const T*)x, gamma, beta, (T*)y, mean, rstd, M, H, eps)
+#define LN_FWD(T, HV) M3AE_LAUNCH((ln_fwd_kernel<T, HV>), grid, LN_WARPS * 32, 0, st, (const T*)x, gamma, beta, (T*)y, mean, rstd, M, H, eps)
   if (dtype == M3AE_BF16 && H == 768) LN_FWD(bf16, 3);
   else if (dtype == M3AE_BF16 && H == 1536) LN_FWD(bf16, 6);
   else if (dtype == M3AE_F32 && H == 768) LN_FWD(float, 6);
@@ -480,7 +489,7 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   const unsigned grid = (unsigned)(want < cap ? want : cap);
   const size_t smem = (size_t)LN_WARPS * H * sizeof(float);
 #define LN_BWD(T, HV, RING, SMEM)                                                                                              \
-  ln_bwd_kernel<T, HV, RING><<<grid, LN_WARPS * 32, SMEM, st>>>((const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
+  M3AE_LAUNCH((ln_bwd_kernel<T, HV, RING>), grid, LN_WARPS * 32, SMEM, st, (const T*)dy, (const T*)x, mean, rstd, gamma, (T*)dx, dgamma, \
                                                                 dbeta, dcolsum, M, H, (T*)dx_drop, drop_p, drop_seed, drop_stream, (const uint8_t*)drop_bits)
   // the fusion stack's case (bf16, H = 768): rows staged through the bulk-copy ring (needs 16-byte aligned rows)
   const bool ring_ok = dtype == M3AE_BF16 && H == 768 && !ln_bwd_force_registers && ((((uintptr_t)x) | ((uintptr_t)dy)) & 15) == 0;
@@ -512,7 +521,7 @@ int colsum(const void* x, float* out, int64_t M, int N, int64_t ld, int dtype, c
     if (rb < 1) rb = 1;
     if ((int64_t)rb * 64 > M) rb = (int)((M + 63) / 64);
     const int rows_per = (int)((M + rb - 1) / rb);
-    colsum_bf16_vec_kernel<<<dim3(cb, rb), dim3(32, 8), 0, st>>>((const bf16*)x, out, M, N, ld, rows_per);
+    M3AE_LAUNCH((colsum_bf16_vec_kernel), dim3(cb, rb), dim3(32, 8), 0, st, (const bf16*)x, out, M, N, ld, rows_per);
     count_launch();
     M3AE_CUDA(cudaGetLastError());
     return M3AE_OK;
@@ -523,8 +532,8 @@ int colsum(const void* x, float* out, int64_t M, int N, int64_t ld, int dtype, c
   if ((int64_t)row_blocks * 64 > M) row_blocks = (int)((M + 63) / 64);
   const int rows_per = (int)((M + row_blocks - 1) / row_blocks);
   dim3 grid(col_blocks, row_blocks), block(32, 8);
-  if (dtype == M3AE_BF16) colsum_kernel<bf16><<<grid, block, 0, st>>>((const bf16*)x, out, M, N, ld, rows_per);
-  else colsum_kernel<float><<<grid, block, 0, st>>>((const float*)x, out, M, N, ld, rows_per);
+  if (dtype == M3AE_BF16) M3AE_LAUNCH((colsum_kernel<bf16>), grid, block, 0, st, (const bf16*)x, out, M, N, ld, rows_per);
+  else M3AE_LAUNCH((colsum_kernel<float>), grid, block, 0, st, (const float*)x, out, M, N, ld, rows_per);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -537,14 +546,14 @@ int cast(const void* src, int sd, void* dst, int dd, int64_t n, cudaStream_t st)
   if (sd == M3AE_F32 && dd == M3AE_BF16 && n % 8 == 0 && ((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0) {
     const int64_t n8 = n / 8;
     int64_t b = (n8 + threads - 1) / threads;
-    cast_f32_bf16_vec_kernel<<<(unsigned)(b < cap ? b : cap), threads, 0, st>>>((const float4*)src, (uint4*)dst, n8);
+    M3AE_LAUNCH((cast_f32_bf16_vec_kernel), (unsigned)(b < cap ? b : cap), threads, 0, st, (const float4*)src, (uint4*)dst, n8);
   } else {
     int64_t b = (n + threads - 1) / threads;
     const unsigned grid = (unsigned)(b < cap ? b : cap);
-    if (sd == M3AE_F32 && dd == M3AE_BF16) cast_kernel<float, bf16><<<grid, threads, 0, st>>>((const float*)src, (bf16*)dst, n);
-    else if (sd == M3AE_BF16 && dd == M3AE_F32) cast_kernel<bf16, float><<<grid, threads, 0, st>>>((const bf16*)src, (float*)dst, n);
-    else if (sd == M3AE_F32 && dd == M3AE_F32) cast_kernel<float, float><<<grid, threads, 0, st>>>((const float*)src, (float*)dst, n);
-    else cast_kernel<bf16, bf16><<<grid, threads, 0, st>>>((const bf16*)src, (bf16*)dst, n);
+    if (sd == M3AE_F32 && dd == M3AE_BF16) M3AE_LAUNCH((cast_kernel<float, bf16>), grid, threads, 0, st, (const float*)src, (bf16*)dst, n);
+    else if (sd == M3AE_BF16 && dd == M3AE_F32) M3AE_LAUNCH((cast_kernel<bf16, float>), grid, threads, 0, st, (const bf16*)src, (float*)dst, n);
+    else if (sd == M3AE_F32 && dd == M3AE_F32) M3AE_LAUNCH((cast_kernel<float, float>), grid, threads, 0, st, (const float*)src, (float*)dst, n);
+    else M3AE_LAUNCH((cast_kernel<bf16, bf16>), grid, threads, 0, st, (const bf16*)src, (bf16*)dst, n);
   }
   count_launch();
   M3AE_CUDA(cudaGetLastError());
@@ -566,7 +575,7 @@ int cast_group(const m3ae_cast_item_t* items, int n, cudaStream_t st) {
   const int64_t cap = (int64_t)sm_count() * 2;
   if (b < 1) b = 1;
   dim3 grid((unsigned)(b < cap ? b : cap), (unsigned)n);
-  cast_group_kernel<<<grid, threads, 0, st>>>(G);
+  M3AE_LAUNCH((cast_group_kernel), grid, threads, 0, st, G);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -578,10 +587,10 @@ int add_rowvec(const void* a, const float* b, void* out, int64_t M, int N, int i
   const int64_t cap = (int64_t)sm_count() * 8;
   int64_t blocks = (M * N + threads - 1) / threads;
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
-  if (in_dtype == M3AE_F32 && out_dtype == M3AE_F32) add_rowvec_kernel<float, float><<<grid, threads, 0, st>>>((const float*)a, b, (float*)out, M, N);
-  else if (in_dtype == M3AE_F32 && out_dtype == M3AE_BF16) add_rowvec_kernel<float, bf16><<<grid, threads, 0, st>>>((const float*)a, b, (bf16*)out, M, N);
-  else if (in_dtype == M3AE_BF16 && out_dtype == M3AE_BF16) add_rowvec_kernel<bf16, bf16><<<grid, threads, 0, st>>>((const bf16*)a, b, (bf16*)out, M, N);
-  else add_rowvec_kernel<bf16, float><<<grid, threads, 0, st>>>((const bf16*)a, b, (float*)out, M, N);
+  if (in_dtype == M3AE_F32 && out_dtype == M3AE_F32) M3AE_LAUNCH((add_rowvec_kernel<float, float>), grid, threads, 0, st, (const float*)a, b, (float*)out, M, N);
+  else if (in_dtype == M3AE_F32 && out_dtype == M3AE_BF16) M3AE_LAUNCH((add_rowvec_kernel<float, bf16>), grid, threads, 0, st, (const float*)a, b, (bf16*)out, M, N);
+  else if (in_dtype == M3AE_BF16 && out_dtype == M3AE_BF16) M3AE_LAUNCH((add_rowvec_kernel<bf16, bf16>), grid, threads, 0, st, (const bf16*)a, b, (bf16*)out, M, N);
+  else M3AE_LAUNCH((add_rowvec_kernel<bf16, float>), grid, threads, 0, st, (const bf16*)a, b, (float*)out, M, N);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -595,8 +604,8 @@ int dropout_apply(const void* x, void* y, int64_t M, int N, int64_t ld, float p,
   const int64_t cap = (int64_t)sm_count() * 8;
   int64_t blocks = (M * N + threads - 1) / threads;
   const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
-  if (dtype == M3AE_BF16) dropout_apply_kernel<bf16><<<grid, threads, 0, st>>>((const bf16*)x, (bf16*)y, M, N, ld, p, seed, stream_id);
-  else dropout_apply_kernel<float><<<grid, threads, 0, st>>>((const float*)x, (float*)y, M, N, ld, p, seed, stream_id);
+  if (dtype == M3AE_BF16) M3AE_LAUNCH((dropout_apply_kernel<bf16>), grid, threads, 0, st, (const bf16*)x, (bf16*)y, M, N, ld, p, seed, stream_id);
+  else M3AE_LAUNCH((dropout_apply_kernel<float>), grid, threads, 0, st, (const float*)x, (float*)y, M, N, ld, p, seed, stream_id);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;

@@ -374,6 +374,11 @@ def argmax_partials(vals, idx, out=None):
     return out
 
 
+def set_pdl(on):
+    """Programmatic dependent launch of the library's kernels on / off (default on)."""
+    L.check(L.load().m3ae_set_pdl(1 if on else 0), "m3ae_set_pdl")
+
+
 def set_gemm_skinny(mode):
     """Test hook for single-CTA GEMM launches (every problem M <= 128): 0 auto, 1 always 128x256 tiles, 2 always 128x64 tiles."""
     L.check(L.load().m3ae_set_gemm_skinny(int(mode)), "m3ae_set_gemm_skinny")
