@@ -36,7 +36,10 @@ import torch  # noqa: E402
 
 # The ONE JSON line goes to the real stdout; everything else a run prints (the reference's own modules print while they are
 # constructed, m3ae_module.py:133) is sent to stderr so that the driver parses a clean line.
-_STDOUT = sys.stdout
+# (file-descriptor level: NCCL prints its version banner from C)
+sys.stdout.flush()
+_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
 sys.stdout = sys.stderr
 
 LT, LI, HID, NLAB = 32, 325, 768, 498  # 32 text tokens, 325 image tokens (288 px / 16 + CLS), hidden 768, 498 answers
@@ -338,9 +341,11 @@ def run_ours(args):
         for p in params:
             p.grad = None
         cat = {k: torch.cat([b[k] for b in allb]) for k in allb[0]}
+        reducer.enabled = False  # local whole-batch gradients: no exchange
         loss, _, _ = model.vqa_loss_from_feats(cat["text"], cat["image"], cat["masks"], cat["targets"])
         loss.backward()
         torch.cuda.synchronize()
+        reducer.enabled = True
         num = torch.sqrt(sum(((g - p.grad.float()) ** 2).sum() for g, p in zip(got, params)))
         den = torch.sqrt(sum((p.grad.float() ** 2).sum() for p in params))
         err = torch.tensor([(num / den).item()], device=dev)
