@@ -46,6 +46,8 @@ extern "C" {
 #define M3AE_GEMM_TCGEN05 1 /* TMA + tcgen05.mma + TMEM (bf16 inputs only) */
 #define M3AE_GEMM_SIMT 2    /* fp32 FFMA tiles (f32 or bf16 inputs): strict-parity + debugging path */
 #define M3AE_ATTN_MMA_SYNC 3 /* attention only: legacy mma.sync flash tiles instead of the tcgen05 kernels */
+#define M3AE_ATTN_NARROW 4   /* attention only: AUTO, but every shape with a side <= 32 tokens goes to the single-pass "narrow" kernels
+                                (AUTO itself sends the forward there only where it measured faster) */
 
 #define M3AE_OK 0
 #define M3AE_ERR_INVALID (-1)

@@ -15,6 +15,7 @@ ACT_NONE, ACT_GELU, ACT_RELU, ACT_QUICKGELU, ACT_TANH = 0, 1, 2, 3, 4
 MAJOR_K, MAJOR_MN = 0, 1
 GEMM_AUTO, GEMM_TCGEN05, GEMM_SIMT = 0, 1, 2
 ATTN_MMA_SYNC = 3
+ATTN_NARROW = 4
 
 
 class GemmEpilogue(C.Structure):

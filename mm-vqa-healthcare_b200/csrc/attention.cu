@@ -15,6 +15,15 @@ int attn_fwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);  // attention_mm
 int attn_bwd_mma(const m3ae_attn_params_t* p, cudaStream_t st);
 int attn_fwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st);   // attention_tc.cu (tcgen05/TMEM); M3AE_ERR_UNSUPPORTED if not covered / not profitable
 int attn_bwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st);
+int attn_fwd_narrow(const m3ae_attn_params_t* p, bool force, cudaStream_t st);  // attention_narrow.cu: one side <= 32 tokens (text), HBM-bound single-pass kernels
+int attn_bwd_narrow(const m3ae_attn_params_t* p, cudaStream_t st);
+// AUTO backend only; M3AE_ATTN_NARROW=0 in the environment sends these shapes to the tcgen05 / mma.sync tiles instead (A/B runs),
+// M3AE_ATTN_NARROW=2 makes the forward take every covered shape (tests), default 1 = where it measured faster
+static int narrow_mode() {
+  static const int mode = [] { const char* e = getenv("M3AE_ATTN_NARROW"); return e ? atoi(e) : 1; }();
+  return mode;
+}
+static bool narrow_on() { return narrow_mode() != 0; }
 
 namespace {
 
@@ -648,7 +657,8 @@ int attn_fwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, false);
   if (rc) return rc;
   if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
-    rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_fwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
+    rc = ((backend == M3AE_GEMM_AUTO && narrow_on()) || backend == M3AE_ATTN_NARROW) ? attn_fwd_narrow(p, narrow_mode() == 2 || backend == M3AE_ATTN_NARROW, st) : M3AE_ERR_UNSUPPORTED;
+    if (rc == M3AE_ERR_UNSUPPORTED) rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_fwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
     if (rc == M3AE_ERR_UNSUPPORTED) rc = attn_fwd_mma(p, st);
     if (rc == M3AE_OK && p->probs) {
       launch_probs<bf16>(p, st);
@@ -679,7 +689,8 @@ int attn_bwd(const m3ae_attn_params_t* p, int backend, cudaStream_t st) {
   int rc = validate(p, true);
   if (rc) return rc;
   if (backend != M3AE_GEMM_SIMT && p->dtype == M3AE_BF16) {
-    rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_bwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
+    rc = ((backend == M3AE_GEMM_AUTO && narrow_on()) || backend == M3AE_ATTN_NARROW) ? attn_bwd_narrow(p, st) : M3AE_ERR_UNSUPPORTED;
+    if (rc == M3AE_ERR_UNSUPPORTED) rc = backend == M3AE_ATTN_MMA_SYNC ? M3AE_ERR_UNSUPPORTED : attn_bwd_tc(p, backend == M3AE_GEMM_TCGEN05, st);
     if (rc == M3AE_ERR_UNSUPPORTED) rc = attn_bwd_mma(p, st);
     if (rc != M3AE_ERR_UNSUPPORTED) return rc;
   }

@@ -7,7 +7,7 @@ import ctypes as C
 import torch
 
 from . import _lib as L
-from ._lib import ACT_GELU, ACT_NONE, ACT_QUICKGELU, ACT_RELU, ACT_TANH, ATTN_MMA_SYNC, BF16, F32, GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, MAJOR_K, MAJOR_MN  # noqa: F401
+from ._lib import ACT_GELU, ACT_NONE, ACT_QUICKGELU, ACT_RELU, ACT_TANH, ATTN_MMA_SYNC, ATTN_NARROW, BF16, F32, GEMM_AUTO, GEMM_SIMT, GEMM_TCGEN05, MAJOR_K, MAJOR_MN  # noqa: F401
 
 
 def _code(dtype):

@@ -260,7 +260,7 @@ ATT_CASES = [  # (B, H, Lq, Lk, dh, masked, causal)
 ]
 
 
-@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO, ops.GEMM_TCGEN05, ops.ATTN_MMA_SYNC])
+@pytest.mark.parametrize("backend", [ops.GEMM_SIMT, ops.GEMM_AUTO, ops.GEMM_TCGEN05, ops.ATTN_MMA_SYNC, ops.ATTN_NARROW])
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 1e-2)])
 @pytest.mark.parametrize("case", ATT_CASES)
 def test_attention_fwd_bwd(backend, dtype, tol, case):
@@ -517,6 +517,63 @@ def test_layernorm_bwd_staging_ring_matches_register_path(M, drop):
         assert torch.equal(a, b)
     for a, b in zip(res[0][1:], res[1][1:]):
         assert rel_err(b, a) < 1e-5
+
+
+@pytest.mark.parametrize("cache", [False, True])
+@pytest.mark.parametrize("shape", [(32, 32), (32, 325), (325, 32), (20, 577), (577, 9), (7, 5)])
+def test_attention_narrow_kernels_with_dropout_and_masks(shape, cache):
+    """attention_narrow.cu (backend ATTN_NARROW = AUTO with every narrow shape forced, one side <= 32 tokens): forward + single-pass backward with a ragged key mask
+    and dropout 0.1 against autograd through the SAME keep mask (read back from the probabilities the library reports),
+    with and without the keep-bit cache; and against the mma.sync tiles on the same seed (identical Philox bits)."""
+    Lq, Lk = shape
+    B, H, dh, p = 3, 12, 64, 0.1
+    q, k, v = (rnd(B * L, H * dh, dtype=torch.bfloat16, seed=i) for i, L in ((0, Lq), (1, Lk), (2, Lk)))
+    lens = torch.randint(max(1, Lk // 4), Lk + 1, (B,), generator=torch.Generator().manual_seed(5))
+    mask = ((torch.arange(Lk)[None, :] >= lens[:, None]).float() * -10000.0).to(DEV).contiguous()
+    kw = dict(B=B, H=H, Lq=Lq, Lk=Lk, dh=dh, mask=mask, drop_p=p, drop_seed=4242, drop_stream=2)
+    res = {}
+    for backend in (ops.ATTN_NARROW, ops.ATTN_MMA_SYNC):
+        ops.set_attention_backend(backend)
+        try:
+            kw2 = dict(kw)
+            if cache:
+                kw2["drop_mask"] = torch.zeros(B * H * Lq * ops.drop_mask_ld(Lk), dtype=torch.uint8, device=DEV)
+            out = torch.empty(B * Lq, H * dh, dtype=torch.bfloat16, device=DEV)
+            lse = torch.empty(B, H, Lq, device=DEV)
+            probs = torch.empty(B, H, Lq, Lk, device=DEV)
+            ops.attn_fwd(q, k, v, out, lse, probs=probs, **kw2)
+            dout = rnd(B * Lq, H * dh, dtype=torch.bfloat16, seed=9)
+            dq, dk, dv = (torch.full_like(t, float("nan")) for t in (q, k, v))
+            delta = torch.empty(B, H, Lq, device=DEV)
+            ops.attn_bwd(q, k, v, out, lse, dout=dout, dq=dq, dk=dk, dv=dv, delta=delta, **kw2)
+            res[backend] = (out, lse, probs, dq, dk, dv, kw2.get("drop_mask"))
+        finally:
+            ops.set_attention_backend(ops.GEMM_AUTO)
+    out, lse, probs, dq, dk, dv, bits = res[ops.ATTN_NARROW]
+    keep = probs != 0
+    valid = (mask == 0).view(B, 1, 1, Lk).expand_as(probs)
+    if Lq * Lk >= 1024:
+        assert abs(keep[valid].float().mean().item() - (1 - p)) < 1e-2
+    qr, kr, vr = (t.float().detach().clone().requires_grad_(True) for t in (q, k, v))
+    _, p2 = _attn_ref(qr, kr, vr, mask, B, H, Lq, Lk, dh, False)
+    o2 = ((p2 * keep / (1 - p)) @ vr.view(B, Lk, H, dh).transpose(1, 2)).transpose(1, 2).reshape(B * Lq, H * dh)
+    assert rel_err(out, o2) < 1e-2, f"narrow fwd {shape}: {rel_err(out, o2):.3e}"
+    lse_ref = torch.logsumexp(qr.view(B, Lq, H, dh).transpose(1, 2) @ kr.view(B, Lk, H, dh).transpose(1, 2).transpose(-1, -2) / 8.0
+                              + mask.view(B, 1, 1, Lk), dim=-1)
+    assert rel_err(lse, lse_ref) < 1e-3
+    o2.backward(dout.float())
+    for name, got, ref in (("dq", dq, qr.grad), ("dk", dk, kr.grad), ("dv", dv, vr.grad)):
+        assert torch.isfinite(got.float()).all(), name
+        assert rel_err(got, ref) < 2e-2, f"narrow bwd {name} {shape}: {rel_err(got, ref):.3e}"
+    # same Philox bits as the mma.sync tiles: identical keep pattern, same cache bytes, outputs within bf16 rounding
+    o_m, lse_m, probs_m, dq_m, dk_m, dv_m, bits_m = res[ops.ATTN_MMA_SYNC]
+    assert torch.equal(probs_m != 0, keep)
+    if cache:
+        units = (Lk + 7) // 8
+        ld = ops.drop_mask_ld(Lk)
+        assert torch.equal(bits.view(-1, ld)[:, :units], bits_m.view(-1, ld)[:, :units])
+    for a, b_ in ((out, o_m), (dq, dq_m), (dk, dk_m), (dv, dv_m)):
+        assert rel_err(a, b_) < 1.5e-2
 
 
 @pytest.mark.parametrize("shape", [(325, 325), (32, 325), (325, 32), (32, 32), (70, 325)])

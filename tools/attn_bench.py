@@ -32,9 +32,22 @@ def run(Lq, Lk, drop=0.0):
         for _ in range(2): fn()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(reps): fn()
-        e1.record(); torch.cuda.synchronize()
+        if os.environ.get("GRAPH", "1") == "1":
+            # a ctypes call costs ~15 us of host time, more than the small kernels run: replay `reps` launches from a CUDA graph
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                fn()
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=side):
+                    for _ in range(reps): fn()
+            torch.cuda.current_stream().wait_stream(side)
+            gr.replay(); torch.cuda.synchronize()
+            e0.record(); gr.replay(); e1.record(); torch.cuda.synchronize()
+        else:
+            e0.record()
+            for _ in range(reps): fn()
+            e1.record(); torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / reps
         flops = mult * B * H * Lq * Lk * dh
         print(f"attn {name} Lq={Lq:4d} Lk={Lk:4d} drop={drop}: {us:8.1f} us  {flops / us / 1e6:7.1f} TFLOP/s (algorithmic {mult}*B*H*Lq*Lk*dh)")
