@@ -20,6 +20,7 @@ At N = 1 the same JSON line also carries:
                            the reference Decoder.search_path at batch 16)
   "whole_step"             config 2 with the uni-modal encoders included (CLIP ViT-B/16 + RoBERTa-base on the same kernels)
   "classifier_forward_b8"  config 1: infer + vqa_head at batch 8, next to the reference's CPU fp32 time
+  "t5_head"                config 4: T5 generative head, teacher-forced fine-tune step at batch 64 (frozen M3AE on the kernels, HF T5-small)
 """
 import argparse
 import json
@@ -505,6 +506,8 @@ def run_ours(args):
         torch.cuda.empty_cache()
         line["classifier_forward_b8"] = bench_config1(args, dev)
         torch.cuda.empty_cache()
+        line["t5_head"] = bench_t5_head(args, dev)
+        torch.cuda.empty_cache()
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(sample_b=8, steps=3)
@@ -621,6 +624,96 @@ def bench_config1(args, dev):
     del model
     if not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_config1_baseline()
+    return out
+
+
+T5_ANSWERS = ["no", "yes", "left lower lobe pneumonia", "right upper lobe", "abdomen", "chest x ray", "the liver", "pleural effusion"]
+
+
+def _t5_config():
+    """finetune_m3ae.sh:9-16: t5_max_length 12, cls feature only, top 4 encoder / decoder blocks unfrozen."""
+    return {"drop_rate": 0.1, "hidden_size": 768, "load_path_t5": "", "t5_max_length": 12, "mm_encoder_inputs_include_cls_feats": True,
+            "mm_encoder_inputs_include_imagetext_feats": False, "mm_encoder_inputs_mm_feats_width": 0,
+            "loss_names": {"mlm": 0, "mim": 0, "itm": 0, "vqa": 1, "cls": 0, "irtr": 0}}
+
+
+def _t5_batch(O, seed, B, device):
+    batch = O.make_model_batch(seed, B, device=device)
+    batch["text"] = ["what abnormality is seen in this image"] * B
+    batch["vqa_answer"] = [[T5_ANSWERS[i % len(T5_ANSWERS)]] for i in range(B)]
+    return batch
+
+
+def cpu_t5_baseline(B=4, threads=None):
+    """The reference's own T5VQA_MMEncoderInput (m3ae_t5_mm_encoder_input.py:191-295, oracle/_ref) with a random-init t5-small,
+    one teacher-forced fine-tune step on the host cores: forward (frozen M3AE + T5) + backward + AdamW.  Its per-step beam-4
+    generation for metrics (:250-259) is NOT part of "teacher-forced" and is switched off through max_length 1."""
+    if not _ref_available():
+        return None
+    from oracle import m3ae_oracle as O
+    from oracle import ref_shim
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    Cls = ref_shim.load_t5_head(O.SynthT5Tokenizer())
+    cfg = ref_shim.m3ae_config(drop_rate=0.1)
+    cfg.update(_t5_config())
+    torch.manual_seed(0)
+    model = Cls(cfg).train()
+    ref_shim.wrap_text_layers(model.m3ae)
+    model.unfreeze_top_layers(4, 4)
+    model.current_tasks = ["vqa"]
+    model.max_answer_length = 2  # shortest generation the reference's forward allows: the metrics-only beam search is not timed work
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(params, lr=1e-5, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01)
+    batch = _t5_batch(O, 90, B, "cpu")
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        model(batch)["vqa_loss"].backward()
+        opt.step()
+
+    step()
+    t = time.perf_counter()
+    step()
+    dt = time.perf_counter() - t
+    return {"value": round(B / dt, 3), "unit": "samples/s", "cores": threads, "kind": "reference", "ms": round(dt * 1e3, 1),
+            "sample": f"batch {B} (of 64), one step after 1 warm-up, fp32, dropout 0.1; the reference's own T5VQA_MMEncoderInput.forward (train branch, "
+                      "generation for metrics cut to 2 tokens) + backward + AdamW over the unfrozen top-4 T5 blocks, random-init t5-small"}
+
+
+def bench_t5_head(args, dev):
+    """BASELINE config 4: T5 generative head, teacher-forced fine-tune step, bf16, batch 64: frozen M3AE.infer on the sm_100a kernels
+    (dropout active: the frozen M3AE stays in train mode, as in the reference) -> prepare_inputs -> HF T5-small encoder (512 positions)
+    -> teacher-forced decoder loss -> backward through the unfrozen top-4 encoder / decoder blocks -> AdamW.  Reported as samples/s
+    only: the T5 arithmetic is third-party library code on both sides."""
+    from m3ae_b200.t5_head import T5VQA_MMEncoderInput
+    from oracle import m3ae_oracle as O  # synthetic batch-dict generator only
+    B = args.batch
+    torch.manual_seed(0)
+    model = T5VQA_MMEncoderInput(_t5_config(), compute_dtype=torch.bfloat16, generate_for_metrics=False).to(dev).train()
+    model.unfreeze_top_layers(4, 4)
+    model.current_tasks = ["vqa"]
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(params, lr=1e-5, betas=(0.9, 0.98), eps=1e-8, weight_decay=0.01, fused=True)
+    batches = [_t5_batch(O, 90 + i, B, dev) for i in range(2)]
+
+    def step(i):
+        opt.zero_grad(set_to_none=True)
+        model(batches[i % 2])["vqa_loss"].backward()
+        opt.step()
+
+    for i in range(3):
+        step(i)
+    steps = max(3, min(args.steps, 10))
+    ms = _event_time(step, steps, torch.cuda.synchronize) / steps
+    out = {"metric": "fine-tune samples/sec (M3AE T5 generative head, teacher-forced)", "value": round(B / (ms * 1e-3), 1), "unit": "samples/s",
+           "ms_per_step": round(ms, 3), "steps": steps, "dtype": "bf16",
+           "config": {"workload": "T5VQA_MMEncoderInput teacher-forced fine-tune step (main_t5_m3ae), batch 64, 288 px / 32 tokens, cls feature as encoder input "
+                                  "(512 positions), top-4 T5 blocks trainable, AdamW(fused); frozen M3AE forward on the sm_100a kernels, T5-small = HF library code under bf16 autocast",
+                      "trainable_params": int(sum(p.numel() for p in params))}}
+    del model, opt, batches
+    if not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_t5_baseline()
     return out
 
 

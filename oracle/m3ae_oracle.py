@@ -423,6 +423,45 @@ class SynthTokenizer:
         return " ".join(self._words.get(i, f"[{i}]") for i in ids if not (skip_special_tokens and i in special))
 
 
+class SynthT5Tokenizer:
+    """Stand-in for HF T5Tokenizer('t5-small') (m3ae_t5_mm_encoder_input.py:26; no sentencepiece model offline): whitespace
+    split, hashed ids in [3, 32000), T5's special ids (pad 0, eos 1).  Same surface the reference uses (:113-117, :232-237,
+    :262-265): `__call__(str | list[str], return_tensors, add_special_tokens, padding, truncation).input_ids`, `batch_decode`."""
+
+    pad_token_id, eos_token_id, unk_token_id = 0, 1, 2
+
+    def __init__(self, vocab_size=32128):
+        self.vocab_size = vocab_size
+        self._words = {}
+
+    def _id(self, w):
+        h = 3 + (sum((i + 1) * ord(c) * 2654435761 for i, c in enumerate(w)) % 31997)
+        self._words.setdefault(h, w)
+        return h
+
+    def __call__(self, texts, return_tensors="pt", add_special_tokens=True, padding=False, truncation=False, max_length=512):
+        if isinstance(texts, str):
+            texts = [texts]
+        rows = []
+        for t in texts:
+            ids = [self._id(w) for w in t.lower().split()]
+            if add_special_tokens:
+                ids = ids[:max_length - 1] + [self.eos_token_id]
+            rows.append(ids)
+        width = max(len(r) for r in rows)
+        out = torch.full((len(rows), width), self.pad_token_id, dtype=torch.long)
+        for i, r in enumerate(rows):
+            out[i, :len(r)] = torch.tensor(r, dtype=torch.long)
+        return type("Enc", (), {"input_ids": out})()
+
+    def batch_decode(self, seqs, skip_special_tokens=True, **kw):
+        outs = []
+        for seq in seqs:
+            ids = seq.tolist() if torch.is_tensor(seq) else list(seq)
+            outs.append(" ".join(self._words.get(i, f"<{i}>") for i in ids if not (skip_special_tokens and i in (0, 1, 2))))
+        return outs
+
+
 def make_fusion_inputs(seed, B, Lt=32, Li=325, num_labels=498, all_valid=False):
     """Seeded synthetic hot-path inputs: uni-modal features of the shapes RoBERTa / CLIP ViT-B/16
     produce at 288 px / 32 tokens, ragged text masks (valid length uniform in [8,32]), one-hot VQA targets."""

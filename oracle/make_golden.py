@@ -186,6 +186,56 @@ def gen_decoder_model():
     print("decoder_model.pt loss", float(loss), "grads", len(grads), "greedy", ids[0, :8].tolist(), "texts", test_ret["vqa_logits"])
 
 
+T5_HEAD_ANSWERS = [["left lower lobe pneumonia"], ["no"]]
+T5_HEAD_QUESTIONS = ["is there a pleural effusion", "what organ is shown in this image"]
+
+
+def t5_head_config(imagetext=False):
+    """finetune_m3ae.sh:9-16 (cls feature only) or its commented variant :29-36 (image/text features, width 10)."""
+    cfg = ref_shim.m3ae_config()
+    cfg.update({"load_path_t5": "", "t5_max_length": 12, "mm_encoder_inputs_include_cls_feats": not imagetext,
+                "mm_encoder_inputs_include_imagetext_feats": imagetext, "mm_encoder_inputs_mm_feats_width": 10 if imagetext else 0,
+                "learning_rate": 1e-5, "weight_decay": 0.01, "end_lr": 0, "decay_power": 1, "optim_type": "adamw", "warmup_steps": 0.1})
+    return cfg
+
+
+def gen_t5_head():
+    """The reference's T5VQA_MMEncoderInput (m3ae_t5_mm_encoder_input.py:100-295), eval mode (dropout off), B=2, both input
+    variants: prepare_inputs (its per-call random nn.Linear layers draw from the CPU RNG: torch.manual_seed(77) right before),
+    T5 encoder, teacher-forced loss, gradients of the unfrozen top-2 encoder / decoder blocks, beam-4 generation."""
+    tok = O.SynthT5Tokenizer()
+    Cls = ref_shim.load_t5_head(tok)
+    out = {}
+    for variant in ("cls", "imagetext"):
+        torch.manual_seed(0)
+        model = Cls(t5_head_config(variant == "imagetext")).eval()
+        O.seed_model_parameters(model, 13)
+        ref_shim.wrap_text_layers(model.m3ae)
+        model.unfreeze_top_layers(2, 2)
+        batch = O.make_model_batch(71, 2)
+        batch["vqa_answer"] = T5_HEAD_ANSWERS
+        batch["text"] = T5_HEAD_QUESTIONS
+        model.current_tasks = ["vqa"]
+        cfg = model.hparams.m3ae_config
+        torch.manual_seed(77)
+        with torch.no_grad():
+            inp = model.prepare_inputs(batch, cfg["mm_encoder_inputs_include_cls_feats"], cfg["mm_encoder_inputs_include_imagetext_feats"],
+                                       cfg["mm_encoder_inputs_mm_feats_width"])
+            enc = model.t5.encoder(inputs_embeds=inp["inputs_embeds"], attention_mask=inp["attention_mask"]).last_hidden_state
+        torch.manual_seed(77)
+        ret = model(batch)
+        loss = ret["vqa_loss"]
+        loss.backward()
+        grads = {n: {"norm": p.grad.norm(), "samples": p.grad.flatten()[:: max(1, p.numel() // 64)][:64].clone()}
+                 for n, p in model.named_parameters() if p.grad is not None}
+        nz = int((inp["inputs_embeds"].abs().sum(-1) > 0).sum(1).max())
+        out[variant] = {"loss": loss.detach(), "inputs_embeds_head": inp["inputs_embeds"][:, :nz + 1].clone(), "nonzero_rows": nz,
+                        "attention_mask_sum": inp["attention_mask"].sum(1), "encoder_sub": enc[:, ::32].clone(), "grads": grads,
+                        "texts": ret["vqa_logits"], "ret_keys": sorted(ret.keys())}
+        print("t5_head", variant, "loss", float(loss), "nonzero rows", nz, "grads", len(grads), "texts", ret["vqa_logits"])
+    torch.save(out, os.path.join(OUT, "t5_head.pt"))
+
+
 class Tok:
     cls_token_id, sep_token_id, eos_token_id, pad_token_id = 101, 102, None, 0
 
@@ -224,11 +274,15 @@ def gen_decoder(ref):
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "t5_head":  # one fixture only
+        gen_t5_head()
+        sys.exit(0)
     ref = ref_shim.load()
     gen_cross_layer(ref)
     gen_decoder(ref)
     gen_fusion()
     gen_full_model()
     gen_decoder_model()
+    gen_t5_head()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")

@@ -248,3 +248,26 @@ def load_decoder_model(tokenizer):
     dec = importlib.import_module("m3ae.modules.m3ae_decoder")
     dec.BertTokenizer = types.SimpleNamespace(from_pretrained=lambda *a, **k: tokenizer)
     return dec.DecoderModel
+
+
+def random_t5():
+    """t5-small's architecture (T5Config() defaults = t5-small) with random weights: the checkpoint does not exist offline."""
+    from transformers import T5Config, T5ForConditionalGeneration
+    return T5ForConditionalGeneration(T5Config(decoder_start_token_id=0))
+
+
+def load_t5_head(tokenizer):
+    """Imports the reference's T5VQA_MMEncoderInput (m3ae_t5_mm_encoder_input.py:12-295) unmodified, wired to the real
+    M3AETransformerSS class (random-init real encoders), to `tokenizer` in place of T5Tokenizer.from_pretrained('t5-small') (:26)
+    and to a random-init t5-small in place of T5ForConditionalGeneration.from_pretrained('t5-small') (:27).  Returns the class."""
+    mm3, Cls = load_m3ae_module(real_encoders=True)
+    mods = sys.modules["m3ae.modules"]
+    mods.M3AETransformerSS = Cls
+    for sub in ("m3ae_t5_utils", "objectives"):
+        m = sys.modules.get(f"m3ae.modules.{sub}") or importlib.import_module(f"m3ae.modules.{sub}")
+        setattr(mods, sub, m)
+    sys.modules.pop("m3ae.modules.m3ae_t5_mm_encoder_input", None)
+    t5m = importlib.import_module("m3ae.modules.m3ae_t5_mm_encoder_input")
+    t5m.T5Tokenizer = types.SimpleNamespace(from_pretrained=lambda *a, **k: tokenizer)
+    t5m.T5ForConditionalGeneration = types.SimpleNamespace(from_pretrained=lambda *a, **k: random_t5())
+    return t5m.T5VQA_MMEncoderInput
