@@ -267,6 +267,45 @@ int m3ae_argmax_rows(const void* logits, int64_t ld, int64_t* out_ids, int64_t M
 int m3ae_decoder_embed(const int64_t* ids, const int32_t* pos, const float* table, const float* pe, void* out, int64_t M,
                        int32_t D, int32_t out_dtype, void* stream);
 
+/* Token hand-over of the greedy decoder in one launch (bf16 activations, D = 768): ids_out[r] = row argmax from the vocabulary
+ * projection's partials (as m3ae_argmax_partials; amax_val == NULL: ids are read from ids_in instead), x[r,:] = 2*E[id] + pe[pos]
+ * (m3ae_decoder.py:125-127) and, when xn != NULL, xn[r,:] = LayerNorm(x[r,:]) (pre_norm, m3ae_decoder.py:58) — bit-identical to
+ * m3ae_argmax_partials + m3ae_decoder_embed + m3ae_layernorm_fwd. */
+int m3ae_decoder_next_token(const float* amax_val, const int32_t* amax_idx, int32_t n_groups, int32_t M, const int64_t* ids_in, int64_t* ids_out,
+                            int32_t pos, const float* table, const float* pe, const float* ln_gamma, const float* ln_beta, float ln_eps, void* x,
+                            void* xn, int32_t D, void* stream);
+
+/* Skinny linear layer of the single-token decoder step (M <= 128 rows = batch; bf16 operands, fp32 accumulate):
+ *   out = act( LN?(x)[M,K] . w[N,K]^T + bias ) (+ residual)
+ * Replaces, for ONE new token per sequence, the projections of m3ae_decoder.py:54-90 — MHA in-proj / out-proj
+ * (nn.MultiheadAttention at :42-43), the FFN (:45, :85-87) — and, when ln_gamma != NULL, the LayerNorm in front of them
+ * (pre_norm :58, layernorm1 :66, layernorm2 :83; K must be 768) folded into the activation load.
+ * The whole activation panel and the CTA's weight slice are staged in shared memory by one burst of cp.async; every CTA takes
+ * 16 or 32 output columns.  Segmented output: column n goes to out[n / seg_cols] + row * ldo[n / seg_cols] + n % seg_cols
+ * (the QKV projection writes q and the K / V cache rows in one launch).  ksplit > 1 splits K across CTAs (K / ksplit <= 768
+ * per CTA): `ws` ([128, N] fp32) and `counters` ([ceil(N/16)] int32) must be ZERO on entry and are left zero. */
+typedef struct m3ae_skinny_params_t {
+  const void* x;        /* [M, K] bf16 */
+  int64_t ldx;
+  const void* w;        /* [N, K] bf16 (nn.Linear layout) */
+  int64_t ldw;
+  const float* bias;    /* [N] fp32 or NULL */
+  const void* residual; /* [M, N] bf16 or NULL */
+  int64_t ldr;
+  void* out[3];         /* bf16 */
+  int64_t ldo[3];
+  int32_t seg_cols;     /* columns per output segment (multiple of 32); = N for a single output */
+  int32_t M, N, K;
+  int32_t ksplit;       /* 0 / 1: no split */
+  int32_t act;          /* M3AE_ACT_NONE or M3AE_ACT_RELU */
+  const float* ln_gamma; /* optional LayerNorm over K in front of the projection */
+  const float* ln_beta;
+  float ln_eps;
+  float* ws;
+  int32_t* counters;
+} m3ae_skinny_params_t;
+int m3ae_skinny_linear(const m3ae_skinny_params_t* p, void* stream);
+
 /* Row argmax from the per-64-column partials of m3ae_gemm (epi.amax_val / amax_idx): ids[row] (int64) = column of the first
  * maximum over groups [0, n_groups).  Replaces argmax(log_softmax(final_linear(x))) of m3ae_decoder.py:151-153. */
 int m3ae_argmax_partials(const float* amax_val, const int32_t* amax_idx, int32_t n_groups, int32_t M, int64_t* ids, void* stream);

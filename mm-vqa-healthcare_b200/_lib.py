@@ -72,6 +72,14 @@ class DropBitsItem(C.Structure):
 MAX_DROPBITS = 12
 
 
+class SkinnyParams(C.Structure):
+    _fields_ = [("x", C.c_void_p), ("ldx", C.c_int64), ("w", C.c_void_p), ("ldw", C.c_int64), ("bias", C.c_void_p),
+                ("residual", C.c_void_p), ("ldr", C.c_int64), ("out", C.c_void_p * 3), ("ldo", C.c_int64 * 3),
+                ("seg_cols", C.c_int32), ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32), ("ksplit", C.c_int32),
+                ("act", C.c_int32), ("ln_gamma", C.c_void_p), ("ln_beta", C.c_void_p), ("ln_eps", C.c_float),
+                ("ws", C.c_void_p), ("counters", C.c_void_p)]
+
+
 # name -> (restype, argtypes); must list every symbol include/m3ae_b200.h declares (tests check this).
 SIGNATURES = {
     "m3ae_version": (C.c_int, []),
@@ -110,6 +118,9 @@ SIGNATURES = {
     "m3ae_set_gemm_epilogue": (C.c_int, [C.c_int32]),
     "m3ae_argmax_partials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "m3ae_set_gemm_skinny": (C.c_int, [C.c_int32]),
+    "m3ae_skinny_linear": (C.c_int, [C.POINTER(SkinnyParams), C.c_void_p]),
+    "m3ae_decoder_next_token": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "m3ae_set_pdl": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_cta_pair": (C.c_int, [C.c_int32]),
     "m3ae_set_layernorm_bwd_staging": (C.c_int, [C.c_int32]),

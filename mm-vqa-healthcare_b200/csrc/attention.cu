@@ -759,6 +759,95 @@ int argmax_partials(const float* val, const int32_t* idx, int G, int M, int64_t*
   return M3AE_OK;
 }
 
+// Token hand-over of the greedy decoder in ONE launch (one warp per sequence): row argmax from the vocabulary projection's
+// per-group partials (as argmax_partials_kernel; skipped when val == NULL: ids are read instead) -> ids_out, then
+// x = 2 E[id] + pe[pos] (decoder_embed_kernel) and xn = pre_norm(x) (ln_fwd_kernel's arithmetic, summation order and bf16
+// rounding points, so the fused path is bit-identical to the three launches it replaces).  D = 768, bf16 activations.
+__global__ void __launch_bounds__(32) decoder_next_token_kernel(const float* __restrict__ val, const int32_t* __restrict__ idx, int G, int M,
+                                                                const int64_t* __restrict__ ids_in, int64_t* __restrict__ ids_out, int pos,
+                                                                const float* __restrict__ table, const float* __restrict__ pe,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                                                bf16* __restrict__ x, bf16* __restrict__ xn) {
+  pdl_sync();
+  constexpr int D = 768;
+  const int row = blockIdx.x, lane = threadIdx.x;
+  int64_t id;
+  if (val != nullptr) {
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int g = lane; g < G; g += 32) {
+      const float v = val[(size_t)g * M + row];
+      const int i = idx[(size_t)g * M + row];
+      if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    id = bi;
+    if (lane == 0) ids_out[row] = id;
+  } else {
+    id = ids_in[row];
+  }
+  const float* e = table + (size_t)id * D;
+  const float* p = pe + (size_t)pos * D;
+  float v[3][8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int c = (i * 32 + lane) * 8;
+    const float4 e0 = *reinterpret_cast<const float4*>(e + c), e1 = *reinterpret_cast<const float4*>(e + c + 4);
+    const float4 p0 = *reinterpret_cast<const float4*>(p + c), p1 = *reinterpret_cast<const float4*>(p + c + 4);
+    const float ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w}, pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) w[j] = pack_bf16x2(ev[2 * j] + (ev[2 * j] + pv[2 * j]), ev[2 * j + 1] + (ev[2 * j + 1] + pv[2 * j + 1]));
+    *reinterpret_cast<uint4*>(x + (size_t)row * D + c) = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {  // LayerNorm sees the bf16-rounded x, as the separate launch does
+      const float2 f = unpack_bf16x2(w[j]);
+      v[i][2 * j] = f.x; v[i][2 * j + 1] = f.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += v[i][j];
+  }
+  if (xn == nullptr) return;
+  const float mean = warp_sum(s) / (float)D;
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; ss += d * d; }
+  const float var = warp_sum(ss) / (float)D;
+  const float rstd = rsqrtf(var + eps);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int c = (i * 32 + lane) * 8;
+    const float4 g0 = *reinterpret_cast<const float4*>(gamma + c), g1 = *reinterpret_cast<const float4*>(gamma + c + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(beta + c), b1 = *reinterpret_cast<const float4*>(beta + c + 4);
+    const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w}, bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * gv[j] + bv[j];
+    *reinterpret_cast<uint4*>(xn + (size_t)row * D + c) =
+        make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+  }
+}
+int decoder_next_token(const float* val, const int32_t* idx, int G, int M, const int64_t* ids_in, int64_t* ids_out, int pos, const float* table,
+                       const float* pe, const float* gamma, const float* beta, float eps, void* x, void* xn, int D, cudaStream_t st) {
+  M3AE_CHECK(D == 768, M3AE_ERR_UNSUPPORTED, "decoder_next_token: D = %d (768 only)", D);
+  M3AE_CHECK(M > 0 && table && pe && x && (val ? (idx && ids_out && G > 0) : ids_in != nullptr), M3AE_ERR_INVALID, "decoder_next_token: null pointer");
+  M3AE_CHECK(xn == nullptr || (gamma && beta), M3AE_ERR_INVALID, "decoder_next_token: LayerNorm output without gamma / beta");
+  M3AE_CHECK((((uintptr_t)table | (uintptr_t)pe | (uintptr_t)x | (uintptr_t)xn | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0, M3AE_ERR_UNSUPPORTED,
+             "decoder_next_token: 16-byte aligned pointers required");
+  M3AE_LAUNCH((decoder_next_token_kernel), (unsigned)M, 32, 0, st, val, idx, G, M, ids_in, ids_out, pos, table, pe, gamma, beta, eps, (bf16*)x, (bf16*)xn);
+  count_launch();
+  M3AE_CUDA(cudaGetLastError());
+  return M3AE_OK;
+}
+
 int argmax_rows(const void* x, int64_t ld, int64_t* out, int64_t M, int N, int dtype, cudaStream_t st) {
   M3AE_CHECK(M > 0 && N > 0, M3AE_ERR_INVALID, "argmax_rows: empty input");
   if (dtype == M3AE_BF16) M3AE_LAUNCH((argmax_rows_kernel<bf16>), (unsigned)M, 256, 0, st, (const bf16*)x, ld, out, N);

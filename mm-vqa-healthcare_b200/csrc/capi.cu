@@ -93,6 +93,9 @@ bool pdl_on() {
   return g_pdl_mode == 1;
 }
 int argmax_partials(const float*, const int32_t*, int, int, int64_t*, cudaStream_t);
+int skinny_linear(const m3ae_skinny_params_t*, cudaStream_t);  // skinny_linear.cu
+int decoder_next_token(const float*, const int32_t*, int, int, const int64_t*, int64_t*, int, const float*, const float*, const float*, const float*,
+                       float, void*, void*, int, cudaStream_t);
 extern bool ln_bwd_force_registers;
 static int g_attn_backend = M3AE_GEMM_AUTO;
 
@@ -232,6 +235,16 @@ int m3ae_argmax_partials(const float* amax_val, const int32_t* amax_idx, int32_t
   ARCH_GATE();
   M3AE_CHECK(amax_val && amax_idx && ids && n_groups > 0 && M > 0, M3AE_ERR_INVALID, "argmax_partials: null pointer or empty input");
   return argmax_partials(amax_val, amax_idx, n_groups, M, ids, (cudaStream_t)stream);
+}
+int m3ae_decoder_next_token(const float* amax_val, const int32_t* amax_idx, int32_t n_groups, int32_t M, const int64_t* ids_in, int64_t* ids_out,
+                            int32_t pos, const float* table, const float* pe, const float* ln_gamma, const float* ln_beta, float ln_eps, void* x,
+                            void* xn, int32_t D, void* stream) {
+  ARCH_GATE();
+  return decoder_next_token(amax_val, amax_idx, n_groups, M, ids_in, ids_out, pos, table, pe, ln_gamma, ln_beta, ln_eps, x, xn, D, (cudaStream_t)stream);
+}
+int m3ae_skinny_linear(const m3ae_skinny_params_t* p, void* stream) {
+  ARCH_GATE();
+  return skinny_linear(p, (cudaStream_t)stream);
 }
 int m3ae_set_pdl(int32_t on) {
   g_pdl_mode = on ? 1 : 0;

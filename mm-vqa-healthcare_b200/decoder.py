@@ -270,6 +270,14 @@ class Decoder(nn.Module):
         self.graph_replayed_launches += n_kernels  # ops.launch_count() only sees capture-time calls
         return out.clone()
 
+    @staticmethod
+    def _all_finished(nxt, sep, eos):
+        """The reference's break condition (m3ae_decoder.py:157-160): every row has produced [SEP] (or eos).  One host sync."""
+        done = nxt == sep
+        if eos is not None:
+            done = done | (nxt == eos)
+        return bool(done.any(dim=0).all())
+
     def _greedy_program(self, cross_attn_feats, tokenizer, early_exit_every=0, operands=None):
         """The greedy decoding program itself (see search_path); max_len single-token steps.  Since the reference blanks
         everything after the first [SEP] and only breaks once ALL rows are finished, running the remaining steps cannot
@@ -314,7 +322,59 @@ class Decoder(nn.Module):
         pe = self.positional_encoding.pe[0].contiguous()
         table = self.target_embedding.weight.detach()
         pos_all = torch.arange(L, dtype=torch.int32, device=dev).repeat_interleave(B).view(L, B)
+        # bf16, batch <= 128: the six per-token projections run on the skinny kernel (whole activation panel + weight slice in
+        # shared memory, LayerNorm folded into the load, K/V written straight into the cache rows): csrc/skinny_linear.cu
+        import os
+        skinny = dt == torch.bfloat16 and B <= 128 and os.environ.get("M3AE_DECODER_SKINNY", "1") != "0"
+        if skinny:
+            f32 = torch.float32
+            fp = lambda v: v.detach().to(f32).contiguous()  # noqa: E731
+            ws = torch.zeros(128 * D, dtype=f32, device=dev)
+            ctr = torch.zeros(64, dtype=torch.int32, device=dev)
+            # LayerNorm folded into the projection's activation load only for small batches: every CTA normalises all B rows
+            # redundantly (measured at B = 128: +7 us per launch against 4.3 us for the separate LayerNorm launch)
+            fuse_ln = B <= 32
+            norms = [(layer.pre_norm, x, xn), (layer.layernorm1, x1, x1n), (layer.layernorm2, x3, x3n)]
+            ln_arg = [(fp(n.weight), fp(n.bias), n.eps) if fuse_ln else None for n, _, _ in norms]
+            src = [raw if fuse_ln else normed for _, raw, normed in norms]
+            S_qkv = ops.SkinnyLinear(src[0], w_in1, [q, k_self[:, 0, :], v_self[:, 0, :]], bias=fp(b_in1), ln=ln_arg[0])
+            S_o1 = ops.SkinnyLinear(a, w_out1, x1, bias=fp(layer.mha1.out_proj.bias), residual=x)
+            S_q2 = ops.SkinnyLinear(src[1], w_in2[:D], q2, bias=bq2.to(f32).contiguous(), ln=ln_arg[1])
+            S_o2 = ops.SkinnyLinear(c, w_out2, x3, bias=fp(layer.mha2.out_proj.bias), residual=x1)
+            S_f0 = ops.SkinnyLinear(src[2], w_f0, h, bias=fp(layer.ffn[0].bias), act=ops.ACT_RELU, ln=ln_arg[2])
+            S_f2 = ops.SkinnyLinear(h, w_f2, x5, bias=fp(layer.ffn[2].bias), residual=x3, workspace=ws, counters=ctr)
+            k0_ptr, v0_ptr, row_bytes = k_self.data_ptr(), v_self.data_ptr(), D * k_self.element_size()
+
+            def norm(i):
+                if not fuse_ln:
+                    n, raw, normed = norms[i]
+                    ops.layernorm_fwd(raw, n.weight, n.bias, n.eps, normed, m1, r1)
+        if skinny:
+            pn = (fp(layer.pre_norm.weight), fp(layer.pre_norm.bias), layer.pre_norm.eps)
+            # token 0: embedding of [CLS] + pre_norm; later tokens: argmax + embedding + pre_norm in one launch (below)
+            ops.decoder_next_token(x, None if fuse_ln else xn, table, pe, 0, ids_in=seq[0], ln=pn)
         for t in range(L):
+            if skinny:
+                S_qkv.p.out[1], S_qkv.p.out[2] = k0_ptr + t * row_bytes, v0_ptr + t * row_bytes  # cache rows [b, t, :]
+                S_qkv.run()
+                ops.decode_attn(q, k_self, v_self, a, H=nh, length=t + 1, dh=dh)
+                S_o1.run()
+                norm(1)
+                S_q2.run()
+                ops.decode_attn(q2, k_mem, v_mem, c, H=nh, length=Lm, dh=dh)
+                S_o2.run()
+                norm(2)
+                S_f0.run()
+                S_f2.run()
+                ops.layernorm_fwd(x5, layer.layernorm3.weight, layer.layernorm3.bias, layer.layernorm3.eps, x6, m1, r1)
+                ops.gemm_group([ops.GemmSpec(x6, w_vocab, None, bias=self.final_linear.bias, amax=(amax_v, amax_i))])
+                if t + 1 < L:
+                    ops.decoder_next_token(x, None if fuse_ln else xn, table, pe, t + 1, ids_out=seq[t + 1], amax=(amax_v, amax_i), ln=pn)
+                else:
+                    ops.argmax_partials(amax_v, amax_i, seq[t + 1])
+                if early_exit_every and (t + 1) % early_exit_every == 0 and self._all_finished(seq[1:t + 2], sep, eos):
+                    break
+                continue
             ops.decoder_embed(seq[t], pos_all[t], table, pe, x)  # 2*E[id] + pe[t]
             ops.layernorm_fwd(x, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps, xn, m1, r1)
             # q for this token; k, v written straight into the cache rows [b, t, :]
@@ -337,13 +397,8 @@ class Decoder(nn.Module):
             else:
                 ops.gemm(x6, w_vocab, logits, bias=self.final_linear.bias)
                 ops.argmax_rows(logits, seq[t + 1])
-            if early_exit_every and (t + 1) % early_exit_every == 0:
-                nxt = seq[1:t + 2]
-                done = nxt == sep
-                if eos is not None:
-                    done = done | (nxt == eos)
-                if bool(done.any(dim=0).all()):
-                    break
+            if early_exit_every and (t + 1) % early_exit_every == 0 and self._all_finished(seq[1:t + 2], sep, eos):
+                break
         out = seq[1:].t().contiguous()
         special = out == sep
         if eos is not None:

@@ -401,3 +401,60 @@ def decoder_embed(ids, pos, table, pe, out):
     L.check(L.load().m3ae_decoder_embed(_ptr(ids), _ptr(pos), _ptr(table), _ptr(pe), _ptr(out), ids.numel(), D,
                                         _code(out.dtype), _stream()), "m3ae_decoder_embed")
     return out
+
+
+class SkinnyLinear:
+    """A cached m3ae_skinny_linear launch (decoder token step): out = act(LN?(x) w^T + bias) (+ residual), M <= 128 rows.
+    `outs`: one output [M, N] or up to three [M, N/3] segments (column blocks of the fused projection, each with its own
+    row pitch — e.g. q and the K / V cache rows of the current position).  `ln` = (gamma, beta, eps) folds the LayerNorm
+    in front of the projection into the activation load (K = 768).  K > 768 is split across CTAs through `workspace`
+    (zeroed fp32 [128, N]) and `counters` (zeroed int32), which the kernel leaves zeroed."""
+
+    def __init__(self, x, w, outs, bias=None, residual=None, act=ACT_NONE, ln=None, workspace=None, counters=None):
+        _need_cuda(x, w)
+        outs = list(outs) if isinstance(outs, (list, tuple)) else [outs]
+        M, K = x.shape
+        N = w.shape[0]
+        assert x.dtype == w.dtype == torch.bfloat16 and w.shape[1] == K and x.stride(1) == 1 and w.stride(1) == 1
+        assert N % len(outs) == 0 and all(o.dtype == torch.bfloat16 and o.shape == (M, N // len(outs)) and o.stride(1) == 1 for o in outs)
+        p = L.SkinnyParams()
+        p.x, p.ldx, p.w, p.ldw = _ptr(x), x.stride(0), _ptr(w), w.stride(0)
+        p.bias = _ptr(bias) if bias is not None else None
+        if bias is not None:
+            assert bias.dtype == torch.float32 and bias.is_contiguous() and bias.numel() == N
+        if residual is not None:
+            assert residual.dtype == torch.bfloat16 and residual.shape == (M, N) and residual.stride(1) == 1
+            p.residual, p.ldr = _ptr(residual), residual.stride(0)
+        for i, o in enumerate(outs):
+            p.out[i], p.ldo[i] = _ptr(o), o.stride(0)
+        p.seg_cols, p.M, p.N, p.K, p.act = N // len(outs), M, N, K, int(act)
+        p.ksplit = 1
+        if K > 768:
+            p.ksplit = next(s for s in range(2, 65) if K % s == 0 and K // s <= 768 and (K // s) % 16 == 0 and (K // s) <= 512)
+            assert workspace is not None and counters is not None and workspace.dtype == torch.float32 and workspace.numel() >= 128 * N
+            assert counters.dtype == torch.int32 and counters.numel() >= (N + 15) // 16
+            p.ws, p.counters = _ptr(workspace), _ptr(counters)
+        if ln is not None:
+            gamma, beta, eps = ln
+            assert gamma.dtype == beta.dtype == torch.float32 and gamma.is_contiguous() and beta.is_contiguous() and K == 768
+            p.ln_gamma, p.ln_beta, p.ln_eps = _ptr(gamma), _ptr(beta), float(eps)
+        self.p, self.keep = p, (x, w, outs, bias, residual, ln, workspace, counters)
+        self.fn = L.load().m3ae_skinny_linear
+
+    def run(self):
+        L.check(self.fn(C.byref(self.p), _stream()), "m3ae_skinny_linear")
+
+
+def decoder_next_token(x, xn, table, pe, pos, ids_in=None, ids_out=None, amax=None, ln=None):
+    """One launch for the greedy decoder's token hand-over: (optional) row argmax from the vocabulary projection's partials
+    `amax` = (values [G, M] fp32, columns [G, M] int32) -> ids_out, x = 2*E[id] + pe[pos], xn = LayerNorm(x) (ln = (gamma, beta,
+    eps); xn None skips it)."""
+    M, D = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and table.dtype == torch.float32 and pe.dtype == torch.float32
+    gamma, beta, eps = ln if ln is not None else (None, None, 0.0)
+    val, idx, G = (amax[0], amax[1], amax[0].shape[0]) if amax is not None else (None, None, 0)
+    L.check(L.load().m3ae_decoder_next_token(_ptr(val) if val is not None else None, _ptr(idx) if idx is not None else None, G, M,
+                                             _ptr(ids_in) if ids_in is not None else None, _ptr(ids_out) if ids_out is not None else None,
+                                             int(pos), _ptr(table), _ptr(pe), _ptr(gamma) if gamma is not None else None,
+                                             _ptr(beta) if beta is not None else None, float(eps), _ptr(x),
+                                             _ptr(xn) if xn is not None else None, D, _stream()), "m3ae_decoder_next_token")

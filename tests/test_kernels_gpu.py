@@ -691,3 +691,77 @@ def test_gemm_row_argmax_epilogue(skinny):
     assert torch.equal(ids, want) and torch.equal(ids2, want)
     assert int(want[3]) == 77, "tie case not exercised"
     assert torch.equal(ops.argmax_rows(logits), want)
+
+
+# ----------------------------------------------------------------------------- skinny linear (decoder token step)
+@pytest.mark.parametrize("M", [128, 37, 1])
+def test_skinny_linear_matches_layernorm_plus_gemm(M):
+    """csrc/skinny_linear.cu against the kernels it replaces in the decoder step (ln_fwd + tcgen05 GEMM): fused LayerNorm +
+    QKV with a segmented output into strided cache rows, out-projection with residual, FFN-up with ReLU (N = 3072: more
+    column tiles than SMs, the activation panel stays resident), FFN-down with split-K (K = 3072) run twice (the kernel must
+    leave its workspace and counters zeroed)."""
+    D, FF, L = 768, 3072, 16
+    bf = torch.bfloat16
+    x = rnd(M, D, seed=1).to(bf)
+    gamma, beta = (1.0 + 0.1 * rnd(D, seed=2)).contiguous(), (0.1 * rnd(D, seed=3)).contiguous()
+    w_qkv, b_qkv = (0.05 * rnd(3 * D, D, seed=4)).to(bf), rnd(3 * D, seed=5)
+    # reference: ln_fwd then three GEMM problems
+    xn = torch.empty_like(x)
+    ops.layernorm_fwd(x, gamma, beta, 1e-5, xn, torch.empty(M, device=DEV), torch.empty(M, device=DEV))
+    ref = torch.empty(M, 3 * D, dtype=bf, device=DEV)
+    ops.gemm(xn, w_qkv, ref, bias=b_qkv)
+    q = torch.empty(M, D, dtype=bf, device=DEV)
+    kc, vc = torch.zeros(M, L, D, dtype=bf, device=DEV), torch.zeros(M, L, D, dtype=bf, device=DEV)
+    t = 5
+    ops.SkinnyLinear(x, w_qkv, [q, kc[:, t, :], vc[:, t, :]], bias=b_qkv, ln=(gamma, beta, 1e-5)).run()
+    got = torch.cat([q, kc[:, t, :], vc[:, t, :]], dim=1)
+    assert rel_err(got, ref) < 4e-3, f"fused LN + QKV M={M}: {rel_err(got, ref):.3e}"
+    assert (kc[:, :t] == 0).all() and (kc[:, t + 1:] == 0).all(), "only cache row t may be written"
+    # out-projection + residual
+    w_o, b_o, res = (0.05 * rnd(D, D, seed=6)).to(bf), rnd(D, seed=7), rnd(M, D, seed=8).to(bf)
+    ref = torch.empty(M, D, dtype=bf, device=DEV)
+    ops.gemm(x, w_o, ref, bias=b_o, residual=res)
+    out = torch.empty(M, D, dtype=bf, device=DEV)
+    ops.SkinnyLinear(x, w_o, out, bias=b_o, residual=res).run()
+    assert rel_err(out, ref) < 4e-3
+    # FFN-up (ReLU, fused LN) and FFN-down (split-K, residual), twice through the same workspace
+    w0, b0 = (0.05 * rnd(FF, D, seed=9)).to(bf), rnd(FF, seed=10)
+    w2, b2 = (0.05 * rnd(D, FF, seed=11)).to(bf), rnd(D, seed=12)
+    h_ref = torch.empty(M, FF, dtype=bf, device=DEV)
+    ops.gemm(xn, w0, h_ref, bias=b0, act=ops.ACT_RELU)
+    y_ref = torch.empty(M, D, dtype=bf, device=DEV)
+    ops.gemm(h_ref, w2, y_ref, bias=b2, residual=res)
+    h, y = torch.empty(M, FF, dtype=bf, device=DEV), torch.empty(M, D, dtype=bf, device=DEV)
+    ws, ctr = torch.zeros(128 * D, device=DEV), torch.zeros(64, dtype=torch.int32, device=DEV)
+    up = ops.SkinnyLinear(x, w0, h, bias=b0, act=ops.ACT_RELU, ln=(gamma, beta, 1e-5))
+    down = ops.SkinnyLinear(h, w2, y, bias=b2, residual=res, workspace=ws, counters=ctr)
+    for rep in range(2):
+        y.fill_(float("nan"))
+        up.run()
+        down.run()
+        assert rel_err(h, h_ref) < 4e-3 and rel_err(y, y_ref) < 4e-3, (rep, rel_err(h, h_ref), rel_err(y, y_ref))
+        assert (ws == 0).all() and (ctr == 0).all(), "split-K workspace / counters must be left zeroed"
+
+
+def test_decoder_next_token_equals_argmax_embed_layernorm():
+    """m3ae_decoder_next_token (one warp per sequence) against the three launches it replaces, bit for bit, including argmax ties."""
+    M, D, V, G = 128, 768, 30522, 148
+    table, pe = rnd(V, D, seed=1), rnd(64, D, seed=2)
+    gamma, beta = (1.0 + 0.1 * rnd(D, seed=3)).contiguous(), (0.1 * rnd(D, seed=4)).contiguous()
+    val = rnd(G, M, seed=5)
+    idx = torch.randint(0, V, (G, M), generator=torch.Generator().manual_seed(6)).to(torch.int32).to(DEV)
+    val[3, :16] = val.max() + 1.0
+    val[77, :16] = val[3, :16]  # ties: the smaller column wins
+    ids_ref = torch.empty(M, dtype=torch.int64, device=DEV)
+    ops.argmax_partials(val, idx, ids_ref)
+    x_ref = torch.empty(M, D, dtype=torch.bfloat16, device=DEV)
+    pos = torch.full((M,), 7, dtype=torch.int32, device=DEV)
+    ops.decoder_embed(ids_ref, pos, table, pe, x_ref)
+    xn_ref = torch.empty_like(x_ref)
+    ops.layernorm_fwd(x_ref, gamma, beta, 1e-5, xn_ref, torch.empty(M, device=DEV), torch.empty(M, device=DEV))
+    ids, x, xn = torch.zeros_like(ids_ref), torch.zeros_like(x_ref), torch.zeros_like(x_ref)
+    ops.decoder_next_token(x, xn, table, pe, 7, ids_out=ids, amax=(val, idx), ln=(gamma, beta, 1e-5))
+    assert torch.equal(ids, ids_ref) and torch.equal(x, x_ref) and torch.equal(xn, xn_ref)
+    x2, xn2 = torch.zeros_like(x_ref), torch.zeros_like(x_ref)
+    ops.decoder_next_token(x2, xn2, table, pe, 7, ids_in=ids_ref, ln=(gamma, beta, 1e-5))
+    assert torch.equal(x2, x_ref) and torch.equal(xn2, xn_ref)
