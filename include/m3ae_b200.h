@@ -320,6 +320,9 @@ int m3ae_set_gemm_epilogue(int32_t generic);
  * 1 = always one CTA per 128x256 tile, 2 = one CTA pair per cluster (no multicast), 3 = always two pairs per cluster.
  * Results are identical.  Process-global test / benchmarking hook: not synchronised with concurrent launches. */
 int m3ae_set_gemm_cta_pair(int32_t mode);
+/* Number of SMs the persistent tcgen05 GEMM leaves free (0 = none, default) for kernels of other streams — the NCCL gradient
+ * all-reduce of data-parallel fine-tuning (ddp.py sets it from M3AE_DDP_RESERVE_SMS when world_size > 1). */
+int m3ae_set_gemm_reserved_sms(int32_t n);
 /* Single-CTA launches (every problem M <= 128): 0 = auto (128x64 tiles when 128x256 tiles would occupy less than a third of
  * the SMs), 1 = always 128x256, 2 = always 128x64.  Results are identical.  Process-global test hook. */
 int m3ae_set_gemm_skinny(int32_t mode);

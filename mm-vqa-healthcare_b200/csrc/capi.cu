@@ -84,6 +84,7 @@ int decoder_embed(const int64_t*, const int32_t*, const float*, const float*, vo
 extern bool force_generic_epilogue;
 extern int gemm_cta_pair_mode;
 extern int gemm_skinny_mode;
+extern int gemm_reserved_sms;
 static int g_pdl_mode = -1;  // -1: not decided yet (M3AE_PDL environment variable), 0 off, 1 on
 bool pdl_on() {
   if (g_pdl_mode < 0) {
@@ -248,6 +249,11 @@ int m3ae_skinny_linear(const m3ae_skinny_params_t* p, void* stream) {
 }
 int m3ae_set_pdl(int32_t on) {
   g_pdl_mode = on ? 1 : 0;
+  return M3AE_OK;
+}
+int m3ae_set_gemm_reserved_sms(int32_t n) {
+  M3AE_CHECK(n >= 0 && n <= 64, M3AE_ERR_INVALID, "m3ae_set_gemm_reserved_sms: %d not in [0, 64]", n);
+  gemm_reserved_sms = n;
   return M3AE_OK;
 }
 int m3ae_set_gemm_skinny(int32_t mode) {

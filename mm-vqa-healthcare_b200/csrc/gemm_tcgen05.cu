@@ -767,6 +767,7 @@ void count_launch();
 bool force_generic_epilogue = false;  // test hook (m3ae_set_gemm_epilogue): run the per-element epilogue everywhere
 int gemm_cta_pair_mode = 0;           // m3ae_set_gemm_cta_pair: 0 auto, 1 always single CTA, 2 always CTA pair
 int gemm_skinny_mode = 0;             // m3ae_set_gemm_skinny: 0 auto, 1 never, 2 always (single-CTA launches only)
+int gemm_reserved_sms = 0;            // m3ae_set_gemm_reserved_sms: SMs the persistent kernel leaves to other streams
 
 namespace {
 // Clusters of CL CTAs that can be resident at once (the kernel is persistent: a cluster that has to wait for another one to
@@ -805,7 +806,13 @@ int launch_tc(TcParams& P, int units, cudaStream_t stream) {
   });
   M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CL, BNV>::SMEM_BYTES,
              cudaGetErrorString(attr_err));
-  const int workers_max = CL == 1 ? sm_count() : max_clusters<CL, BNV>();
+  int workers_max = CL == 1 ? sm_count() : max_clusters<CL, BNV>();
+  // SMs left free for concurrently running kernels of other streams (the NCCL gradient all-reduce of data-parallel fine-tuning:
+  // a persistent GEMM on every SM makes the collective's CTAs wait for a GEMM launch to retire) — m3ae_set_gemm_reserved_sms
+  if (gemm_reserved_sms > 0) {
+    const int keep = (sm_count() - gemm_reserved_sms) / CL;
+    if (keep >= 1 && keep < workers_max) workers_max = keep;
+  }
   const int workers = units < workers_max ? units : workers_max;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

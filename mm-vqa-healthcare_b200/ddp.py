@@ -56,6 +56,12 @@ class GradientAllReducer:
         self.group = group
         self.cuda = self.params[0].is_cuda
         self.comm_stream = torch.cuda.Stream() if self.cuda else None
+        # M3AE_DDP_RESERVE_SMS: SMs the persistent GEMM leaves to NCCL's kernels while an exchange overlaps backward
+        # (default 0; A/B in profiles/r2_ddp_reserve_ab_n2.txt)
+        reserve = int(os.environ.get("M3AE_DDP_RESERVE_SMS", "0"))
+        if self.cuda and self.world > 1 and reserve > 0:
+            from . import ops
+            ops.set_gemm_reserved_sms(reserve)
         self.buckets = []        # (flat, [params]) — bucketed parameters
         self.groups = []         # [params] — zero-copy groups
         self._slot = {}          # id(param) -> ("b", bucket index) | ("g", group index)

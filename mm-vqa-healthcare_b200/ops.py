@@ -379,6 +379,11 @@ def set_pdl(on):
     L.check(L.load().m3ae_set_pdl(1 if on else 0), "m3ae_set_pdl")
 
 
+def set_gemm_reserved_sms(n):
+    """SMs the persistent tcgen05 GEMM leaves free for kernels of other streams (the NCCL all-reduce under data parallelism)."""
+    L.check(L.load().m3ae_set_gemm_reserved_sms(int(n)), "m3ae_set_gemm_reserved_sms")
+
+
 def set_gemm_skinny(mode):
     """Test hook for single-CTA GEMM launches (every problem M <= 128): 0 auto, 1 always 128x256 tiles, 2 always 128x64 tiles."""
     L.check(L.load().m3ae_set_gemm_skinny(int(mode)), "m3ae_set_gemm_skinny")
