@@ -44,12 +44,13 @@ def test_struct_layouts_match_header_sizes():
     import m3ae_b200
     with tempfile.TemporaryDirectory() as d:
         src = os.path.join(d, "p.c")
-        open(src, "w").write('#include <stdio.h>\n#include "m3ae_b200.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(m3ae_gemm_epilogue_t), sizeof(m3ae_gemm_problem_t), sizeof(m3ae_attn_params_t));return 0;}\n')
+        open(src, "w").write('#include <stdio.h>\n#include "m3ae_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n", sizeof(m3ae_gemm_epilogue_t), sizeof(m3ae_gemm_problem_t), sizeof(m3ae_attn_params_t), sizeof(m3ae_skinny_params_t), sizeof(m3ae_dropbits_item_t));return 0;}\n')
         exe = os.path.join(d, "p")
         subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), src, "-o", exe], check=True)
         sizes = [int(x) for x in subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()]
     L = m3ae_b200._lib
-    assert sizes == [ctypes.sizeof(L.GemmEpilogue), ctypes.sizeof(L.GemmProblem), ctypes.sizeof(L.AttnParams)]
+    assert sizes == [ctypes.sizeof(L.GemmEpilogue), ctypes.sizeof(L.GemmProblem), ctypes.sizeof(L.AttnParams),
+                     ctypes.sizeof(L.SkinnyParams), ctypes.sizeof(L.DropBitsItem)]
 
 
 def test_no_cpu_fallback(lib):
