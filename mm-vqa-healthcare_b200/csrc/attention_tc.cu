@@ -1033,13 +1033,14 @@ int set_smem_attr(K kernel) {
 
 int attn_fwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st) {
   if (!tc_supported(p, false, force)) return M3AE_ERR_UNSUPPORTED;
-  static std::once_flag once;
-  static int attr_rc = M3AE_OK;
-  std::call_once(once, [] {
-    attr_rc = set_smem_attr(attn_fwd_tc_kernel<false>);
-    if (!attr_rc) attr_rc = set_smem_attr(attn_fwd_tc_kernel<true>);
+  static std::once_flag once[64];
+  static int attr_rcs[64];
+  const int slot = current_device_slot();
+  std::call_once(once[slot], [slot] {
+    attr_rcs[slot] = set_smem_attr(attn_fwd_tc_kernel<false>);
+    if (!attr_rcs[slot]) attr_rcs[slot] = set_smem_attr(attn_fwd_tc_kernel<true>);
   });
-  if (attr_rc) return attr_rc;
+  if (attr_rcs[slot]) return attr_rcs[slot];
   TcAttn A;
   memset(&A, 0, sizeof(A));
   int smem = 0;
@@ -1055,13 +1056,14 @@ int attn_fwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st) {
 
 int attn_bwd_tc(const m3ae_attn_params_t* p, bool force, cudaStream_t st) {
   if (!tc_supported(p, true, force)) return M3AE_ERR_UNSUPPORTED;
-  static std::once_flag once;
-  static int attr_rc = M3AE_OK;
-  std::call_once(once, [] {
-    attr_rc = set_smem_attr(attn_bwd_tc_kernel<false>);
-    if (!attr_rc) attr_rc = set_smem_attr(attn_bwd_tc_kernel<true>);
+  static std::once_flag once[64];
+  static int attr_rcs[64];
+  const int slot = current_device_slot();
+  std::call_once(once[slot], [slot] {
+    attr_rcs[slot] = set_smem_attr(attn_bwd_tc_kernel<false>);
+    if (!attr_rcs[slot]) attr_rcs[slot] = set_smem_attr(attn_bwd_tc_kernel<true>);
   });
-  if (attr_rc) return attr_rc;
+  if (attr_rcs[slot]) return attr_rcs[slot];
   TcAttn A;
   memset(&A, 0, sizeof(A));
   int smem = 0;

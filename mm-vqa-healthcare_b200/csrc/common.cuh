@@ -34,6 +34,13 @@ void set_last_error(const char* fmt, ...);
   } while (0)
 
 int check_device_sm100();  // 0 when the current device is sm_100, else error code (and sets last error)
+// cudaFuncSetAttribute (dynamic shared memory opt-in) is per DEVICE: call sites keep one flag per device ordinal, so a second
+// GPU driven from the same process gets its opt-in too
+inline int current_device_slot() {
+  int dev = 0;
+  (void)cudaGetDevice(&dev);
+  return dev & 63;
+}
 int sm_count();
 
 // ---------------------------------------------------------------- programmatic dependent launch

@@ -799,11 +799,13 @@ int max_clusters() {
 
 template <int CL, int BNV>
 int launch_tc(TcParams& P, int units, cudaStream_t stream) {
-  static std::once_flag attr_once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_tcgen05_kernel<CL, BNV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CL, BNV>::SMEM_BYTES);
+  static std::once_flag attr_once[64];
+  static cudaError_t attr_errs[64];
+  const int slot = current_device_slot();
+  std::call_once(attr_once[slot], [slot] {
+    attr_errs[slot] = cudaFuncSetAttribute(gemm_tcgen05_kernel<CL, BNV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CL, BNV>::SMEM_BYTES);
   });
+  const cudaError_t attr_err = attr_errs[slot];
   M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(smem=%d) failed: %s", Cfg<CL, BNV>::SMEM_BYTES,
              cudaGetErrorString(attr_err));
   int workers_max = CL == 1 ? sm_count() : max_clusters<CL, BNV>();

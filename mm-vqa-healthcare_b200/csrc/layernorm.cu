@@ -507,11 +507,13 @@ int layernorm_bwd(const void* dy, const void* x, const float* mean, const float*
   const bool ring_ok = dtype == M3AE_BF16 && H == 768 && !ln_bwd_force_registers && ((((uintptr_t)x) | ((uintptr_t)dy)) & 15) == 0;
   if (ring_ok) {
     const size_t smem_ring = smem + (size_t)LN_WARPS * LN_RING * 2 * H * sizeof(bf16) + (size_t)LN_WARPS * LN_RING * sizeof(uint64_t);
-    static std::once_flag once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(once, [smem_ring] {
-      attr_err = cudaFuncSetAttribute(ln_bwd_kernel<bf16, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ring);
+    static std::once_flag once[64];
+    static cudaError_t attr_errs[64];
+    const int slot = current_device_slot();
+    std::call_once(once[slot], [smem_ring, slot] {
+      attr_errs[slot] = cudaFuncSetAttribute(ln_bwd_kernel<bf16, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ring);
     });
+    const cudaError_t attr_err = attr_errs[slot];
     M3AE_CHECK(attr_err == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(ln_bwd ring smem) failed: %s", cudaGetErrorString(attr_err));
     LN_BWD(bf16, 3, true, smem_ring);
   } else if (dtype == M3AE_BF16 && H == 768) LN_BWD(bf16, 3, false, smem);

@@ -117,8 +117,7 @@ class Decoder(nn.Module):
         dh = D // nh
         xn = Fn.layernorm(e2, layer.pre_norm.weight, layer.pre_norm.bias, layer.pre_norm.eps)
         qkv = Fn.linear(xn, layer.mha1.in_proj_weight, layer.mha1.in_proj_bias, dtype=dt)
-        a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], pad_mask_add, B, nh, T, T, dh, causal=True,
-                         drop_p=drop_p, drop_seed=seed, drop_site=1)
+        a = Fn.attention_packed(qkv, pad_mask_add, B, nh, T, dh, causal=True, drop_p=drop_p, drop_seed=seed, drop_site=1)
         x = Fn.linear(a, layer.mha1.out_proj.weight, layer.mha1.out_proj.bias, dtype=dt, residual=e2,
                       drop_p=drop_p, drop_seed=seed, drop_site=2)                      # residual + dropout1(mha1)
         residual = x
@@ -127,8 +126,7 @@ class Decoder(nn.Module):
         w2, b2 = layer.mha2.in_proj_weight, layer.mha2.in_proj_bias
         q2 = Fn.linear(x, w2[:E], b2[:E], dtype=dt)
         kv2 = Fn.linear(mem2, w2[E:], b2[E:], dtype=dt)
-        c = Fn.attention(q2, kv2[:, :D], kv2[:, D:], None, B, nh, T, Lm, dh, causal=False,
-                         drop_p=drop_p, drop_seed=seed, drop_site=3)
+        c = Fn.attention_packed_kv(q2, kv2, None, B, nh, T, Lm, dh, causal=False, drop_p=drop_p, drop_seed=seed, drop_site=3)
         x = Fn.linear(c, layer.mha2.out_proj.weight, layer.mha2.out_proj.bias, dtype=dt, residual=residual,
                       drop_p=drop_p, drop_seed=seed, drop_site=4)                      # dropout2(mha2) + residual
         residual = x

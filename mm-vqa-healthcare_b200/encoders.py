@@ -101,7 +101,7 @@ class ClipVisionEncoder(nn.Module):
             nh = blk.n_head
             h = Fn.layernorm(x2, blk.ln_1.weight, blk.ln_1.bias, blk.ln_1.eps)
             qkv = Fn.linear(h, blk.attn.in_proj_weight, blk.attn.in_proj_bias, dtype=dt)
-            a = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], None, B, nh, L, L, D // nh)
+            a = Fn.attention_packed(qkv, None, B, nh, L, D // nh)
             x2 = Fn.linear(a, blk.attn.out_proj.weight, blk.attn.out_proj.bias, dtype=dt, residual=x2)   # x + attn(ln_1(x))
             h = Fn.layernorm(x2, blk.ln_2.weight, blk.ln_2.bias, blk.ln_2.eps)
             x2 = Fn.ffn(h, blk.mlp.c_fc.weight, blk.mlp.c_fc.bias, blk.mlp.c_proj.weight, blk.mlp.c_proj.bias, residual=x2,
@@ -133,7 +133,7 @@ def roberta_layer(layer, h, mask_add, B, L, compute_dtype, training):
     wqkv = torch.cat([att.query.weight, att.key.weight, att.value.weight], dim=0)
     bqkv = torch.cat([att.query.bias, att.key.bias, att.value.bias], dim=0)
     qkv = Fn.linear(h, wqkv, bqkv, dtype=compute_dtype)
-    c = Fn.attention(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], mask_add, B, nh, L, L, D // nh, drop_p=pa, drop_seed=seed,
+    c = Fn.attention_packed(qkv, mask_add, B, nh, L, D // nh, drop_p=pa, drop_seed=seed,
                      drop_site=0)
     h1 = Fn.linear(c, so.dense.weight, so.dense.bias, dtype=compute_dtype, residual=h, drop_p=ph, drop_seed=seed, drop_site=1)
     a = Fn.layernorm(h1, so.LayerNorm.weight, so.LayerNorm.bias, so.LayerNorm.eps)
