@@ -290,7 +290,8 @@ def run_ours(args):
     from m3ae_b200.ddp import GradientAllReducer
     # M3AE_BENCH_FORCE_REDUCER=1: diagnostic — run the N>1 gradient bookkeeping (bucket views, accumulate, zero) on one GPU
     force_reducer = os.environ.get("M3AE_BENCH_FORCE_REDUCER", "0") == "1"
-    reducer = GradientAllReducer(params, world) if (world > 1 or force_reducer) else None
+    # fp32 (strict-parity) runs keep the exact fp32 gradient exchange; bf16 runs take the reducer's default (bf16 wire from 4 ranks on)
+    reducer = GradientAllReducer(params, world, wire_dtype=torch.float32 if dtype == torch.float32 else None) if (world > 1 or force_reducer) else None
     if reducer is not None:
         reducer.broadcast_parameters(0)
 
@@ -480,7 +481,7 @@ def run_ours(args):
             "dtype": args.dtype, "data": "synthetic (seeded uni-modal features 288px/32tok, random-init weights)",
             "config": {"workload": "M3AE VQA-RAD fine-tune step (fwd+bwd), fusion stack 6+6 BertCrossLayer + heads + BCE, batch 64/GPU, 288px (325 image tokens) / 32 text tokens",
                        "per_gpu_batch": B, "global_batch": B * world, "dropout": 0.1, "optimizer": "AdamW(fused) inside the timed step",
-                       "parallelism": f"dp{world}" + (" (NCCL gradient all-reduce)" if world > 1 else ""),
+                       "parallelism": f"dp{world}" + (f" (NCCL gradient all-reduce, {'bf16' if reducer.wire_dtype == torch.bfloat16 else 'fp32'} wire)" if world > 1 else ""),
                        "l2": "no explicit flush: per-step working set (>4 GB of activations + 0.7 GB weights) far exceeds the 126 MB L2"},
             "clocks": sampler.summary() if sampler else None,
             "e2e": {"value": round(sps_e2e, 2), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,

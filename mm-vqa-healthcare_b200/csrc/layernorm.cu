@@ -62,6 +62,8 @@ __device__ __forceinline__ void ld_param(const float* p, float (&v)[VN]) {
   }
 }
 
+// (A persistent variant — 8 CTAs per SM walking rows with the next row prefetched — measured SLOWER: 20-21 us against 17.9 us
+// for an image-sized launch under ncu, round 2; one short-lived 4-row CTA per 4 rows is kept.)
 // H == HV * 32 * Vec<T>::N exactly (768 or 1536 columns on this path).  One warp per row; gamma / beta come in as
 // 16-byte loads (the first version read them as scalars: 48 extra load instructions per row, 4x slower than the HBM bound).
 template <typename T, int HV>

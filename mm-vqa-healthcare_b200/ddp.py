@@ -23,11 +23,14 @@ class GradientAllReducer:
     Bucketed parameters.  Everything else (heads, poolers, projections; every parameter of a model whose gradients do
     not share storage) keeps `.grad` as a view into flat fp32 buckets that are all-reduced when complete.
 
-    bf16 wire format (CUDA, opt-in: M3AE_DDP_WIRE=bf16 or wire_dtype=torch.bfloat16).  The payload of an exchange unit is
+    bf16 wire format (CUDA; default from 4 ranks on, M3AE_DDP_WIRE=fp32|bf16|auto or wire_dtype= override).  The payload of an exchange unit is
     cast to bf16 on the communication stream, all-reduced (NCCL AVG) and cast back into the fp32 gradient buffer: half the
     bytes over NVLink; master gradients, optimizer and its state stay fp32 (the trade PyTorch DDP's bf16_compress_hook
     makes).  Measured at N = 2 (profiles/r2_ddp_wire_ab_n2.txt): 15.81 ms/step against 15.71 ms with the exact fp32
-    exchange — the cost of data parallelism on this path is not link bytes, so the default stays fp32.
+    exchange (neutral: the two casts cost what the shorter collective saves); at N = 8 (profiles/r2_bench_8gpu*.json):
+    15.61 against 16.12 ms/step — the collective's kernels occupy SMs and HBM beside the persistent GEMM for half as long
+    (in-step GEMM rate 985 vs 958 TFLOP/s).  Averaged gradients differ from the exact exchange by 3.4e-3 relative
+    (bench grad_check, gate 2e-2); replicas stay bit-identical.
 
     Use: `zero_grad()` before every backward, `wait()` after it, then the optimizer step.  One backward per exchange.
     """
@@ -46,13 +49,17 @@ class GradientAllReducer:
             bucket_mb = float(os.environ.get("M3AE_DDP_BUCKET_MB", "64"))
         self.overlap, self.zero_copy, self.bucket_mb = bool(overlap), bool(zero_copy), bucket_mb
         self.params = [p for p in params if p.requires_grad]
+        self.world = world_size if world_size is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         if wire_dtype is None:
-            wire_dtype = torch.bfloat16 if os.environ.get("M3AE_DDP_WIRE", "fp32") == "bf16" else torch.float32
+            # auto: exact fp32 exchange up to 2 ranks (bf16 measured neutral there), bf16 wire from 4 ranks on, where the
+            # collective's kernels run long enough beside the persistent GEMM to matter (N = 8: 16.12 -> 15.61 ms/step,
+            # profiles/r2_bench_8gpu*.json).  M3AE_DDP_WIRE=fp32 / bf16 or wire_dtype= force either.
+            env = os.environ.get("M3AE_DDP_WIRE", "auto")
+            wire_dtype = torch.bfloat16 if env == "bf16" or (env == "auto" and self.world >= 4) else torch.float32
         if not self.params[0].is_cuda:
             wire_dtype = torch.float32  # gloo (CPU tests): exact exchange
         self.wire_dtype = wire_dtype
         self._wire = {}          # exchange unit -> persistent bf16 staging buffer
-        self.world = world_size if world_size is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.group = group
         self.cuda = self.params[0].is_cuda
         self.comm_stream = torch.cuda.Stream() if self.cuda else None
