@@ -290,7 +290,7 @@ def run_ours(args):
     from m3ae_b200.ddp import GradientAllReducer
     # M3AE_BENCH_FORCE_REDUCER=1: diagnostic — run the N>1 gradient bookkeeping (bucket views, accumulate, zero) on one GPU
     force_reducer = os.environ.get("M3AE_BENCH_FORCE_REDUCER", "0") == "1"
-    # fp32 (strict-parity) runs keep the exact fp32 gradient exchange; bf16 runs take the reducer's default (bf16 wire from 4 ranks on)
+    # fp32 (strict-parity) runs keep the exact fp32 gradient exchange; bf16 runs take the reducer's default (bf16 wire from 8 ranks on)
     reducer = GradientAllReducer(params, world, wire_dtype=torch.float32 if dtype == torch.float32 else None) if (world > 1 or force_reducer) else None
     if reducer is not None:
         reducer.broadcast_parameters(0)

@@ -23,11 +23,11 @@ class GradientAllReducer:
     Bucketed parameters.  Everything else (heads, poolers, projections; every parameter of a model whose gradients do
     not share storage) keeps `.grad` as a view into flat fp32 buckets that are all-reduced when complete.
 
-    bf16 wire format (CUDA; default from 4 ranks on, M3AE_DDP_WIRE=fp32|bf16|auto or wire_dtype= override).  The payload of an exchange unit is
+    bf16 wire format (CUDA; default from 8 ranks on, M3AE_DDP_WIRE=fp32|bf16|auto or wire_dtype= override).  The payload of an exchange unit is
     cast to bf16 on the communication stream, all-reduced (NCCL AVG) and cast back into the fp32 gradient buffer: half the
     bytes over NVLink; master gradients, optimizer and its state stay fp32 (the trade PyTorch DDP's bf16_compress_hook
     makes).  Measured at N = 2 (profiles/r2_ddp_wire_ab_n2.txt): 15.81 ms/step against 15.71 ms with the exact fp32
-    exchange (neutral: the two casts cost what the shorter collective saves); at N = 8 (profiles/r2_bench_8gpu*.json):
+    exchange (neutral: the two casts cost what the shorter collective saves; N = 4: 15.60 vs 15.59); at N = 8 (profiles/r2_ddp_wire_ab.txt):
     15.61 against 16.12 ms/step — the collective's kernels occupy SMs and HBM beside the persistent GEMM for half as long
     (in-step GEMM rate 985 vs 958 TFLOP/s).  Averaged gradients differ from the exact exchange by 3.4e-3 relative
     (bench grad_check, gate 2e-2); replicas stay bit-identical.
@@ -51,11 +51,11 @@ class GradientAllReducer:
         self.params = [p for p in params if p.requires_grad]
         self.world = world_size if world_size is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         if wire_dtype is None:
-            # auto: exact fp32 exchange up to 2 ranks (bf16 measured neutral there), bf16 wire from 4 ranks on, where the
-            # collective's kernels run long enough beside the persistent GEMM to matter (N = 8: 16.12 -> 15.61 ms/step,
-            # profiles/r2_bench_8gpu*.json).  M3AE_DDP_WIRE=fp32 / bf16 or wire_dtype= force either.
+            # auto: exact fp32 exchange below 8 ranks (bf16 measured neutral at N = 2 and N = 4), bf16 wire from 8 ranks on, where
+            # the collective's kernels run long enough beside the persistent GEMM to matter (N = 8: 16.12 -> 15.61 ms/step,
+            # profiles/r2_ddp_wire_ab.txt).  M3AE_DDP_WIRE=fp32 / bf16 or wire_dtype= force either.
             env = os.environ.get("M3AE_DDP_WIRE", "auto")
-            wire_dtype = torch.bfloat16 if env == "bf16" or (env == "auto" and self.world >= 4) else torch.float32
+            wire_dtype = torch.bfloat16 if env == "bf16" or (env == "auto" and self.world >= 8) else torch.float32
         if not self.params[0].is_cuda:
             wire_dtype = torch.float32  # gloo (CPU tests): exact exchange
         self.wire_dtype = wire_dtype
