@@ -59,12 +59,13 @@ def peaks():
 
 def gemm_traffic():
     """Per-launch DRAM bytes of the dominant kernel from the committed `ncu --set full` capture (tools/gemm_traffic.py)."""
-    p = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
-    if not os.path.exists(p):
-        return None, None
-    d = json.load(open(p))
-    return d.get("avg_dram_bytes_per_launch"), (f"profiles/r1_gemm_traffic.json: mean of 6 forward launches of one layer pair, "
-                                                 f"algorithmic mean {d.get('avg_algorithmic_bytes_per_launch')} B")
+    for name in ("r2_gemm_traffic.json", "r1_gemm_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            d = json.load(open(p))
+            return d.get("avg_dram_bytes_per_launch"), (f"profiles/{name}: mean of 6 forward launches of one layer pair, "
+                                                         f"algorithmic mean {d.get('avg_algorithmic_bytes_per_launch')} B")
+    return None, None
 
 
 def synth_batch(B, device, seed, pin=False):

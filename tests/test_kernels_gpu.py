@@ -765,3 +765,20 @@ def test_decoder_next_token_equals_argmax_embed_layernorm():
     x2, xn2 = torch.zeros_like(x_ref), torch.zeros_like(x_ref)
     ops.decoder_next_token(x2, xn2, table, pe, 7, ids_in=ids_ref, ln=(gamma, beta, 1e-5))
     assert torch.equal(x2, x_ref) and torch.equal(xn2, xn_ref)
+
+
+def test_gemm_reserved_sms_is_bit_identical():
+    """m3ae_set_gemm_reserved_sms only shrinks the persistent grid: same tiles, same K order -> identical bits."""
+    M, N, K = 2600, 768, 3072
+    a, b = rnd(M, K, seed=1).to(torch.bfloat16), (0.05 * rnd(N, K, seed=2)).to(torch.bfloat16)
+    bias = rnd(N, seed=3)
+    ref = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    ops.gemm(a, b, ref, bias=bias, act=ops.ACT_GELU)
+    try:
+        for n in (8, 64):
+            ops.set_gemm_reserved_sms(n)
+            out = torch.empty_like(ref)
+            ops.gemm(a, b, out, bias=bias, act=ops.ACT_GELU)
+            assert torch.equal(out, ref), n
+    finally:
+        ops.set_gemm_reserved_sms(0)
