@@ -13,6 +13,7 @@ path running on the sm_100a kernels.
 `patch_m3ae(model)` swaps the 12 BertCrossLayer instances of an EXISTING reference model for the B200 ones, re-using
                    its Parameter objects.
 """
+import collections.abc
 import json
 import os
 
@@ -37,8 +38,10 @@ except Exception:  # pragma: no cover
             self.hparams.config = config
 
         def log(self, name, value, **kw):
+            # kept as (detached) tensors: float() here would synchronise the host with the GPU in the middle of every step,
+            # before backward has been queued (pytorch_lightning's own log() defers the read as well)
             self.logged = getattr(self, "logged", {})
-            self.logged[name] = float(value) if torch.is_tensor(value) and value.numel() == 1 else value
+            self.logged[name] = value.detach() if torch.is_tensor(value) else value
 
         @property
         def device(self):
@@ -55,6 +58,32 @@ def init_weights(module):
         module.weight.data.fill_(1.0)
     if isinstance(module, nn.Linear) and module.bias is not None:
         module.bias.data.zero_()
+
+
+class _LazyAnswers(collections.abc.Sequence):
+    """list[str] of predicted answers (objectives.py:183-186), looked up on first use: reading it costs one device-to-host copy
+    and a synchronisation, which a training step that only needs the loss never pays."""
+
+    def __init__(self, predictions, label2ans):
+        self._pred, self._l2a, self._items = predictions.detach(), label2ans, None
+
+    def _get(self):
+        if self._items is None:
+            self._items = [self._l2a.get(str(p), str(p)) for p in self._pred.tolist()]
+            self._pred = None
+        return self._items
+
+    def __getitem__(self, i):
+        return self._get()[i]
+
+    def __len__(self):
+        return len(self._get()) if self._items is not None else int(self._pred.shape[0])
+
+    def __eq__(self, other):
+        return list(self._get()) == list(other)
+
+    def __repr__(self):
+        return repr(self._get())
 
 
 class Pooler(nn.Module):
@@ -275,8 +304,10 @@ class M3AETransformerSS(M3AEFusion):
         infer = self.infer(batch)
         logits = self.vqa_head(infer["multi_modal_cls_feats"])
         predictions = logits.argmax(dim=1)
-        l2a = self.label2ans()
-        english_answers = [l2a.get(str(p), str(p)) for p in predictions.tolist()]  # one D2H copy instead of B .item() calls
+        # objectives.py:183-186 turns every prediction into its answer string with one .item() per sample — B host syncs in the
+        # middle of every training step, before backward has even been queued.  The strings are only consumed by the CPU string
+        # metrics / logging, so they are materialised (one D2H copy) when something reads them.
+        english_answers = _LazyAnswers(predictions, self.label2ans())
         n = self.hparams.config["vqa_label_size"]
         rows, cols, vals = [], [], []
         for i, (labels, scores) in enumerate(zip(batch["vqa_labels"], batch["vqa_scores"])):

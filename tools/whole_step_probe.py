@@ -49,3 +49,24 @@ if os.environ.get("PROFILE", "0") == "1":
         step(0)
         torch.cuda.synchronize()
     print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=70))
+
+# ---- host-issue breakdown (no synchronisation inside a step: pure Python / launch overhead per segment)
+import collections
+seg = collections.defaultdict(float)
+torch.cuda.synchronize()
+for i in range(3):
+    b = batches[i % 2]
+    t = time.perf_counter(); opt.zero_grad(set_to_none=True); seg["zero_grad"] += time.perf_counter() - t
+    t = time.perf_counter(); ut = model.encode_text(b["text_ids"], b["text_masks"]); seg["text encoder fwd"] += time.perf_counter() - t
+    t = time.perf_counter(); ui = model.vision_encoder(b["image"][0]); seg["vision encoder fwd"] += time.perf_counter() - t
+    t = time.perf_counter(); ret = model.fuse(ut, ui, b["text_masks"], 1, False); seg["fusion fwd"] += time.perf_counter() - t
+    t = time.perf_counter()
+    logits = model.vqa_head(ret["multi_modal_cls_feats"])
+    targets = torch.zeros(len(logits), 498, device=dev)
+    from m3ae_b200 import functional as Fn
+    loss = Fn.vqa_bce_loss(logits, targets)
+    seg["head + loss"] += time.perf_counter() - t
+    t = time.perf_counter(); loss.backward(); seg["backward (all)"] += time.perf_counter() - t
+    t = time.perf_counter(); opt.step(); seg["optimizer step"] += time.perf_counter() - t
+    torch.cuda.synchronize()
+print("host ms per step by segment:", {k: round(v / 3 * 1e3, 2) for k, v in seg.items()})
