@@ -593,6 +593,64 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) gemm_tcgen05_kernel(const __gr
       const bool row_ok = row < q.M;
       float best = -INFINITY;  // row maximum of this warp's 64 columns and its column (epi.amax_val)
       int best_col = col_base < q.N ? col_base : 0;
+      // Arg-max only (the decoder's vocabulary projection: bias, no output tensor): the general path below spends ~25 instructions
+      // per element (scalar bias loads, run-time epilogue switches, a 16-deep dependent compare-select chain) — 26k warp
+      // instructions per 128x256 tile at 19 % issue rate, 30k of the kernel's 34k cycles (profiles/r2_ncu_vocab_gemm.txt).
+      // Here: vector bias loads, a max tree, and an index search only in the chunk that raises the maximum.
+      const bool amax_only = epi.amax_val != nullptr && epi.out == nullptr && epi.aux_out == nullptr && epi.act == M3AE_ACT_NONE &&
+                             epi.dact == M3AE_ACT_NONE && epi.residual == nullptr && epi.drop_p == 0.f && epi.alpha == 1.0f &&
+                             (epi.bias == nullptr || (((uintptr_t)epi.bias) & 15) == 0);
+      if (amax_only) {
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          const int col = col_base + c * 16;
+          if (col >= q.N || !cg_live) break;  // warp-uniform
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(tacc + (uint32_t)(c * 16), r);
+          tmem_ld_wait();
+          const int n_valid = min(16, q.N - col);
+          float v[16];
+          if (n_valid == 16) {
+            if (epi.bias != nullptr) {
+#pragma unroll
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 bq = __ldg(reinterpret_cast<const float4*>(epi.bias + col) + j4);
+                v[4 * j4 + 0] = __uint_as_float(r[4 * j4 + 0]) + bq.x; v[4 * j4 + 1] = __uint_as_float(r[4 * j4 + 1]) + bq.y;
+                v[4 * j4 + 2] = __uint_as_float(r[4 * j4 + 2]) + bq.z; v[4 * j4 + 3] = __uint_as_float(r[4 * j4 + 3]) + bq.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = j < n_valid ? __uint_as_float(r[j]) + (epi.bias ? __ldg(epi.bias + col + j) : 0.f) : -INFINITY;
+          }
+          float m8[8], m4[4];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) m8[j] = fmaxf(v[2 * j], v[2 * j + 1]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) m4[j] = fmaxf(m8[2 * j], m8[2 * j + 1]);
+          const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+          if (m > best) {  // strict: an equal maximum in a later chunk does not displace the first one
+            int jj = 15;
+#pragma unroll
+            for (int j = 14; j >= 0; --j) jj = v[j] == m ? j : jj;  // first column of the chunk that holds the maximum
+            best = m;
+            best_col = col + jj;
+          }
+        }
+        if (row_ok && cg_live && col_base < q.N) {
+          const int64_t g = (int64_t)(col_base >> 6) * epi.amax_ld + row;
+          epi.amax_val[g] = best;
+          epi.amax_idx[g] = best_col;
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) release_acc(acc);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         const int col = col_base + c * 16;
