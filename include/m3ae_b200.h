@@ -283,7 +283,8 @@ int m3ae_decoder_next_token(const float* amax_val, const int32_t* amax_idx, int3
  * The whole activation panel and the CTA's weight slice are staged in shared memory by one burst of cp.async; every CTA takes
  * 16 or 32 output columns.  Segmented output: column n goes to out[n / seg_cols] + row * ldo[n / seg_cols] + n % seg_cols
  * (the QKV projection writes q and the K / V cache rows in one launch).  ksplit > 1 splits K across CTAs (K / ksplit <= 768
- * per CTA): `ws` ([128, N] fp32) and `counters` ([ceil(N/16)] int32) must be ZERO on entry and are left zero. */
+ * per CTA): `ws` ([128, N] fp32) and `counters` (256 int32) must be ZERO on entry and are left zero.  A CTA takes a 2-D tile
+ * (128x16 ... 32x32 rows x columns, chosen for the fewest staged bytes per CTA at about one wave of CTAs). */
 typedef struct m3ae_skinny_params_t {
   const void* x;        /* [M, K] bf16 */
   int64_t ldx;

@@ -9,6 +9,10 @@
 // row-sized bulk copies (cp.async.bulk onto one mbarrier: one L2/DRAM round trip), every SM takes NC = 16 (or 32) output
 // columns, and the arithmetic is mma.sync.m16n8k16 on register fragments (0.2-0.6 GFLOP per launch: three orders of
 // magnitude below the tensor roofline, so tcgen05/TMEM plumbing would only add latency).
+//   * 2-D tiles: a CTA takes MTR rows x NC columns (128x16, 128x32, 64x32, 64x48 or 32x32, chosen so that about one wave of
+//     CTAs covers the output and the bytes a CTA stages — (MTR + NC) x K-chunk x 2 — are smallest): one SM ingests only
+//     ~24 B/clk from L2/HBM through bulk copies (profiles/r2_ncu_skinny.txt: 220 KB per CTA = 5 us of an 8-10 us launch), so
+//     the staged bytes per CTA, not the weight bytes, set the launch time.
 //   * LayerNorm folded into the A load (pre_norm -> QKV, layernorm1 -> cross Q, layernorm2 -> FFN-up): each warp normalises
 //     ITS 16 rows in shared memory (same two-pass fp32 statistics and the same summation order as ln_fwd_kernel, so the bf16
 //     operand is bit-identical to what the separate LayerNorm launch wrote) — three launches per token disappear.
@@ -45,23 +49,30 @@ struct SkinnyDev {
   m3ae_skinny_params_t p;
   int kc;        // K-chunk in shared memory
   int ntiles;    // ceil(N / NC)
+  int nrt;       // row tiles: ceil(M / MTR)
 };
 
-template <int NC>
+template <int MTR, int NC>
 __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S) {
+  constexpr int RW = MTR / 16;        // row warps
+  constexpr int CW = 8 / RW;          // column warps
+  constexpr int WC = NC / CW;         // columns per warp (multiple of 8)
+  constexpr int NTL = WC / 8;         // n-tiles per warp
+  static_assert(MTR % 16 == 0 && 8 % RW == 0 && NC % CW == 0 && WC % 8 == 0, "tile shape");
   pdl_sync();
   extern __shared__ __align__(16) uint8_t smem[];
   const m3ae_skinny_params_t& P = S.p;
   const int KC = S.kc, ksplit = P.ksplit, M = P.M, N = P.N;
   const int pitch = (KC + PAD) * 2;  // bytes per smem row
-  const uint32_t sA = smem_u32(smem), sW = sA + MT * pitch;
+  const uint32_t sA = smem_u32(smem), sW = sA + MTR * pitch;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int mi = lane >> 3, r8 = lane & 7;
   const bf16* __restrict__ X = (const bf16*)P.x;
   const bf16* __restrict__ W = (const bf16*)P.w;
   const int vec_per_row = KC >> 3;
-  int& s_last = *reinterpret_cast<int*>(smem + (MT + NC) * pitch);  // after the two tiles (the launcher adds 32 bytes)
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (MT + NC) * pitch + 8);
+  int& s_last = *reinterpret_cast<int*>(smem + (MTR + NC) * pitch);  // after the two tiles (the launcher adds 32 bytes)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (MTR + NC) * pitch + 8);
+  const int rw = warp % RW, cw = warp / RW;
   if (tid == 0) {
     mbar_init(bar, 1);
     fence_barrier_init();
@@ -70,24 +81,28 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
   uint32_t phase = 0;
   const uint32_t row_bytes = (uint32_t)KC * 2;
 
-  int a_chunk = -1;  // K-chunk currently resident in sA
-  const int nunits = S.ntiles * ksplit;
+  int a_chunk = -1;  // (row tile, K-chunk) currently resident in sA
+  const int nrt = S.nrt;
+  const int nunits = S.ntiles * ksplit * nrt;
+  // unit = ((column tile * ksplit) + K-chunk) * nrt + row tile; the grid is a multiple of nrt, so a CTA's units share its row tile
   for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
-    const int tile = unit / ksplit, ks = unit - tile * ksplit;
-    const int n0 = tile * NC, k0 = ks * KC;
+    const int rt = unit % nrt, rest = unit / nrt;
+    const int tile = rest / ksplit, ks = rest - tile * ksplit;
+    const int n0 = tile * NC, k0 = ks * KC, m0 = rt * MTR;
+    const int m_valid = M - m0 < MTR ? (M - m0 > 0 ? M - m0 : 0) : MTR;
     // ---- loads: one bulk copy (cp.async.bulk, 1-1.5 KB) per row of the CTA's weight slice and — unless it is already
     // resident — of the activation panel, all completing on one mbarrier.  (The first version issued 13.8k 16-byte cp.async
     // per CTA: 16k cycles for 220 KB, ~14 B/clk per SM — profiles/r2_ncu_skinny.txt.)
-    const bool load_a = a_chunk != ks;
-    const int w_valid = N - n0 < NC ? N - n0 : NC, a_valid = load_a ? M : 0;
+    const bool load_a = a_chunk != ks * nrt + rt;
+    const int w_valid = N - n0 < NC ? N - n0 : NC, a_valid = load_a ? m_valid : 0;
     if (tid == 0) mbar_expect_tx(bar, (uint32_t)(w_valid + a_valid) * row_bytes);
     fence_proxy_async();  // this thread's earlier generic-proxy reads of the tiles are ordered before the async-proxy writes
-    for (int r = tid; r < NC + (load_a ? MT : 0); r += NTH) {
+    for (int r = tid; r < NC + (load_a ? MTR : 0); r += NTH) {
       const bool is_w = r < NC;
       const int rr = is_w ? r : r - NC;
       const uint32_t dst = (is_w ? sW : sA) + rr * pitch;
-      if (rr < (is_w ? w_valid : M)) {
-        const bf16* src = is_w ? W + (int64_t)(n0 + rr) * P.ldw + k0 : X + (int64_t)rr * P.ldx + k0;
+      if (rr < (is_w ? w_valid : m_valid)) {
+        const bf16* src = is_w ? W + (int64_t)(n0 + rr) * P.ldw + k0 : X + (int64_t)(m0 + rr) * P.ldx + k0;
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"((uint64_t)src),
                      "r"(row_bytes), "r"(smem_u32(bar))
                      : "memory");
@@ -95,10 +110,10 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
         for (uint32_t c = 0; c < row_bytes; c += 16) asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst + c), "r"(0u) : "memory");
       }
     }
-    if (load_a) a_chunk = ks;
+    if (load_a) a_chunk = ks * nrt + rt;
     mbar_wait(bar, phase);
     phase ^= 1u;
-    if (load_a && P.ln_gamma != nullptr) {
+    if (MTR == MT && load_a && P.ln_gamma != nullptr) {  // folded LayerNorm: 128-row tiles only (each warp owns its 16 rows)
       // LayerNorm over the K = KC = 768 columns of this warp's rows, in place (ln_fwd_kernel's arithmetic and order)
       __syncwarp();
       float gam[3][8], bet[3][8];
@@ -147,30 +162,42 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
     __syncthreads();  // weight slice (all threads' copies) visible; A rows are warp-private but ordered by the same barrier
 
     // ---- [16 rows x NC] per warp over the K-chunk
-    float acc[NC / 8][4];
+    float acc[NTL][4];
 #pragma unroll
-    for (int j = 0; j < NC / 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
-    const uint32_t a_lane = sA + (warp * 16 + (mi & 1) * 8 + r8) * pitch + (mi >> 1) * 16;
-    const uint32_t b_lane = sW + ((mi >> 1) * 8 + r8) * pitch + (mi & 1) * 16;
-#pragma unroll 4
-    for (int kk = 0; kk < KC / 16; ++kk) {
-      uint32_t af[4];
-      ldsm_x4(af, a_lane + kk * 32);
+    for (int j = 0; j < NTL; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+    const uint32_t a_lane = sA + (rw * 16 + (mi & 1) * 8 + r8) * pitch + (mi >> 1) * 16;
+    // B fragments: one ldmatrix.x4 = one 8-column n-tile x two 16-wide k-steps (k 0-7 | 8-15 | 16-23 | 24-31)
+    const uint32_t b_lane = sW + (cw * WC + r8) * pitch + mi * 16;
+#pragma unroll 2
+    for (int kk2 = 0; kk2 < KC / 32; ++kk2) {
+      uint32_t af0[4], af1[4];
+      ldsm_x4(af0, a_lane + kk2 * 64);
+      ldsm_x4(af1, a_lane + kk2 * 64 + 32);
 #pragma unroll
-      for (int jp = 0; jp < NC / 16; ++jp) {
+      for (int j = 0; j < NTL; ++j) {
         uint32_t bb[4];
-        ldsm_x4(bb, b_lane + jp * 16 * pitch + kk * 32);
-        mma16816(acc[2 * jp], af, bb[0], bb[1]);
-        mma16816(acc[2 * jp + 1], af, bb[2], bb[3]);
+        ldsm_x4(bb, b_lane + j * 8 * pitch + kk2 * 64);
+        mma16816(acc[j], af0, bb[0], bb[1]);
+        mma16816(acc[j], af1, bb[2], bb[3]);
+      }
+    }
+    if (KC % 32) {  // K-chunk = 16 (mod 32): one more k-step (the second half of the x4 load stays inside the padded row)
+      uint32_t af0[4];
+      ldsm_x4(af0, a_lane + (KC / 32) * 64);
+#pragma unroll
+      for (int j = 0; j < NTL; ++j) {
+        uint32_t bb[4];
+        ldsm_x4(bb, b_lane + j * 8 * pitch + (KC / 32) * 64);
+        mma16816(acc[j], af0, bb[0], bb[1]);
       }
     }
 
     // ---- epilogue
-    const int row0 = warp * 16 + g, row1 = row0 + 8;
+    const int row0 = m0 + rw * 16 + g, row1 = row0 + 8;
     if (ksplit == 1) {
 #pragma unroll
-      for (int j = 0; j < NC / 8; ++j) {
-        const int n = n0 + j * 8 + 2 * t;
+      for (int j = 0; j < NTL; ++j) {
+        const int n = n0 + cw * WC + j * 8 + 2 * t;
         if (n >= N) continue;  // N is even: a column pair is in or out together
         const float b0 = P.bias ? P.bias[n] : 0.f, b1 = P.bias ? P.bias[n + 1] : 0.f;
         float v00 = acc[j][0] + b0, v01 = acc[j][1] + b1, v10 = acc[j][2] + b0, v11 = acc[j][3] + b1;
@@ -196,20 +223,20 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
     } else {
       // split-K: fp32 partials into the zeroed workspace [MT, N]; the last CTA of the column tile finishes it
 #pragma unroll
-      for (int j = 0; j < NC / 8; ++j) {
-        const int n = n0 + j * 8 + 2 * t;
+      for (int j = 0; j < NTL; ++j) {
+        const int n = n0 + cw * WC + j * 8 + 2 * t;
         if (n >= N) continue;
         if (row0 < M) { atomicAdd(P.ws + (int64_t)row0 * N + n, acc[j][0]); atomicAdd(P.ws + (int64_t)row0 * N + n + 1, acc[j][1]); }
         if (row1 < M) { atomicAdd(P.ws + (int64_t)row1 * N + n, acc[j][2]); atomicAdd(P.ws + (int64_t)row1 * N + n + 1, acc[j][3]); }
       }
       __threadfence();
       __syncthreads();
-      if (tid == 0) s_last = atomicAdd(P.counters + tile, 1) == ksplit - 1;
+      if (tid == 0) s_last = atomicAdd(P.counters + tile * nrt + rt, 1) == ksplit - 1;
       __syncthreads();
       if (s_last) {
         __threadfence();
-        for (int i = tid; i < MT * (NC / 2); i += NTH) {
-          const int row = i / (NC / 2), n = n0 + (i - row * (NC / 2)) * 2;
+        for (int i = tid; i < MTR * (NC / 2); i += NTH) {
+          const int row = m0 + i / (NC / 2), n = n0 + (i % (NC / 2)) * 2;
           if (row >= M || n >= N) continue;
           float* wsp = P.ws + (int64_t)row * N + n;
           const float2 s2 = __ldcg(reinterpret_cast<const float2*>(wsp));
@@ -223,24 +250,23 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
           *reinterpret_cast<uint32_t*>((bf16*)P.out[seg] + (int64_t)row * P.ldo[seg] + cn) = pack_bf16x2(v0, v1);
           *reinterpret_cast<float2*>(wsp) = make_float2(0.f, 0.f);  // leave the workspace zeroed for the next launch
         }
-        if (tid == 0) P.counters[tile] = 0;
+        if (tid == 0) P.counters[tile * nrt + rt] = 0;
       }
     }
     __syncthreads();  // before the next unit's copies overwrite the weight slice / activation panel
   }
 }
 
-template <int NC>
+template <int MTR, int NC>
 int launch(const SkinnyDev& S, int smem, int grid, cudaStream_t st) {
-  int dev = 0;
-  M3AE_CUDA(cudaGetDevice(&dev));
   static int done[64];
-  if (dev < 64 && !done[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(skinny_linear_kernel<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  const int slot = current_device_slot();
+  if (!done[slot]) {
+    cudaError_t e = cudaFuncSetAttribute(skinny_linear_kernel<MTR, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     M3AE_CHECK(e == cudaSuccess, M3AE_ERR_CUDA, "cudaFuncSetAttribute(skinny_linear) failed: %s", cudaGetErrorString(e));
-    done[dev] = 1;
+    done[slot] = 1;
   }
-  M3AE_LAUNCH((skinny_linear_kernel<NC>), grid, NTH, smem, st, S);
+  M3AE_LAUNCH((skinny_linear_kernel<MTR, NC>), grid, NTH, smem, st, S);
   count_launch();
   M3AE_CUDA(cudaGetLastError());
   return M3AE_OK;
@@ -270,14 +296,40 @@ int skinny_linear(const m3ae_skinny_params_t* p, cudaStream_t st) {
   S.p = *p;
   S.p.ksplit = ksplit;
   S.kc = kc;
-  // 32 columns per CTA when that still gives every SM work (fewer CTAs re-read the activation panel), else 16
-  const int nc = (((p->N + 31) / 32) * ksplit >= 96 && (MT + 32) * (kc + PAD) * 2 <= 227 * 1024) ? 32 : 16;
-  S.ntiles = (p->N + nc - 1) / nc;
-  const int smem = (MT + nc) * (kc + PAD) * 2 + 32;
-  M3AE_CHECK(smem <= 227 * 1024, M3AE_ERR_UNSUPPORTED, "skinny_linear: %d bytes of shared memory", smem);
-  const int units = S.ntiles * ksplit;
-  const int grid = units < sm_count() ? units : sm_count();
-  return nc == 32 ? launch<32>(S, smem, grid, st) : launch<16>(S, smem, grid, st);
+  // Tile shape: the fewest staged bytes per CTA, (MTR + NC) x kc, among the shapes that cover the output with at least ~2/3 of a
+  // wave of CTAs and at most ~2.6 waves; the folded LayerNorm needs the 128-row tile (each warp normalises the rows it owns).
+  struct Shape { int mtr, nc; };
+  const Shape shapes[] = {{32, 32}, {64, 32}, {64, 48}, {128, 16}, {128, 32}};
+  const int sms = sm_count();
+  int best = -1;
+  long best_cost = 0;
+  for (int i = 0; i < 5; ++i) {
+    const Shape& sh = shapes[i];
+    if (p->ln_gamma && sh.mtr != MT) continue;
+    const int smem_i = (sh.mtr + sh.nc) * (kc + PAD) * 2 + 32;
+    if (smem_i > 227 * 1024) continue;
+    const int nrt_i = (p->M + sh.mtr - 1) / sh.mtr;
+    const long units_i = (long)((p->N + sh.nc - 1) / sh.nc) * ksplit * nrt_i;
+    const long waves_x100 = units_i * 100 / sms;
+    // staged bytes per CTA, counted once per wave the CTA takes part in (the activation panel is re-used, the weights are not)
+    const long rounds = (units_i + sms - 1) / sms;
+    // + a second dependent load round trip (and, with split-K, a second pass of atomics + tile counters)
+    long cost = (long)sh.mtr * kc * 2 + rounds * sh.nc * kc * 2 + (rounds - 1) * (ksplit > 1 ? 60000 : 20000);
+    if (waves_x100 < 60) cost += cost * (60 - waves_x100) / 30;  // too few CTAs: the launch's latency chain gets no help
+    if (best < 0 || cost < best_cost) { best = i; best_cost = cost; }
+  }
+  M3AE_CHECK(best >= 0, M3AE_ERR_UNSUPPORTED, "skinny_linear: no tile shape fits (K-chunk %d)", kc);
+  const Shape sh = shapes[best];
+  S.ntiles = (p->N + sh.nc - 1) / sh.nc;
+  S.nrt = (p->M + sh.mtr - 1) / sh.mtr;
+  const int smem = (sh.mtr + sh.nc) * (kc + PAD) * 2 + 32;
+  const int units = S.ntiles * ksplit * S.nrt;
+  int grid = units < sms ? units : sms / S.nrt * S.nrt;  // a multiple of the row-tile count: a CTA keeps its row tile
+  if (grid < 1) grid = 1;
+  M3AE_CHECK(ksplit == 1 || S.ntiles * S.nrt <= 256, M3AE_ERR_UNSUPPORTED, "skinny_linear: split-K needs %d counters (256 at most)", S.ntiles * S.nrt);
+  if (sh.mtr == 32) return launch<32, 32>(S, smem, grid, st);
+  if (sh.mtr == 64) return sh.nc == 32 ? launch<64, 32>(S, smem, grid, st) : launch<64, 48>(S, smem, grid, st);
+  return sh.nc == 16 ? launch<128, 16>(S, smem, grid, st) : launch<128, 32>(S, smem, grid, st);
 }
 
 }  // namespace m3ae

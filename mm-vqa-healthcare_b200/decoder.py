@@ -328,7 +328,7 @@ class Decoder(nn.Module):
             f32 = torch.float32
             fp = lambda v: v.detach().to(f32).contiguous()  # noqa: E731
             ws = torch.zeros(128 * D, dtype=f32, device=dev)
-            ctr = torch.zeros(64, dtype=torch.int32, device=dev)
+            ctr = torch.zeros(256, dtype=torch.int32, device=dev)
             # LayerNorm folded into the projection's activation load only for small batches: every CTA normalises all B rows
             # redundantly (measured at B = 128: +7 us per launch against 4.3 us for the separate LayerNorm launch)
             fuse_ln = B <= 32

@@ -732,7 +732,7 @@ def test_skinny_linear_matches_layernorm_plus_gemm(M):
     y_ref = torch.empty(M, D, dtype=bf, device=DEV)
     ops.gemm(h_ref, w2, y_ref, bias=b2, residual=res)
     h, y = torch.empty(M, FF, dtype=bf, device=DEV), torch.empty(M, D, dtype=bf, device=DEV)
-    ws, ctr = torch.zeros(128 * D, device=DEV), torch.zeros(64, dtype=torch.int32, device=DEV)
+    ws, ctr = torch.zeros(128 * D, device=DEV), torch.zeros(256, dtype=torch.int32, device=DEV)
     up = ops.SkinnyLinear(x, w0, h, bias=b0, act=ops.ACT_RELU, ln=(gamma, beta, 1e-5))
     down = ops.SkinnyLinear(h, w2, y, bias=b2, residual=res, workspace=ws, counters=ctr)
     for rep in range(2):
