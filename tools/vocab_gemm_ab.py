@@ -1,5 +1,7 @@
+"""Times the decoder's vocabulary projection (M=128, N=30522, K=768, bias + arg-max partials) on the tcgen05 GEMM with wide (128x256)
+and skinny (128x64) tiles, L2 flushed between launches.  Usage (GPU box): python tools/vocab_gemm_ab.py"""
 import os, sys, torch
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import m3ae_b200
 from m3ae_b200 import ops
 dev="cuda"
