@@ -120,27 +120,40 @@ class ClipVisionEncoder(nn.Module):
 
 
 # ----------------------------------------------------------------------------- RoBERTa-base encoder layers
+def _roberta_params(layer):
+    """The layer's parameters in functional.PARAM_NAMES order (crossattention.* slots None: a RobertaLayer is a BertCrossLayer
+    without the cross-attention block; HF names attention.self.{query,key,value}, attention.output.{dense,LayerNorm},
+    intermediate.dense, output.{dense,LayerNorm})."""
+    att, so, out = layer.attention.self, layer.attention.output, layer.output
+    p = [None] * Fn.NP
+    p[Fn.WQ], p[Fn.BQ], p[Fn.WK], p[Fn.BK], p[Fn.WV], p[Fn.BV] = (att.query.weight, att.query.bias, att.key.weight, att.key.bias,
+                                                                att.value.weight, att.value.bias)
+    p[Fn.WO], p[Fn.BO], p[Fn.G1], p[Fn.B1] = so.dense.weight, so.dense.bias, so.LayerNorm.weight, so.LayerNorm.bias
+    p[Fn.W1], p[Fn.BI] = layer.intermediate.dense.weight, layer.intermediate.dense.bias
+    p[Fn.W2], p[Fn.BO3], p[Fn.G3], p[Fn.B3] = out.dense.weight, out.dense.bias, out.LayerNorm.weight, out.LayerNorm.bias
+    return p
+
+
 def roberta_layer(layer, h, mask_add, B, L, compute_dtype, training):
     """One HF RobertaLayer on rows h [B*L, 768]: self-attention (RobertaSelfAttention + RobertaSelfOutput) and FFN
     (RobertaIntermediate + RobertaOutput), post-LN, erf GELU — the arithmetic of BertCrossLayer's self-attention and FFN
-    blocks (bert_model.py:253-364,416-442) with this layer's own parameters.  mask_add: additive key mask [B, L] fp32."""
+    blocks (bert_model.py:253-364,416-442) with this layer's own parameters, so it runs as ONE fused autograd node of
+    `functional` (LayerConfig.has_cross False: persistent workspace, cached launch descriptors, one flat gradient buffer) instead
+    of eight composable nodes per layer: the whole-model step is host-bound and the 12 text layers were a third of its host time
+    (tools/whole_step_probe.py).  mask_add: additive key mask [B, L] fp32."""
     att, so = layer.attention.self, layer.attention.output
-    nh = att.num_attention_heads
+    key = (compute_dtype, float(att.dropout.p), float(so.dropout.p), float(so.LayerNorm.eps), int(att.num_attention_heads))
+    state = layer.__dict__.get("_m3ae_fused")
+    if state is None or state[0] != key:
+        cfg = Fn.LayerConfig(num_heads=key[4], eps=key[3], hidden_dropout=key[2], attn_dropout=key[1], compute_dtype=compute_dtype,
+                             has_cross=False)
+        state = (key, cfg, Fn.LayerOperands())
+        layer.__dict__["_m3ae_fused"] = state
+    _, cfg, operands = state
     D = h.shape[-1]
-    pa = float(att.dropout.p) if training else 0.0
-    ph = float(so.dropout.p) if training else 0.0
-    seed = Fn.new_seed() if training and (pa > 0 or ph > 0) else 0
-    wqkv = torch.cat([att.query.weight, att.key.weight, att.value.weight], dim=0)
-    bqkv = torch.cat([att.query.bias, att.key.bias, att.value.bias], dim=0)
-    qkv = Fn.linear(h, wqkv, bqkv, dtype=compute_dtype)
-    c = Fn.attention_packed(qkv, mask_add, B, nh, L, D // nh, drop_p=pa, drop_seed=seed,
-                     drop_site=0)
-    h1 = Fn.linear(c, so.dense.weight, so.dense.bias, dtype=compute_dtype, residual=h, drop_p=ph, drop_seed=seed, drop_site=1)
-    a = Fn.layernorm(h1, so.LayerNorm.weight, so.LayerNorm.bias, so.LayerNorm.eps)
-    out = layer.output
-    o = Fn.ffn(a, layer.intermediate.dense.weight, layer.intermediate.dense.bias, out.dense.weight, out.dense.bias, residual=a,
-               act=ops.ACT_GELU, dtype=compute_dtype, drop_p=ph, drop_seed=seed, drop_site=2)
-    return Fn.layernorm(o, out.LayerNorm.weight, out.LayerNorm.bias, out.LayerNorm.eps)
+    stream = dict(hidden=h.view(B, L, D), encoder=None, mask=mask_add, enc_mask=None, params=_roberta_params(layer), operands=operands)
+    (out,), = Fn.cross_layers_apply(cfg, training, [stream])
+    return out.reshape(B * L, D)
 
 
 def text_encoder_forward(language_encoder, text_ids, text_masks, compute_dtype, training):
