@@ -9,11 +9,13 @@
                      clip_model.py:27-33); the residual stream is kept in the compute dtype.
 `roberta_layer`      one HF `RobertaLayer` (post-LN BERT layer; called one by one with the additive mask at
                      m3ae_module.py:230-234) driven from the HF module's own Parameters: fused QKV GEMM, flash
-                     attention with the key-padding mask, out-proj + dropout + residual epilogue, LayerNorm, GELU FFN.
+                     attention with the key-padding mask, out-proj + dropout + residual epilogue, LayerNorm, GELU FFN —
+                     as ONE fused autograd node per layer (functional.cross_layers_apply with LayerConfig.has_cross=False:
+                     a RobertaLayer is a BertCrossLayer without its cross-attention block).
 
-Both are built from the composable autograd nodes in `functional` (linear / layernorm / attention / ffn): every matmul,
-attention, LayerNorm and activation on these paths is a kernel of libm3ae_b200.so; torch is used for the reshapes that
-build the patch matrix and for the embedding gathers.
+The ViT is built from the composable autograd nodes in `functional` (linear / layernorm / attention_packed / ffn); every
+matmul, attention, LayerNorm and activation on both paths is a kernel of libm3ae_b200.so; torch is used for the reshapes
+that build the patch matrix and for the embedding gathers.
 """
 from collections import OrderedDict
 
