@@ -37,7 +37,6 @@ constexpr int RLD = 72;    // fp32 row pitch of the cross-warp reduction buffer
 constexpr int OLD = 68;    // fp32 row pitch of the forward merge buffer
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
-constexpr int SMEM_2CTA = 115712;  // (228 KB - 2 x 1 KB reserved) / 2
 
 typedef bf16 (*Tile)[LDS];
 
@@ -64,7 +63,6 @@ __device__ __forceinline__ uint32_t movm_t(uint32_t a) {
 __device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // A-operand fragments (16 rows x 64 k) of rows [0, 16) of `tile`: f[kk] covers k = 16kk .. 16kk+15
 __device__ __forceinline__ void load_a_frags(uint32_t (&f)[4][4], Tile tile, int lane) {
@@ -300,7 +298,7 @@ __global__ void __launch_bounds__(NT, 2) attn_fwd_narrow_kernel(const m3ae_attn_
   bf16* __restrict__ O = (bf16*)P.out + (int64_t)b * Lq * P.ldo + h * D;
   float* __restrict__ lse = P.lse + sbase;
 
-  if (!NQ) {
+  if constexpr (!NQ) {
     for (int i = 0; i < nmine; ++i) {
       if (i % per == 0) {
         cp_async_wait_pending(NG - 1 - i / per);
@@ -325,9 +323,7 @@ __global__ void __launch_bounds__(NT, 2) attn_fwd_narrow_kernel(const m3ae_attn_
         if (q1 < Lq) lse[q1] = (m1 + log2f(l1)) * LN2;
       }
     }
-    return;
-  }
-
+  } else {
   // ---- queries narrow: this warp's key chunks against both row blocks
   uint32_t qa[2][4][4];
   float o[2][8][4], mm[2][2], ll[2][2];
@@ -400,6 +396,7 @@ __global__ void __launch_bounds__(NT, 2) attn_fwd_narrow_kernel(const m3ae_attn_
     *reinterpret_cast<uint4*>(O + (int64_t)q * P.ldo + d0) = w4;
     if (d0 == 0) lse[q] = (M + log2f(L)) * LN2;
   }
+  }  // NQ
 }
 
 // ------------------------------------------------------------------------------------------------ backward

@@ -40,10 +40,6 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t saddr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(saddr));
 }
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 struct SkinnyDev {
   m3ae_skinny_params_t p;
@@ -69,7 +65,6 @@ __global__ void __launch_bounds__(NTH, 1) skinny_linear_kernel(const SkinnyDev S
   const int mi = lane >> 3, r8 = lane & 7;
   const bf16* __restrict__ X = (const bf16*)P.x;
   const bf16* __restrict__ W = (const bf16*)P.w;
-  const int vec_per_row = KC >> 3;
   int& s_last = *reinterpret_cast<int*>(smem + (MTR + NC) * pitch);  // after the two tiles (the launcher adds 32 bytes)
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + (MTR + NC) * pitch + 8);
   const int rw = warp % RW, cw = warp / RW;
