@@ -214,3 +214,50 @@ def test_bce_and_cross_entropy_kernels_match_torch():
     ref = nn.CrossEntropyLoss(ignore_index=0)(lr.transpose(1, 2), tg)   # the reference's call, m3ae_decoder.py:365
     ref.backward()
     assert abs(loss.item() - ref.item()) / ref.item() < 1e-5 and rel(lg.grad, lr.grad) < 1e-5
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+def test_roberta_layer_fused_node_matches_hf_layer(dtype, tol):
+    """encoders.roberta_layer (ONE fused autograd node: the BertCrossLayer node with has_cross=False) against the HF RobertaLayer
+    it drives, eval mode, ragged key-padding mask: output, input gradient and every parameter gradient (the reference calls
+    these layers one by one at m3ae_module.py:230-234)."""
+    from transformers import RobertaConfig
+    from transformers.models.roberta.modeling_roberta import RobertaLayer
+    from m3ae_b200.encoders import roberta_layer
+    torch.manual_seed(3)
+    cfg = RobertaConfig(vocab_size=100, hidden_size=768, num_hidden_layers=1, num_attention_heads=12, intermediate_size=3072,
+                        max_position_embeddings=40, type_vocab_size=1, layer_norm_eps=1e-5)
+    cfg._attn_implementation = "eager"
+    layer = RobertaLayer(cfg).to(DEV).eval()
+    for p in layer.parameters():  # HF initialises LayerNorm to (1, 0): perturb so that gamma / beta gradients are exercised
+        if p.dim() == 1:
+            p.data.add_(0.1 * torch.randn_like(p))
+    B, L = 5, 32
+    x = torch.randn(B, L, 768, device=DEV)
+    lens = torch.tensor([32, 9, 17, 32, 8], device=DEV)
+    mask = (torch.arange(L, device=DEV)[None, :] < lens[:, None]).float()
+    mask_add = ((1.0 - mask) * -10000.0).contiguous()
+    xr = x.clone().requires_grad_(True)
+    ref = layer(xr, attention_mask=mask_add[:, None, None, :])
+    ref = ref[0] if isinstance(ref, tuple) else ref
+    w = torch.randn_like(ref)
+    (ref * w).sum().backward()
+    ref_grads = {n: p.grad.clone() for n, p in layer.named_parameters()}
+    dx_ref = xr.grad.clone()
+    for p in layer.parameters():
+        p.grad = None
+    xc = x.clone().requires_grad_(True)
+    out = roberta_layer(layer, xc.reshape(B * L, 768).to(dtype), mask_add, B, L, dtype, False).view(B, L, 768)
+    (out.float() * w).sum().backward()
+    assert rel(out, ref) < tol, rel(out, ref)
+    assert rel(xc.grad, dx_ref) < 2 * tol, rel(xc.grad, dx_ref)
+    worst = max(((n, rel(p.grad, ref_grads[n])) for n, p in layer.named_parameters()), key=lambda t: t[1])
+    assert all(p.grad is not None for p in layer.parameters())
+    # the key projection's bias gradient is identically zero in exact arithmetic (softmax is shift-invariant): compare by absolute size
+    for n, p in layer.named_parameters():
+        if n.endswith("key.bias"):
+            noise = 1e-3 if dtype == torch.float32 else 1e-2  # rounding noise around an exact zero, relative to the query bias gradient
+            assert p.grad.abs().max() < noise * ref_grads["attention.self.query.bias"].abs().max() + 1e-6
+        else:
+            assert rel(p.grad, ref_grads[n]) < 2 * tol, (n, rel(p.grad, ref_grads[n]))
+    print(f"roberta_layer {dtype}: out {rel(out, ref):.2e}, dx {rel(xc.grad, dx_ref):.2e}, worst parameter gradient {worst}")
