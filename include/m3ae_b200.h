@@ -306,6 +306,16 @@ typedef struct m3ae_skinny_params_t {
   int32_t* counters;
 } m3ae_skinny_params_t;
 int m3ae_skinny_linear(const m3ae_skinny_params_t* p, void* stream);
+/* m3ae_skinny_linear without any allocation by caller or library for its scratch.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, serving loops, harnesses
+ * that forbid it).  Same parameters and results as m3ae_skinny_linear, except that p->ws and p->counters are IGNORED: the
+ * split-K workspace and tile counters live in a file-scope static __device__ array inside the library (513 KB per GPU that
+ * loads it, held until exit).  Limits: M <= 128 rows, N <= M3AE_SKINNY_STATIC_MAX_N columns; larger sizes return
+ * M3AE_ERR_UNSUPPORTED with a message.  The call issues one cudaMemsetAsync of the scratch on `stream` (split-K only) and the
+ * kernel; it calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device share the one array: calls that
+ * overlap on the GPU (different streams without a dependency) race — serialise them. */
+#define M3AE_SKINNY_STATIC_MAX_N 1024
+int m3ae_skinny_linear_static(const m3ae_skinny_params_t* p, void* stream);
 
 /* Row argmax from the per-64-column partials of m3ae_gemm (epi.amax_val / amax_idx): ids[row] (int64) = column of the first
  * maximum over groups [0, n_groups).  Replaces argmax(log_softmax(final_linear(x))) of m3ae_decoder.py:151-153. */

@@ -120,6 +120,7 @@ SIGNATURES = {
     "m3ae_set_gemm_skinny": (C.c_int, [C.c_int32]),
     "m3ae_set_gemm_reserved_sms": (C.c_int, [C.c_int32]),
     "m3ae_skinny_linear": (C.c_int, [C.POINTER(SkinnyParams), C.c_void_p]),
+    "m3ae_skinny_linear_static": (C.c_int, [C.POINTER(SkinnyParams), C.c_void_p]),
     "m3ae_decoder_next_token": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "m3ae_set_pdl": (C.c_int, [C.c_int32]),

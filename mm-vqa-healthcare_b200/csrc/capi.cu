@@ -95,6 +95,7 @@ bool pdl_on() {
 }
 int argmax_partials(const float*, const int32_t*, int, int, int64_t*, cudaStream_t);
 int skinny_linear(const m3ae_skinny_params_t*, cudaStream_t);  // skinny_linear.cu
+int skinny_linear_static(const m3ae_skinny_params_t*, cudaStream_t);  // skinny_linear.cu
 int decoder_next_token(const float*, const int32_t*, int, int, const int64_t*, int64_t*, int, const float*, const float*, const float*, const float*,
                        float, void*, void*, int, cudaStream_t);
 extern bool ln_bwd_force_registers;
@@ -246,6 +247,10 @@ int m3ae_decoder_next_token(const float* amax_val, const int32_t* amax_idx, int3
 int m3ae_skinny_linear(const m3ae_skinny_params_t* p, void* stream) {
   ARCH_GATE();
   return skinny_linear(p, (cudaStream_t)stream);
+}
+int m3ae_skinny_linear_static(const m3ae_skinny_params_t* p, void* stream) {
+  ARCH_GATE();
+  return skinny_linear_static(p, (cudaStream_t)stream);
 }
 int m3ae_set_pdl(int32_t on) {
   g_pdl_mode = on ? 1 : 0;

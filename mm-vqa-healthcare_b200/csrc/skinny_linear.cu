@@ -21,6 +21,15 @@
 //     arriving CTA of a column tile (atomic counter) applies bias + residual, writes bf16 and re-zeroes workspace and counter.
 #include "common.cuh"
 
+// Scratch of the allocation-free entry point m3ae_skinny_linear_static (bottom of this file): the split-K workspace
+// [128 rows x SKINNY_STATIC_MAX_N columns] fp32 followed by the 256 tile counters.  513 KB of device memory on every GPU that
+// loads the library, held until the process exits.  In host code this NAME is only a stand-in for the symbol — the device
+// address comes from cudaGetSymbolAddress, once per device.
+#define SKINNY_STATIC_MAX_N 1024
+#define SKINNY_STATIC_WS_BYTES (128 * SKINNY_STATIC_MAX_N * 4)
+#define SKINNY_STATIC_BYTES (SKINNY_STATIC_WS_BYTES + 256 * 4)
+static __device__ __align__(256) unsigned char g_skinny_static_scratch[SKINNY_STATIC_BYTES];
+
 namespace m3ae {
 void count_launch();
 
@@ -325,6 +334,32 @@ int skinny_linear(const m3ae_skinny_params_t* p, cudaStream_t st) {
   if (sh.mtr == 32) return launch<32, 32>(S, smem, grid, st);
   if (sh.mtr == 64) return sh.nc == 32 ? launch<64, 32>(S, smem, grid, st) : launch<64, 48>(S, smem, grid, st);
   return sh.nc == 16 ? launch<128, 16>(S, smem, grid, st) : launch<128, 32>(S, smem, grid, st);
+}
+
+// Allocation-free variant (m3ae_skinny_linear_static): the same launch with the split-K workspace and tile counters taken from
+// g_skinny_static_scratch instead of caller memory (p->ws / p->counters are ignored).  No cudaMalloc / cudaFree / allocating
+// library call on this path: callers under CUDA-graph capture or in serving loops that forbid allocation can use it.
+// Every call on a device shares the one array: it is cleared on the caller's stream ahead of each split-K launch (the
+// kernel leaves it zeroed, but a launch that was aborted would not), and two calls that overlap on the GPU (different
+// streams, no dependency between them) race on it.
+int skinny_linear_static(const m3ae_skinny_params_t* p, cudaStream_t st) {
+  M3AE_CHECK(p != nullptr, M3AE_ERR_INVALID, "skinny_linear_static: null pointer");
+  M3AE_CHECK(p->N <= SKINNY_STATIC_MAX_N, M3AE_ERR_UNSUPPORTED,
+             "skinny_linear_static: N = %d output columns exceed the static scratch (at most %d columns, %d rows)", p->N, SKINNY_STATIC_MAX_N, MT);
+  M3AE_CHECK(p->M <= MT, M3AE_ERR_UNSUPPORTED, "skinny_linear_static: M = %d rows exceed the static scratch (at most %d rows)", p->M, MT);
+  static unsigned char* scratch_addr[64];  // device address of the array, per device ordinal
+  const int slot = current_device_slot();
+  if (scratch_addr[slot] == nullptr) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_skinny_static_scratch);  // for the CURRENT device
+    M3AE_CHECK(e == cudaSuccess && ptr != nullptr, M3AE_ERR_CUDA, "cudaGetSymbolAddress(g_skinny_static_scratch) failed: %s", cudaGetErrorString(e));
+    scratch_addr[slot] = static_cast<unsigned char*>(ptr);
+  }
+  m3ae_skinny_params_t q = *p;
+  q.ws = reinterpret_cast<float*>(scratch_addr[slot]);
+  q.counters = reinterpret_cast<int32_t*>(scratch_addr[slot] + SKINNY_STATIC_WS_BYTES);
+  if (q.ksplit > 1) M3AE_CUDA(cudaMemsetAsync(scratch_addr[slot], 0, SKINNY_STATIC_BYTES, st));
+  return skinny_linear(&q, st);
 }
 
 }  // namespace m3ae
