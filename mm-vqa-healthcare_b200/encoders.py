@@ -13,10 +13,11 @@
                      as ONE fused autograd node per layer (functional.cross_layers_apply with LayerConfig.has_cross=False:
                      a RobertaLayer is a BertCrossLayer without its cross-attention block).
 
-The ViT is built from the composable autograd nodes in `functional` (linear / layernorm / attention_packed / ffn); every
-matmul, attention, LayerNorm and activation on both paths is a kernel of libm3ae_b200.so; torch is used for the reshapes
-that build the patch matrix and for the embedding gathers.
+The ViT's residual attention blocks run as ONE fused autograd node each (vit_block.py; the patch embedding, ln_pre and ln_post
+are composable nodes of `functional`); every matmul, attention, LayerNorm and activation on both paths is a kernel of
+libm3ae_b200.so; torch is used for the reshapes that build the patch matrix and for the embedding gathers.
 """
+import os
 from collections import OrderedDict
 
 import torch
@@ -24,6 +25,10 @@ import torch.nn as nn
 
 from . import functional as Fn
 from . import ops
+from .vit_block import vit_block
+
+# M3AE_VIT_FUSED=0: run the CLIP blocks from the composable autograd nodes (A/B and cross-check of the fused node)
+VIT_FUSED = os.environ.get("M3AE_VIT_FUSED", "1") != "0"
 
 
 # ----------------------------------------------------------------------------- CLIP ViT-B/16 visual tower
@@ -100,6 +105,9 @@ class ClipVisionEncoder(nn.Module):
             x2 = x2.to(dt)
         x2 = Fn.layernorm(x2, v.ln_pre.weight, v.ln_pre.bias, v.ln_pre.eps)
         for blk in v.transformer.resblocks:
+            if VIT_FUSED:
+                x2 = vit_block(blk, x2, B, L)   # the same seven kernels as below, as ONE autograd node (vit_block.py)
+                continue
             nh = blk.n_head
             h = Fn.layernorm(x2, blk.ln_1.weight, blk.ln_1.bias, blk.ln_1.eps)
             qkv = Fn.linear(h, blk.attn.in_proj_weight, blk.attn.in_proj_bias, dtype=dt)

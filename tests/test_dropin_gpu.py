@@ -261,3 +261,76 @@ def test_roberta_layer_fused_node_matches_hf_layer(dtype, tol):
         else:
             assert rel(p.grad, ref_grads[n]) < 2 * tol, (n, rel(p.grad, ref_grads[n]))
     print(f"roberta_layer {dtype}: out {rel(out, ref):.2e}, dx {rel(xc.grad, dx_ref):.2e}, worst parameter gradient {worst}")
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+def test_vit_block_fused_node_matches_torch_block_and_composable_nodes(dtype, tol):
+    """vit_block.vit_block (ONE fused autograd node per CLIP ResidualAttentionBlock) against (a) the block's arithmetic in plain
+    torch fp32 through the module's own nn.MultiheadAttention, sequence-first as the reference runs it (clip_model.py:53-63), and
+    (b) the composable-node path it replaces (same kernels, same order: the output must be bit-identical); output, input gradient
+    and every parameter gradient, twice through the same workspace."""
+    from m3ae_b200 import functional as Fn
+    from m3ae_b200 import ops
+    from m3ae_b200.encoders import _ResBlock
+    from m3ae_b200.vit_block import vit_block
+    torch.manual_seed(5)
+    D, nh = 768, 12
+    blk = _ResBlock(D, nh).to(DEV).eval()
+    for p in blk.parameters():  # LayerNorm starts at (1, 0) and the biases at 0: perturb so that their gradients are exercised
+        if p.dim() == 1:
+            p.data.add_(0.1 * torch.randn_like(p))
+    B, L = 3, 50
+    x = torch.randn(B, L, D, device=DEV)
+    w = torch.randn(B, L, D, device=DEV)
+
+    def grads_and_reset():
+        g = {n: p.grad.clone() for n, p in blk.named_parameters()}
+        for p in blk.parameters():
+            p.grad = None
+        return g
+
+    xr = x.clone().requires_grad_(True)
+    xs = xr.permute(1, 0, 2)
+    h = blk.ln_1(xs)
+    x1 = xs + blk.attn(h, h, h, need_weights=False)[0]
+    u = blk.mlp.c_fc(blk.ln_2(x1))
+    ref = (x1 + blk.mlp.c_proj(u * torch.sigmoid(1.702 * u))).permute(1, 0, 2)
+    (ref * w).sum().backward()
+    ref_grads, dx_ref = grads_and_reset(), xr.grad.clone()
+
+    def fused():
+        xc = x.clone().requires_grad_(True)
+        out = vit_block(blk, xc.reshape(B * L, D).to(dtype), B, L).view(B, L, D)
+        (out.float() * w).sum().backward()
+        return out.detach(), xc.grad.clone(), grads_and_reset()
+
+    out, dx, grads = fused()
+    assert rel(out, ref) < tol, rel(out, ref)
+    assert rel(dx, dx_ref) < 2 * tol, rel(dx, dx_ref)
+    worst = max(((n, rel(grads[n], ref_grads[n])) for n in ref_grads), key=lambda t: t[1])
+    assert worst[1] < 2 * tol, worst
+    # the path it replaces (encoders.ClipVisionEncoder.forward_trans with M3AE_VIT_FUSED=0)
+    xd = x.clone().requires_grad_(True)
+    x2 = xd.reshape(B * L, D).to(dtype)
+    h = Fn.layernorm(x2, blk.ln_1.weight, blk.ln_1.bias, blk.ln_1.eps)
+    qkv = Fn.linear(h, blk.attn.in_proj_weight, blk.attn.in_proj_bias, dtype=dtype)
+    a = Fn.attention_packed(qkv, None, B, nh, L, D // nh)
+    x2 = Fn.linear(a, blk.attn.out_proj.weight, blk.attn.out_proj.bias, dtype=dtype, residual=x2)
+    h = Fn.layernorm(x2, blk.ln_2.weight, blk.ln_2.bias, blk.ln_2.eps)
+    out_c = Fn.ffn(h, blk.mlp.c_fc.weight, blk.mlp.c_fc.bias, blk.mlp.c_proj.weight, blk.mlp.c_proj.bias, residual=x2,
+                   act=ops.ACT_QUICKGELU, dtype=dtype).view(B, L, D)
+    (out_c.float() * w).sum().backward()
+    grads_c = grads_and_reset()
+    assert torch.equal(out_c.detach(), out), "same kernels on the same operands: bit-identical forward"
+    same = 1e-5 if dtype == torch.float32 else 1e-3  # attention backward / split-K sums: equal up to summation order
+    assert rel(dx, xd.grad) < same, rel(dx, xd.grad)
+    for n in grads:  # weight gradients are split-K atomic sums: equal up to fp32 summation order
+        assert rel(grads[n], grads_c[n]) < 1e-5, (n, rel(grads[n], grads_c[n]))
+    # second step re-uses the workspace and the cached launch descriptors
+    out2, dx2, grads2 = fused()
+    assert torch.equal(out2, out) and rel(dx2, dx) < same
+    assert all(rel(grads2[n], grads[n]) < 1e-5 for n in grads)
+    with torch.no_grad():  # inference call: no workspace is kept busy
+        out3 = vit_block(blk, x.reshape(B * L, D).to(dtype), B, L).view(B, L, D)
+    assert torch.equal(out3, out)
+    print(f"vit_block {dtype}: out {rel(out, ref):.2e}, dx {rel(dx, dx_ref):.2e}, worst parameter gradient {worst}")
