@@ -646,6 +646,16 @@ def bench_config1(args, dev):
     ms = _event_time(run, 20, torch.cuda.synchronize) / 20
     out = {"metric": "classifier forward samples/sec (infer + vqa_head, batch 8)", "value": round(8 / (ms * 1e-3), 1), "unit": "samples/s",
            "ms_per_forward": round(ms, 3), "dtype": "bf16", "model_tflops": round(8 / (ms * 1e-3) * 103.24e9 / 1e12, 1)}
+
+    def run_graphed(i):  # the same forward replayed from a CUDA graph (M3AETransformerSS.vqa_logits_graphed): input copies + replay + logits clone
+        with torch.no_grad():
+            return model.vqa_logits_graphed(batch)
+
+    for i in range(3):
+        run_graphed(i)
+    ms_g = _event_time(run_graphed, 20, torch.cuda.synchronize) / 20
+    out["cuda_graph"] = {"value": round(8 / (ms_g * 1e-3), 1), "unit": "samples/s", "ms_per_forward": round(ms_g, 3),
+                         "kernels_per_replay": next(iter(model._infer_graphs.values()))["kernels"]}
     del model
     if not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_config1_baseline()

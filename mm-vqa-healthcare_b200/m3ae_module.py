@@ -292,6 +292,63 @@ class M3AETransformerSS(M3AEFusion):
                     "text_masks": text_masks})
         return ret
 
+    # ---- serving path: the eval-mode classifier forward replayed from a CUDA graph
+    def _fused_states(self):
+        """Every operand cache / workspace pool the fused nodes of this model own (fusion layers, RoBERTa layers, CLIP blocks)."""
+        out = [l._operands for l in list(self.multi_modal_vision_layers) + list(self.multi_modal_language_layers)]
+        for m in self.modules():
+            st = m.__dict__.get("_m3ae_fused")
+            if st is not None:
+                out.append(st[2] if isinstance(st, tuple) else st)
+        return out
+
+    def vqa_logits_graphed(self, batch):
+        """logits = vqa_head(infer(batch)["multi_modal_cls_feats"]) (objectives.py:177-178) for an eval-mode model, replayed from a
+        CUDA graph: at batch 8 the eager forward is bound by the host (≈ 400 ctypes launches + PyTorch glue per call, §8(f)#4), the
+        replay by the GPU.  One graph per (input shapes, dtypes); the inputs are copied into the graph's static buffers, the logits
+        come back as a fresh tensor, bit-identical to the eager call (tests/test_full_model_gpu.py).  The graph reads the
+        compute-dtype operand caches as they were at capture: it is dropped when a parameter's address or version changes and
+        by every training-mode forward (fused optimizers do not bump version counters), and it keeps the workspaces it was
+        captured on alive.  Not for concurrent use from several streams."""
+        if self.training or torch.is_grad_enabled():
+            raise RuntimeError("vqa_logits_graphed is the inference path: call it on model.eval() under torch.no_grad()")
+        key_img = "image_0" if "image_0" in batch else "image"
+        img, ids, masks = batch[key_img][0], batch["text_ids"], batch["text_masks"]
+        if not img.is_cuda:
+            raise RuntimeError("M3AETransformerSS (B200) needs CUDA tensors: there is no CPU fallback")
+        graphs = self.__dict__.setdefault("_infer_graphs", {})
+        stamp = tuple((p.data_ptr(), p._version) for p in self.parameters())
+        key = (tuple(img.shape), img.dtype, tuple(ids.shape), ids.dtype, masks.dtype, self.compute_dtype, img.device)
+        entry = graphs.get(key)
+        if entry is not None and entry["stamp"] != stamp:
+            graphs.clear()
+            entry = None
+        if entry is None:
+            s_img, s_ids, s_masks = img.clone(), ids.clone(), masks.clone()
+            static = {key_img: [s_img], "text_ids": s_ids, "text_labels": s_ids, "text_masks": s_masks}
+
+            def run():
+                return self.vqa_head(self.infer(static)["multi_modal_cls_feats"])
+
+            for _ in range(2):  # eager warm-up: operand caches settle, workspaces / descriptors exist, one-time kernel attributes are set
+                run()
+            torch.cuda.synchronize(img.device)
+            graph = torch.cuda.CUDAGraph()
+            n0 = ops.launch_count()
+            with torch.cuda.graph(graph):
+                logits = run()
+            pinned = [list(st.workspaces) for st in self._fused_states()]  # their buffers are written by every replay
+            if len(graphs) >= 2:
+                graphs.pop(next(iter(graphs)))
+            entry = graphs[key] = dict(graph=graph, img=s_img, ids=s_ids, masks=s_masks, logits=logits, stamp=stamp, pinned=pinned,
+                                       kernels=ops.launch_count() - n0)
+        entry["img"].copy_(img, non_blocking=True)
+        entry["ids"].copy_(ids, non_blocking=True)
+        entry["masks"].copy_(masks, non_blocking=True)
+        entry["graph"].replay()
+        self.graph_replayed_launches = getattr(self, "graph_replayed_launches", 0) + entry["kernels"]
+        return entry["logits"].clone()
+
     def label2ans(self):
         """objectives.py:180-181 reads label2ans.json (CWD) every step; here it is read once.  Missing file: labels as text."""
         if self._label2ans is None:
@@ -329,6 +386,8 @@ class M3AETransformerSS(M3AEFusion):
 
     def forward(self, batch, test=False):
         ret = dict()
+        if self.training and "_infer_graphs" in self.__dict__:
+            self.__dict__["_infer_graphs"].clear()  # an optimizer step is about to move the weights the graphs were captured on
         if len(self.current_tasks) == 0:
             ret.update(self.infer(batch))
             return ret

@@ -134,3 +134,43 @@ def test_whole_model_gradients_b2_match_reference(dtype):
     for name in gold["no_grad"]:
         if name in params:
             assert params[name].grad is None or float(params[name].grad.abs().max()) == 0.0, name
+
+
+def test_graphed_classifier_forward_equals_eager_and_tracks_weight_updates():
+    """M3AETransformerSS.vqa_logits_graphed (config 1's forward replayed from a CUDA graph) against the eager infer + vqa_head on
+    the same model: bit-identical logits on the capture batch and on a second batch through the same graph; an in-place weight
+    update (version bump) and a training-mode forward both drop the graph, so the next call sees the new weights."""
+    model = build(torch.bfloat16)
+    b1, b2 = O.make_model_batch(51, 8, device=DEV), O.make_model_batch(52, 8, device=DEV)
+
+    def eager(batch):
+        with torch.no_grad():
+            return model.vqa_head(model.infer(batch)["multi_modal_cls_feats"])
+
+    with torch.no_grad():
+        e1, e2 = eager(b1), eager(b2)
+        g1 = model.vqa_logits_graphed(b1)
+        g2 = model.vqa_logits_graphed(b2)
+        g1b = model.vqa_logits_graphed(b1)
+    assert not torch.equal(e1, e2), "the two batches must differ"
+    assert torch.equal(g1, e1) and torch.equal(g2, e2) and torch.equal(g1b, e1)
+    kernels = next(iter(model._infer_graphs.values()))["kernels"]  # library kernels recorded in the graph (282 at this configuration)
+    assert len(model._infer_graphs) == 1 and kernels > 200 and model.graph_replayed_launches == 3 * kernels
+    gold = torch.load(GOLD)["b8"]
+    assert rel(g1, gold["vqa_logits"]) < TOL[torch.bfloat16]
+    with torch.no_grad():  # in-place update through the version counter (load_state_dict, non-fused optimizers)
+        model.vqa_head[0].weight.mul_(0.5)
+        e3 = eager(b1)
+        g3 = model.vqa_logits_graphed(b1)
+    assert not torch.equal(e3, e1) and torch.equal(g3, e3)
+    model.train()
+    model.current_tasks = ["vqa"]
+    model(b1)["vqa_loss"].backward()  # a training forward: an optimizer step may follow without bumping any version
+    assert len(model._infer_graphs) == 0
+    with pytest.raises(RuntimeError):
+        model.vqa_logits_graphed(b1)
+    model.eval()
+    with torch.no_grad():
+        for p in model.multi_modal_vision_pooler.parameters():
+            p.data.mul_(0.9)  # what a fused optimizer does: no version bump
+        assert torch.equal(model.vqa_logits_graphed(b1), eager(b1))
