@@ -426,13 +426,28 @@ __global__ void __launch_bounds__(128) decode_attn_kernel(const T* __restrict__ 
 // dependent chain per key: ~1 us per key, 102 us per call at B=128, Lm=359).  Here every phase issues independent 16-byte
 // loads: (1) scores, 4 lanes per key, 32 keys per CTA iteration; (2) block softmax over the scores in shared memory;
 // (3) O = P V with one thread per (16-byte slice of the head dimension, key residue), reduced through shared memory.
+// `stream_kv`: the cache is larger than what L2 can keep between two token steps (cross-attention memory: 141 MB per step at
+// B = 128): its 16-byte loads carry an L2 evict-first policy (and skip L1), so the pass does not push the decoder's ~66 MB of
+// projection / vocabulary weights — re-read by every token step — out of the 126 MB L2.
 constexpr int DEC_MAX_LEN = 1024;
+__device__ __forceinline__ uint4 ld_kv16(const bf16* p, uint64_t policy, bool stream_kv) {
+  uint4 v;
+  if (stream_kv)
+    asm("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.b32 {%0,%1,%2,%3}, [%4], %5;"
+        : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(policy));
+  else
+    v = __ldg(reinterpret_cast<const uint4*>(p));
+  return v;
+}
 template <int DH>
 __global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __restrict__ q, int64_t ldq, const bf16* __restrict__ kc,
                                                               const bf16* __restrict__ vc, int64_t ldk, int64_t ldv, int64_t bsk,
                                                               int64_t bsv, bf16* __restrict__ out, int64_t ldo, int H, int len,
-                                                              float scale) {
+                                                              float scale, int stream_kv_i) {
   pdl_sync();  // programmatic dependent launch: let the next kernel be scheduled, then wait for the previous one's results
+  const bool stream_kv = stream_kv_i != 0;
+  uint64_t policy = 0;
+  if (stream_kv) asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
   constexpr int NCH = DH / 8;        // 16-byte chunks per row (12 for dh 96, 8 for dh 64)
   constexpr int CPL = NCH / 4;       // chunks per lane in the score phase (4 lanes per key)
   constexpr int NG = 128 / NCH;      // key residues in the P V phase (10 / 16)
@@ -467,7 +482,7 @@ __global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __res
       const int j = j0 + u * 32 + kq;
       if (j < len) {
 #pragma unroll
-        for (int c = 0; c < CPL; ++c) kw[u][c] = __ldg(reinterpret_cast<const uint4*>(K + (size_t)j * ldk + (sub * CPL + c) * 8));
+        for (int c = 0; c < CPL; ++c) kw[u][c] = ld_kv16(K + (size_t)j * ldk + (sub * CPL + c) * 8, policy, stream_kv);
       }
     }
 #pragma unroll
@@ -523,7 +538,7 @@ __global__ void __launch_bounds__(128) decode_attn_bf16_kernel(const bf16* __res
       for (int u = 0; u < 4; ++u) {
         const int j = j0 + u * NG;
         p[u] = j < len ? sc[j] : 0.f;
-        vw[u] = j < len ? __ldg(reinterpret_cast<const uint4*>(V + (size_t)j * ldv + ch * 8)) : make_uint4(0u, 0u, 0u, 0u);
+        vw[u] = j < len ? ld_kv16(V + (size_t)j * ldv + ch * 8, policy, stream_kv) : make_uint4(0u, 0u, 0u, 0u);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -707,8 +722,11 @@ int decode_attn(const void* q, int64_t ldq, const void* kc, const void* vc, int6
   // bf16 with 16-byte aligned rows and a cache that fits the score buffer: the bandwidth kernel
   if (dtype == M3AE_BF16 && len <= DEC_MAX_LEN && ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && bsk % 8 == 0 && bsv % 8 == 0 &&
       ((((uintptr_t)q) | ((uintptr_t)kc) | ((uintptr_t)vc)) & 15) == 0) {
-    if (dh == 64) M3AE_LAUNCH((decode_attn_bf16_kernel<64>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
-    else M3AE_LAUNCH((decode_attn_bf16_kernel<96>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale);
+    // K + V bytes of this call; above 32 MB the cache is streamed with an L2 evict-first policy (M3AE_DECODE_EVICT_FIRST=0: off, A/B)
+    static const bool evict_env = [] { const char* e = getenv("M3AE_DECODE_EVICT_FIRST"); return !(e && e[0] == '0'); }();
+    const int stream_kv = evict_env && (int64_t)B * len * H * dh * 4 > (int64_t)32 << 20 ? 1 : 0;
+    if (dh == 64) M3AE_LAUNCH((decode_attn_bf16_kernel<64>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale, stream_kv);
+    else M3AE_LAUNCH((decode_attn_bf16_kernel<96>), B * H, 128, 0, st, (const bf16*)q, ldq, (const bf16*)kc, (const bf16*)vc, ldk, ldv, bsk, bsv, (bf16*)out, ldo, H, len, scale, stream_kv);
     count_launch();
     M3AE_CUDA(cudaGetLastError());
     return M3AE_OK;
