@@ -6,7 +6,7 @@ Why: built from the composable nodes (functional.layernorm / linear / attention_
 four separate weight casts, ~25 tensor allocations and as many ctypes struct constructions per step; with 11 blocks the
 whole-model step and the small-batch classifier forward are bound by that host time, not by the GPU (tools/whole_step_probe.py).
 Here a step is one ctypes call per kernel launch.  The kernels, their arguments and their order are the composable path's, so
-the activations are bit-identical to it (tests/test_encoders_gpu.py compares the two; M3AE_VIT_FUSED=0 selects the old path).
+the activations are bit-identical to it (tests/test_dropin_gpu.py compares the two; M3AE_VIT_FUSED=0 selects the old path).
 
 Forward (7 launches)                              kept for backward
   h1  = LN1(x)                                    h1, mean1, rstd1 (x is the caller's tensor)
